@@ -1,0 +1,179 @@
+/*
+ * isogs_rast.h -- C ABI of the B200-native (sm_100a) differentiable Gaussian
+ * rasterizer and the SLAM step kernels around it.
+ *
+ * Drop-in boundary for the hot path of mzli112358/IsoGS-SLAM-cpp.  Every entry
+ * point takes raw DEVICE pointers, sizes and a cudaStream_t (passed as void*);
+ * no torch types, no allocation, no exceptions.  Return value: 0 on success,
+ * negative ISOGS_E_* on error (text via isogs_last_error()).  All arrays are
+ * contiguous row-major fp32 unless stated.  The library is re-entrant per
+ * (device, stream) and keeps no global device state.
+ *
+ * Each entry point names the reference interface it replaces (file:line under
+ * /root/reference).
+ */
+#ifndef ISOGS_RAST_H
+#define ISOGS_RAST_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ISOGS_REC 12   /* floats per projected record and per gradient record */
+#define ISOGS_TILE 16
+
+#define ISOGS_OK 0
+#define ISOGS_E_ARG (-1)      /* bad argument */
+#define ISOGS_E_CUDA (-2)     /* CUDA runtime error */
+#define ISOGS_E_CAPACITY (-3) /* intersection buffers too small: *n_isects holds the need */
+
+/* flags (match the oracle's) */
+#define ISOGS_F_LOG_SCALES 1     /* scales are log-scales (python_ordinary/utils/slam_helpers.py:136) */
+#define ISOGS_F_LOGIT_OPAC 2     /* opacities are logits  (slam_helpers.py:135) */
+#define ISOGS_F_NO_OPAC_EXTENT 4 /* fixed 3.33 sigma extent (gsplat _torch_impl.py:356) */
+
+/* GaussianRasterizationSettings reduced to what the kernels need
+ * (python_ordinary/utils/recon_helpers.py:4-27; gsplat Ks/viewmats of Ops.h:42-64). */
+typedef struct isogs_camera {
+    int32_t width, height;
+    float fx, fy, cx, cy;
+    float R[9]; /* row-major world->camera rotation of the view matrix */
+    float t[3];
+    float near_plane, far_plane, eps2d;
+    float bg[3];
+} isogs_camera;
+
+/* per-frame pose applied before the view matrix == transform_to_frame
+ * (python_ordinary/utils/slam_helpers.py:252-304).  HOST struct. */
+typedef struct isogs_pose {
+    float q[4]; /* w,x,y,z un-normalised */
+    float t[3];
+} isogs_pose;
+
+const char* isogs_last_error(void);
+int isogs_version(void);
+
+/* ---- rasterizer forward, stage by stage ------------------------------------------------ */
+
+/* Bytes of scratch the scan / sort stages need for N Gaussians and `cap` intersections. */
+int isogs_temp_bytes(int64_t N, int64_t cap, size_t* scan_bytes, size_t* sort_bytes);
+
+/* preprocess: replaces diff_gaussian_rasterization's preprocessCUDA ==
+ * gsplat projection_ewa_3dgs_fused_fwd (Ops.h:42-64; ProjectionEWA3DGSFused.cu:16-212)
+ * + intersect_tile pass 1 (IntersectTile.cu:66-84) + cumsum (Intersect.cpp:79).
+ * scale_dim 1 = isotropic [N,1]; 3 = [N,3] with quats [N,4].
+ * pose (HOST, nullable) or pose_dev (DEVICE float[7] q,t; nullable) is applied first.
+ * ch 4: record colours {c0,c1,c2,z}; ch 5: {c0,c1,c2,z,z*z}.
+ * Outputs: rec [N,12], radii [N,2] i32, tiles [N] i32, cum [N] i32 (inclusive scan of tiles).
+ * If n_isects_host (PINNED or pageable HOST int64*) is non-null the call copies cum[N-1]
+ * there and synchronises the stream (the one sync of a forward, == Intersect.cpp:80). */
+int isogs_preprocess_fwd(const isogs_camera* cam, const isogs_pose* pose, const float* pose_dev,
+                         int64_t N, const float* means, const float* scales, int scale_dim,
+                         const float* quats, const float* opacities, const float* colors,
+                         int ch, int flags,
+                         float* rec, int32_t* radii, int32_t* tiles, int32_t* cum,
+                         void* scan_temp, size_t scan_temp_bytes,
+                         int64_t* n_isects_host, void* stream);
+
+/* duplicateWithKeys + radix sort + identifyTileRanges: replaces gsplat intersect_tile pass 2,
+ * radix_sort_double_buffer and intersect_offset (Ops.h:186-204; IntersectTile.cu:87-113,
+ * 296-339, 209-257).  keys_* [M] u64, vals_* [M] i32, tile_ranges [n_tiles+1] i32. */
+int isogs_tile_bin(const isogs_camera* cam, int64_t N, int64_t M,
+                   const float* rec, const int32_t* radii, const int32_t* cum,
+                   uint64_t* keys_unsorted, int32_t* vals_unsorted,
+                   uint64_t* keys_sorted, int32_t* vals_sorted, int32_t* tile_ranges,
+                   void* sort_temp, size_t sort_temp_bytes, void* stream);
+
+/* renderCUDA forward: replaces rasterize_to_pixels_3dgs_fwd (Ops.h:223-238;
+ * RasterizeToPixels3DGSFwd.cu:17-188).  render [ch,H,W] planar (the Inria API's CHW),
+ * alpha [H,W] = 1 - T_final (the silhouette), last [H,W] = sorted index of the last contributor. */
+int isogs_blend_fwd(const isogs_camera* cam, int ch, const float* rec, const int32_t* vals_sorted,
+                    const int32_t* tile_ranges, float* render, float* alpha, int32_t* last,
+                    void* stream);
+
+/* ---- rasterizer backward --------------------------------------------------------------- */
+
+/* renderCUDA backward: replaces rasterize_to_pixels_3dgs_bwd (Ops.h:239-264;
+ * RasterizeToPixels3DGSBwd.cu:15-278).  v_rec [N,12] must be ZEROED by the caller; receives
+ * v_x,v_y,v_conic_a,v_conic_b,v_conic_c,v_opacity,v_c0..v_c4,0 by atomic accumulation. */
+int isogs_blend_bwd(const isogs_camera* cam, int ch, int64_t N, const float* rec,
+                    const int32_t* vals_sorted, const int32_t* tile_ranges,
+                    const float* alpha, const int32_t* last,
+                    const float* v_render, const float* v_alpha /*nullable*/,
+                    float* v_rec, void* stream);
+
+/* preprocess backward: replaces projection_ewa_3dgs_fused_bwd (Ops.h:65-88;
+ * ProjectionEWA3DGSFused.cu:294-531) and, when a pose is given, the autograd backward of
+ * transform_to_frame (slam_helpers.py:252-304) including the N->7 pose reduction.
+ * Any output pointer may be null (gradient not needed).  v_pose: DEVICE float[7]
+ * (d/dq un-normalised, d/dt), must be zeroed by the caller; pose_acc: DEVICE float[16] scratch,
+ * zeroed by the caller.  v_means2d [N,3] (nullable) receives the Inria-style screen-space
+ * gradient side channel (splatam.py:528-530) = v_xy * (W/2, H/2). */
+int isogs_preprocess_bwd(const isogs_camera* cam, const isogs_pose* pose, const float* pose_dev,
+                         int64_t N, const float* means, const float* scales, int scale_dim,
+                         const float* quats, const float* opacities, int ch, int flags,
+                         const int32_t* radii, const float* v_rec,
+                         float* v_means, float* v_scales, float* v_quats, float* v_opac,
+                         float* v_colors, float* v_means2d,
+                         float* v_pose, float* pose_acc, void* stream);
+
+/* ---- the step around it ---------------------------------------------------------------- */
+
+/* fused masked L1 colour/depth loss on the 5-channel render: replaces get_loss's mask + L1
+ * section (python_ordinary/scripts/splatam.py:534-570,747-749).  mode 0 tracking (sums over
+ * gt_d>0 & !nan & sil>thres), mode 1 mapping (means).  Writes v_render [5,H,W] and
+ * losses (DEVICE float[4], zeroed by the caller) = {total, colour, depth, n_valid_depth}.
+ * For mode 1 n_valid (number of gt_depth>0 pixels) must be supplied by the caller as
+ * inv_n_depth = 1/n_valid (it is a per-frame constant). */
+int isogs_loss_l1_fused(const isogs_camera* cam, int mode, const float* render, const float* alpha,
+                        const float* gt_rgb, const float* gt_depth, float w_im, float w_depth,
+                        float sil_thres, int use_sil, float inv_n_depth,
+                        float* v_render, float* losses, void* stream);
+
+/* fused multi-tensor Adam with torch.optim.Adam semantics: replaces launch_adam_update
+ * (cpp/cuda/kernels/optimizer.cu:15-98), gsplat adam (Ops.h:173-183) and the Python
+ * torch.optim.Adam of splatam.py:402-408.  One launch covers n_groups tensors. */
+typedef struct isogs_adam_group {
+    float* param; const float* grad; float* exp_avg; float* exp_avg_sq;
+    int64_t numel; float lr;
+} isogs_adam_group;
+int isogs_adam_fused(const isogs_adam_group* groups /*HOST*/, int n_groups, float beta1, float beta2,
+                     float eps, int step, void* stream);
+
+/* silhouette-driven prune compaction: replaces prune_gaussians + remove_points
+ * (python_ordinary/utils/slam_external.py:139-188) and GaussianModel::prune
+ * (cpp/src/core/gaussian_model.cpp:291-331).  keep[i] = !(sigmoid(logit_o) < opac_thres ||
+ * max exp(log_s) > max_scale).  Order-preserving gather of n_rows row-major tensors.
+ * new_count: DEVICE int32. */
+typedef struct isogs_rows { const float* in; float* out; int32_t width; } isogs_rows;
+int isogs_prune_mask(int64_t N, const float* logit_opac, const float* log_scales, int scale_dim,
+                     float opac_thres, float max_scale, uint8_t* keep, void* stream);
+int isogs_compact(int64_t N, const uint8_t* keep, const isogs_rows* rows /*HOST*/, int n_rows,
+                  int32_t* scan /*[N] scratch*/, void* scan_temp, size_t scan_temp_bytes,
+                  int32_t* new_count, void* stream);
+
+/* silhouette-driven densification: replaces add_new_gaussians + get_pointcloud +
+ * initialize_new_params (splatam.py:799-841,298-348,763-796) and Mapper::addNewGaussians
+ * (cpp/src/slam/mapper.cpp:175-206).  Selects pixels with (alpha < sil_thres ||
+ * (render_depth > gt_d && |gt_d - render_depth| > depth_err_thres)) && gt_d > 0,
+ * back-projects them with the inverse of (pose, view) and appends, in pixel order, at
+ * offset *count (DEVICE int32, updated) up to capacity.  Appended rows:
+ * means[3], rgb[3], quat=[1,0,0,0], logit_opac=0, log_scale=log(z/((fx+fy)/2)) x scale_dim
+ * (+ noise_std * N(0,1) per axis from a counter-based generator keyed by (seed, pixel, axis)
+ * when scale_dim == 3: the IsoGS symmetry-breaking jitter of splatam.py:771-777). */
+int isogs_backproject_append(const isogs_camera* cam, const isogs_pose* pose,
+                             const float* gt_rgb, const float* gt_depth,
+                             const float* render_depth, const float* alpha,
+                             float sil_thres, float depth_err_thres,
+                             float* means, float* rgb, float* quats, float* logit_opac,
+                             float* log_scales, int scale_dim, float noise_std, uint64_t seed,
+                             int64_t capacity,
+                             int32_t* scan /*[2*H*W] scratch*/, void* scan_temp, size_t scan_temp_bytes,
+                             int32_t* count, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

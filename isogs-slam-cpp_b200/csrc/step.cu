@@ -1,0 +1,345 @@
+// step.cu -- north_star (5): fused masked L1 colour/depth loss, fused multi-tensor Adam, and the
+// silhouette-driven densify / prune compaction.  All HBM-streaming kernels.
+// References: python_ordinary/scripts/splatam.py:534-570,747-749 (loss), :402-408 (Adam),
+// :799-841,298-348,763-796 (densify); python_ordinary/utils/slam_external.py:139-188 (prune);
+// cpp/cuda/kernels/optimizer.cu:15-98; cpp/src/core/gaussian_model.cpp:291-331.
+#include <cub/device/device_scan.cuh>
+
+#include <cmath>
+
+#include "common.cuh"
+
+namespace isogs {
+
+// ------------------------------------------------------------------------------------------
+// loss
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float sgnf(float d) { return (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f); }
+
+__global__ void __launch_bounds__(256)
+loss_l1_kernel(int64_t P, int mode, const float* __restrict__ render, const float* __restrict__ alpha,
+               const float* __restrict__ gt_rgb, const float* __restrict__ gt_depth, float w_im, float w_depth,
+               float sil_thres, int use_sil, float inv_nd, float inv_nc, float* __restrict__ v_render,
+               float* __restrict__ losses) {
+    float sum_d = 0.f, sum_c = 0.f, cnt = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < P; i += (int64_t)gridDim.x * blockDim.x) {
+        const float d = render[3 * P + i], d2 = render[4 * P + i];
+        const float gd = gt_depth[i];
+        const float unc = d2 - d * d;
+        const bool nan_ok = !(isnan(d) || isnan(unc));
+        bool m = (gd > 0.f) && nan_ok;
+        bool mc = true;
+        if (mode == 0) {
+            if (use_sil) m = m && (alpha[i] > sil_thres);
+            mc = use_sil ? m : true;
+        }
+        if (gd > 0.f) cnt += 1.f;
+        const float dd = d - gd;
+        if (m) sum_d += fabsf(dd);
+        v_render[3 * P + i] = m ? (w_depth * inv_nd) * sgnf(dd) : 0.f;
+        v_render[4 * P + i] = 0.f;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float dc = render[k * P + i] - gt_rgb[k * P + i];
+            if (mc) sum_c += fabsf(dc);
+            v_render[k * P + i] = mc ? (w_im * inv_nc) * sgnf(dc) : 0.f;
+        }
+    }
+    __shared__ float sm[3][8];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        sum_d += __shfl_xor_sync(0xffffffffu, sum_d, off);
+        sum_c += __shfl_xor_sync(0xffffffffu, sum_c, off);
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
+    }
+    if (lane == 0) { sm[0][wid] = sum_d; sm[1][wid] = sum_c; sm[2][wid] = cnt; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float sd = 0.f, sc = 0.f, n = 0.f;
+        for (int w = 0; w < 8; ++w) { sd += sm[0][w]; sc += sm[1][w]; n += sm[2][w]; }
+        const float ld = sd * inv_nd, lc = sc * inv_nc;
+        atomicAdd(losses + 0, w_im * lc + w_depth * ld);
+        atomicAdd(losses + 1, lc);
+        atomicAdd(losses + 2, ld);
+        atomicAdd(losses + 3, n);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Adam (torch.optim.Adam semantics: bias-corrected, step counted from 1)
+// ------------------------------------------------------------------------------------------
+constexpr int MAX_GROUPS = 8;
+struct AdamArgs {
+    float* p[MAX_GROUPS]; const float* g[MAX_GROUPS]; float* m[MAX_GROUPS]; float* v[MAX_GROUPS];
+    int64_t numel[MAX_GROUPS];
+    int64_t block_start[MAX_GROUPS + 1]; // in units of blocks
+    float step_size[MAX_GROUPS];
+    int n;
+    float b1, b2, one_minus_b1, one_minus_b2, inv_bc2_sqrt, eps;
+};
+
+constexpr int ADAM_BLOCK = 256, ADAM_VEC = 4;
+
+__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamArgs& a, float step_size) {
+    const float mi = m + (g - m) * a.one_minus_b1;
+    const float vi = v * a.b2 + a.one_minus_b2 * g * g;
+    m = mi; v = vi;
+    const float denom = sqrtf(vi) * a.inv_bc2_sqrt + a.eps;
+    p = p - step_size * (mi / denom);
+}
+
+__global__ void __launch_bounds__(ADAM_BLOCK) adam_kernel(AdamArgs a) {
+    int grp = 0;
+#pragma unroll
+    for (int k = 1; k < MAX_GROUPS; ++k)
+        if (k < a.n && (int64_t)blockIdx.x >= a.block_start[k]) grp = k;
+    const int64_t local_block = (int64_t)blockIdx.x - a.block_start[grp];
+    const int64_t base = (local_block * ADAM_BLOCK + threadIdx.x) * ADAM_VEC;
+    const int64_t n = a.numel[grp];
+    if (base >= n) return;
+    float* p = a.p[grp]; const float* g = a.g[grp]; float* m = a.m[grp]; float* v = a.v[grp];
+    const float ss = a.step_size[grp];
+    const bool vec_ok = (base + ADAM_VEC <= n) &&
+                        ((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0);
+    if (vec_ok) {
+        float4 P4 = *reinterpret_cast<float4*>(p + base);
+        const float4 G4 = *reinterpret_cast<const float4*>(g + base);
+        float4 M4 = *reinterpret_cast<float4*>(m + base);
+        float4 V4 = *reinterpret_cast<float4*>(v + base);
+        adam_one(P4.x, G4.x, M4.x, V4.x, a, ss);
+        adam_one(P4.y, G4.y, M4.y, V4.y, a, ss);
+        adam_one(P4.z, G4.z, M4.z, V4.z, a, ss);
+        adam_one(P4.w, G4.w, M4.w, V4.w, a, ss);
+        *reinterpret_cast<float4*>(p + base) = P4;
+        *reinterpret_cast<float4*>(m + base) = M4;
+        *reinterpret_cast<float4*>(v + base) = V4;
+    } else {
+        for (int64_t i = base; i < n && i < base + ADAM_VEC; ++i) adam_one(p[i], g[i], m[i], v[i], a, ss);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// prune mask + order-preserving compaction
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+prune_mask_kernel(int64_t N, const float* __restrict__ logit_opac, const float* __restrict__ log_scales, int sd,
+                  float opac_thres, float max_scale, uint8_t* __restrict__ keep) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    bool rm = det_sigmoidf(logit_opac[i]) < opac_thres; // slam_external.py:175
+    float smax = det_expf(log_scales[sd * i]);
+    for (int k = 1; k < sd; ++k) smax = fmaxf(smax, det_expf(log_scales[sd * i + k]));
+    rm = rm || (smax > max_scale); // :177-179
+    keep[i] = rm ? 0 : 1;
+}
+
+constexpr int MAX_ROWS = 24;
+struct RowsArgs { const float* in[MAX_ROWS]; float* out[MAX_ROWS]; int width[MAX_ROWS]; int n; };
+
+__global__ void __launch_bounds__(256)
+compact_kernel(int64_t N, const uint8_t* __restrict__ keep, const int32_t* __restrict__ scan, RowsArgs rows,
+               int32_t* __restrict__ new_count) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const bool k = keep[i] != 0;
+    const int32_t dst = scan[i] - (k ? 1 : 0); // inclusive scan -> exclusive position
+    if (i == N - 1) *new_count = scan[i];
+    if (!k) return;
+    for (int r = 0; r < rows.n; ++r) {
+        const int w = rows.width[r];
+        const float* src = rows.in[r] + i * w;
+        float* d = rows.out[r] + (int64_t)dst * w;
+        for (int c = 0; c < w; ++c) d[c] = src[c];
+    }
+}
+
+__global__ void __launch_bounds__(256) u8_to_i32_kernel(int64_t N, const uint8_t* __restrict__ in, int32_t* __restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) out[i] = in[i] ? 1 : 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// silhouette-driven densification
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+densify_mask_kernel(int64_t P, const float* __restrict__ gt_depth, const float* __restrict__ render_depth,
+                    const float* __restrict__ alpha, float sil_thres, float depth_err_thres, int32_t* __restrict__ flag) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const float gd = gt_depth[i], rd = render_depth[i];
+    const float err = fabsf(gd - rd) * ((gd > 0.f) ? 1.f : 0.f); // splatam.py:811
+    const bool np = (alpha[i] < sil_thres) || ((rd > gd) && (err > depth_err_thres)); // :807,812,814
+    flag[i] = (np && gd > 0.f) ? 1 : 0;                                                // :826-827
+}
+
+__device__ __forceinline__ uint32_t hash_u32(uint64_t x) {
+    x ^= x >> 33; x *= 0xff51afd7ed558ccdull; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull; x ^= x >> 33;
+    return (uint32_t)x;
+}
+__device__ __forceinline__ float counter_normal(uint64_t seed, uint64_t idx, int axis) {
+    const uint64_t c = seed * 0x9E3779B97F4A7C15ull + idx * 6ull + (uint64_t)axis * 2ull;
+    const float u1 = ((float)(hash_u32(c) >> 8) + 0.5f) * (1.0f / 16777216.0f);
+    const float u2 = ((float)(hash_u32(c + 1) >> 8) + 0.5f) * (1.0f / 16777216.0f);
+    return sqrtf(-2.0f * logf(u1)) * cospif(2.0f * u2);
+}
+
+__global__ void __launch_bounds__(256)
+densify_append_kernel(DevCam cam, DevPose pose, const float* __restrict__ gt_rgb, const float* __restrict__ gt_depth,
+                      const int32_t* __restrict__ flag, const int32_t* __restrict__ scan, float* __restrict__ means,
+                      float* __restrict__ rgb, float* __restrict__ quats, float* __restrict__ logit_opac,
+                      float* __restrict__ log_scales, int sd, float noise_std, uint64_t seed, int64_t capacity,
+                      const int32_t* __restrict__ count_in) {
+    const int64_t P = (int64_t)cam.width * cam.height;
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const int32_t base = *count_in;
+    if (!flag[i]) return;
+    const int64_t dst = (int64_t)base + scan[i] - 1;
+    if (dst >= capacity) return;
+    const int px = (int)(i % cam.width), py = (int)(i / cam.width);
+    const float z = gt_depth[i];
+    // get_pointcloud, splatam.py:306-322 (integer pixel coordinates)
+    float pc[3] = {((float)px - cam.cx) / cam.fx * z, ((float)py - cam.cy) / cam.fy * z, z};
+    // inverse of view then of pose: p_f = Rv^T (p_c - tv), p_w = Rp^T (p_f - tp)
+    float d[3] = {pc[0] - cam.t[0], pc[1] - cam.t[1], pc[2] - cam.t[2]};
+    float pf[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) pf[k] = cam.R[k] * d[0] + cam.R[3 + k] * d[1] + cam.R[6 + k] * d[2];
+    float pw[3] = {pf[0], pf[1], pf[2]};
+    if (pose.mode != 0) {
+        float q[4], t[3], Rp[9];
+        for (int k = 0; k < 4; ++k) q[k] = (pose.mode == 2) ? pose.dev[k] : pose.q[k];
+        for (int k = 0; k < 3; ++k) t[k] = (pose.mode == 2) ? pose.dev[4 + k] : pose.t[k];
+        quat_to_R(q, Rp, nullptr, nullptr);
+        float e[3] = {pf[0] - t[0], pf[1] - t[1], pf[2] - t[2]};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) pw[k] = Rp[k] * e[0] + Rp[3 + k] * e[1] + Rp[6 + k] * e[2];
+    }
+    means[3 * dst] = pw[0]; means[3 * dst + 1] = pw[1]; means[3 * dst + 2] = pw[2];
+    rgb[3 * dst] = gt_rgb[i]; rgb[3 * dst + 1] = gt_rgb[P + i]; rgb[3 * dst + 2] = gt_rgb[2 * P + i];
+    if (quats) { quats[4 * dst] = 1.f; quats[4 * dst + 1] = 0.f; quats[4 * dst + 2] = 0.f; quats[4 * dst + 3] = 0.f; }
+    logit_opac[dst] = 0.f;
+    const float ls = det_logf(z / ((cam.fx + cam.fy) / 2.0f)); // splatam.py:330-331,769
+    for (int k = 0; k < sd; ++k)
+        log_scales[sd * dst + k] = (sd == 3 && noise_std > 0.f) ? ls + noise_std * counter_normal(seed, (uint64_t)i, k) : ls;
+}
+
+// runs after the append kernel (stream order), so no thread still reads the old count
+__global__ void densify_count_kernel(int64_t P, const int32_t* __restrict__ scan, int64_t capacity, int32_t* count) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        int64_t total = (int64_t)(*count) + scan[P - 1];
+        *count = (int32_t)(total < capacity ? total : capacity);
+    }
+}
+
+} // namespace isogs
+
+using namespace isogs;
+
+extern "C" int isogs_loss_l1_fused(const isogs_camera* cam, int mode, const float* render, const float* alpha,
+                                   const float* gt_rgb, const float* gt_depth, float w_im, float w_depth,
+                                   float sil_thres, int use_sil, float inv_n_depth, float* v_render, float* losses,
+                                   void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!cam || (mode != 0 && mode != 1)) { set_error("isogs_loss_l1_fused: bad argument"); return ISOGS_E_ARG; }
+    const int64_t P = (int64_t)cam->width * cam->height;
+    if (P == 0) return ISOGS_OK;
+    const float inv_nd = (mode == 1) ? inv_n_depth : 1.0f;
+    const float inv_nc = (mode == 1) ? 1.0f / (float)(3 * P) : 1.0f;
+    const int blocks = (int)std::min<int64_t>((P + 255) / 256, 148 * 8);
+    loss_l1_kernel<<<blocks, 256, 0, stream>>>(P, mode, render, alpha, gt_rgb, gt_depth, w_im, w_depth, sil_thres,
+                                               use_sil, inv_nd, inv_nc, v_render, losses);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
+
+extern "C" int isogs_adam_fused(const isogs_adam_group* groups, int n_groups, float beta1, float beta2, float eps,
+                                int step, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!groups || n_groups < 0 || n_groups > MAX_GROUPS || step < 1) {
+        set_error("isogs_adam_fused: bad argument (n_groups=%d, max %d, step=%d)", n_groups, MAX_GROUPS, step);
+        return ISOGS_E_ARG;
+    }
+    AdamArgs a;
+    a.n = 0;
+    const double bc1 = 1.0 - std::pow((double)beta1, step);
+    const double bc2 = 1.0 - std::pow((double)beta2, step);
+    a.b1 = beta1; a.b2 = beta2;
+    a.one_minus_b1 = 1.0f - beta1; a.one_minus_b2 = 1.0f - beta2;
+    a.inv_bc2_sqrt = (float)(1.0 / std::sqrt(bc2));
+    a.eps = eps;
+    int64_t blocks = 0;
+    for (int k = 0; k < n_groups; ++k) {
+        const isogs_adam_group& g = groups[k];
+        if (g.grad == nullptr || g.numel <= 0) continue; // torch skips params whose .grad is None
+        const int j = a.n++;
+        a.p[j] = g.param; a.g[j] = g.grad; a.m[j] = g.exp_avg; a.v[j] = g.exp_avg_sq;
+        a.numel[j] = g.numel;
+        a.step_size[j] = (float)((double)g.lr / bc1);
+        a.block_start[j] = blocks;
+        blocks += (g.numel + (int64_t)ADAM_BLOCK * ADAM_VEC - 1) / ((int64_t)ADAM_BLOCK * ADAM_VEC);
+    }
+    a.block_start[a.n] = blocks;
+    if (blocks == 0) return ISOGS_OK;
+    adam_kernel<<<(unsigned)blocks, ADAM_BLOCK, 0, stream>>>(a);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
+
+extern "C" int isogs_prune_mask(int64_t N, const float* logit_opac, const float* log_scales, int scale_dim,
+                                float opac_thres, float max_scale, uint8_t* keep, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (N < 0 || (scale_dim != 1 && scale_dim != 3)) { set_error("isogs_prune_mask: bad argument"); return ISOGS_E_ARG; }
+    if (N == 0) return ISOGS_OK;
+    prune_mask_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(N, logit_opac, log_scales, scale_dim, opac_thres,
+                                                                       max_scale, keep);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
+
+extern "C" int isogs_compact(int64_t N, const uint8_t* keep, const isogs_rows* rows, int n_rows, int32_t* scan,
+                             void* scan_temp, size_t scan_temp_bytes, int32_t* new_count, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (N < 0 || n_rows < 0 || n_rows > MAX_ROWS || N >= (1ll << 31)) { set_error("isogs_compact: bad argument"); return ISOGS_E_ARG; }
+    if (N == 0) { ISOGS_CUDA(cudaMemsetAsync(new_count, 0, sizeof(int32_t), stream)); return ISOGS_OK; }
+    u8_to_i32_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(N, keep, scan);
+    size_t need = 0;
+    ISOGS_CUDA(cub::DeviceScan::InclusiveSum(nullptr, need, scan, scan, (int)N, stream));
+    if (need > scan_temp_bytes) { set_error("scan temp too small"); return ISOGS_E_ARG; }
+    ISOGS_CUDA(cub::DeviceScan::InclusiveSum(scan_temp, scan_temp_bytes, scan, scan, (int)N, stream));
+    RowsArgs ra;
+    ra.n = n_rows;
+    for (int r = 0; r < n_rows; ++r) { ra.in[r] = rows[r].in; ra.out[r] = rows[r].out; ra.width[r] = rows[r].width; }
+    compact_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(N, keep, scan, ra, new_count);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
+
+extern "C" int isogs_backproject_append(const isogs_camera* cam, const isogs_pose* pose, const float* gt_rgb,
+                                        const float* gt_depth, const float* render_depth, const float* alpha,
+                                        float sil_thres, float depth_err_thres, float* means, float* rgb, float* quats,
+                                        float* logit_opac, float* log_scales, int scale_dim, float noise_std,
+                                        uint64_t seed, int64_t capacity, int32_t* scan, void* scan_temp,
+                                        size_t scan_temp_bytes, int32_t* count, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!cam || (scale_dim != 1 && scale_dim != 3)) { set_error("isogs_backproject_append: bad argument"); return ISOGS_E_ARG; }
+    const int64_t P = (int64_t)cam->width * cam->height;
+    if (P == 0) return ISOGS_OK;
+    DevCam dc = make_devcam(*cam);
+    DevPose dp = make_devpose(pose, nullptr);
+    // flags live in the upper half of the scan scratch: scan must hold 2*P int32
+    int32_t* flag = scan + P;
+    densify_mask_kernel<<<(unsigned)((P + 255) / 256), 256, 0, stream>>>(P, gt_depth, render_depth, alpha, sil_thres,
+                                                                         depth_err_thres, flag);
+    size_t need = 0;
+    ISOGS_CUDA(cub::DeviceScan::InclusiveSum(nullptr, need, flag, scan, (int)P, stream));
+    if (need > scan_temp_bytes) { set_error("scan temp too small"); return ISOGS_E_ARG; }
+    ISOGS_CUDA(cub::DeviceScan::InclusiveSum(scan_temp, scan_temp_bytes, flag, scan, (int)P, stream));
+    densify_append_kernel<<<(unsigned)((P + 255) / 256), 256, 0, stream>>>(dc, dp, gt_rgb, gt_depth, flag, scan, means, rgb,
+                                                                           quats, logit_opac, log_scales, scale_dim,
+                                                                           noise_std, seed, capacity, count);
+    densify_count_kernel<<<1, 32, 0, stream>>>(P, scan, capacity, count);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
