@@ -1,0 +1,343 @@
+"""bench.py -- the driver's measurement contract for the IsoGS-SLAM hot path on B200.
+
+A "step" is ONE MAPPING ITERATION on one keyframe: transform_to_frame + activations + fused
+5-channel render (rgb, depth, depth^2; silhouette = alpha) + masked-L1 loss + backward
+(blend bwd + projection bwd) + fused Adam on every Gaussian parameter
+(python_ordinary/scripts/splatam.py:1412-1476 with the L1 terms; SSIM/flat/iso are SURVEY 8(f) "next").
+Workload at N=1: BASELINE.json configs[2] shape -- Replica-shaped 1200x680, 1 M isotropic Gaussians.
+
+  python bench.py [--gpus N --steps K --warmup W] [--impl reference]
+
+N > 1 (torchrun): every rank renders a DIFFERENT keyframe of the 8-keyframe window against the
+replicated map; one NCCL all-reduce of the flat gradient buffer per iteration; weak scaling,
+value = keyframe-renders (iterations x ranks) per second.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SHAPE = os.environ.get("ISOGS_BENCH_SHAPE", "replica")
+N_GAUSS = int(os.environ.get("ISOGS_BENCH_N", "1000000"))
+WINDOW = 8
+METRIC = "mapping iters/s (render fwd+bwd + L1 loss + Adam) @1200x680, 1M iso Gaussians"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        self.stop_flag = True
+        sm = [int(r[0]) for r in self.rows if len(r) >= 6 and r[0].isdigit()]
+        mx = [int(r[1]) for r in self.rows if len(r) >= 6 and r[1].isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 6:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": int(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_workload(shape, n_gauss, window):
+    import importlib
+
+    import isogs_b200  # noqa: F401
+    syn = importlib.import_module("isogs_slam_cpp_b200.synthetic")
+    params, frames, K = syn.make_map(shape, n_gauss, isotropic=True, seed=0, max_frames=max(window, 8))
+    traj = syn.trajectory(64, step=4.0)
+    while len(frames) < window:
+        k = len(frames)
+        c, d, _ = syn.render_frame(shape, traj[k], seed=k)
+        frames.append((c, d, traj[k]))
+    frames = frames[:window]
+    keyframes = []
+    for c, d, w2c in frames:
+        q, t = syn.w2c_to_pose(w2c)
+        keyframes.append(dict(rgb=c, depth=d[0], q=q, t=t, inv_nd=1.0 / max(1, int((d > 0).sum()))))
+    return syn, params, keyframes
+
+
+def algorithmic_bytes(N, V, M, P, n_tiles):
+    """SURVEY.md 8(d) per-stage algorithmic bytes (isotropic: g_in 20 B, g_col 12 B, rec 32 B)."""
+    g_in, g_col, rec = 20, 12, 32
+    return {
+        "preprocess_fwd": N * (g_in + g_col) + V * (rec + 4),
+        "tile_bin": 12 * M + 24 * M + 4 * M + 8 * n_tiles,
+        "blend_fwd": M * (4 + rec + 12) + P * 9 * 4,
+        "loss": P * (7 + 4) * 4 + P * 7 * 4,
+        "blend_bwd": M * (4 + rec + 12) + P * 9 * 4 + 2 * V * 40,
+        "preprocess_bwd": V * (40 + g_in) + N * (g_in + g_col),
+        "adam": (N * (g_in + g_col) // 4) * 28,
+    }
+
+
+def run_ours(args):
+    import importlib
+
+    import torch
+    import torch.distributed as dist
+
+    import isogs_b200
+    pkg = isogs_b200.pkg
+    ss = importlib.import_module("isogs_slam_cpp_b200.slam_step")
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    syn, params, kfs = build_workload(SHAPE, N_GAUSS, WINDOW)
+    W, H, fx, fy, cx, cy = syn.SHAPES[SHAPE][:6]
+    cam = pkg.make_camera(W, H, fx, fy, cx, cy)
+    gmap = ss.GaussianMap(params, device=dev)
+    ws = ss.StepWorkspace(cam, gmap.count, dev)
+    P = W * H
+    # keyframes resident in HBM (for `value`) and in pinned host memory (for `e2e`)
+    for k in kfs:
+        k["pose"] = pkg.make_pose(k["q"], k["t"])
+        k["rgb_d"] = torch.from_numpy(k["rgb"]).to(dev)
+        k["depth_d"] = torch.from_numpy(k["depth"]).to(dev)
+        k["rgb_h"] = torch.from_numpy(k["rgb"]).pin_memory()
+        k["depth_h"] = torch.from_numpy(k["depth"]).pin_memory()
+    stage_rgb = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    stage_depth = torch.empty((H, W), dtype=torch.float32, device=dev)
+    loss_host = torch.empty((4,), dtype=torch.float32).pin_memory()
+
+    def allreduce(flat):
+        dist.all_reduce(flat)          # sum; averaged by scaling the learning signal below
+        flat.mul_(1.0 / world)
+    ar = allreduce if world > 1 else None
+
+    def step_resident(i, marks=None):
+        k = kfs[(i * world + rank) % WINDOW]
+        return ss.map_step(ws, gmap, k["pose"], k["rgb_d"], k["depth_d"], k["inv_nd"], allreduce=ar, marks=marks)
+
+    def step_e2e(i):
+        k = kfs[(i * world + rank) % WINDOW]
+        stage_rgb.copy_(k["rgb_h"], non_blocking=True)
+        stage_depth.copy_(k["depth_h"], non_blocking=True)
+        losses = ss.map_step(ws, gmap, k["pose"], stage_rgb, stage_depth, k["inv_nd"], allreduce=ar)
+        loss_host.copy_(losses, non_blocking=True)
+        torch.cuda.current_stream().synchronize()   # the user reads the loss every iteration
+        return float(loss_host[0])
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, marks_list=None):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            if marks_list is not None:
+                m = []
+                fn(i, m)
+                marks_list.append(m)
+            else:
+                fn(i)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for i in range(max(3, args.warmup)):
+        step_resident(i)
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    marks_list = []
+    ms_total = timed(step_resident, args.steps, marks_list)
+    clocks = sampler.summary() if sampler else None
+    M = ws.M
+    V = int((ws.radii[:gmap.count, 0] > 0).sum().item())
+    # per-stage device time from the events recorded INSIDE the timed region
+    stage_ms = {}
+    for m in marks_list:
+        for (n0, ev0), (n1, ev1) in zip(m[:-1], m[1:]):
+            stage_ms[n1] = stage_ms.get(n1, 0.0) + ev0.elapsed_time(ev1)
+    stage_ms = {k: v / len(marks_list) for k, v in stage_ms.items()}
+    # end-to-end arm (host buffers, H2D + D2H inside the timed region)
+    for i in range(3):
+        step_e2e(i)
+    ms_e2e = timed(lambda i: step_e2e(i), args.steps)
+    # tracking iterations (single GPU by nature): reported as an extra
+    track_ips = None
+    if world == 1:
+        k = kfs[1]
+        ps = ss.PoseState(kfs[0]["q"], kfs[0]["t"], dev)
+        for i in range(3):
+            ss.track_step(ws, gmap, ps, k["rgb_d"], k["depth_d"])
+        ms_tr = timed(lambda i: ss.track_step(ws, gmap, ps, k["rgb_d"], k["depth_d"]), args.steps)
+        track_ips = args.steps / (ms_tr * 1e-3)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peak, peak_src = peaks()
+    ab = algorithmic_bytes(gmap.count, V, M, P, cam.n_tiles)
+    dom = max((s for s in stage_ms if s in ab), key=lambda s: stage_ms[s])
+    achieved = ab[dom] / (stage_ms[dom] * 1e-3) / 1e9
+    raster_ms = sum(stage_ms.get(s, 0.0) for s in ("preprocess_fwd", "tile_bin", "blend_fwd", "zero_v_rec",
+                                                   "blend_bwd", "preprocess_bwd"))
+    step_bytes = sum(ab.values())
+    out = {
+        "metric": METRIC, "value": args.steps * world / (ms_total * 1e-3), "unit": "iters/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{SHAPE}-shaped {W}x{H}, N={gmap.count} isotropic Gaussians, M={M} tile intersections, "
+                               f"{WINDOW}-keyframe window, one keyframe per rank per iteration",
+                   "loss": "masked L1 colour+depth (SSIM/flat/iso: SURVEY 8(f) next)",
+                   "l2": "working set per step ~%.0f MB > 126 MB L2; keyframes rotate every step" % (step_bytes / 1e6 + 300),
+                   "parallelism": f"keyframe-dp{world}" if world > 1 else "single"},
+        "raster_fwd_bwd_ms": raster_ms, "tracking_iters_per_s": track_ips,
+        "stage_ms": {k: round(v, 4) for k, v in stage_ms.items()},
+        "step_hbm_frac": step_bytes / (ms_total / args.steps * 1e-3) / 1e9 / peak,
+        "e2e": {"value": args.steps * world / (ms_e2e * 1e-3), "unit": "iters/s",
+                "h2d_bytes_per_step": 4 * P * 4, "d2h_bytes_per_step": 16},
+        "gpu_launches": 17 * args.steps,
+        "roofline": {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "note": "blend kernels are smem-broadcast / L2-atomic bound, not HBM bound (SURVEY 8(d)); "
+                             "achieved = algorithmic bytes / CUDA-event time of the stage inside the timed region"},
+        "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu:
+        out["cpu_baseline"] = cpu_baseline(syn, params, kfs, sample_steps=1)
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def oracle_map_iteration(orc, ocam, state, kf):
+    """One mapping iteration of the CPU oracle (checker used as the timed CPU baseline)."""
+    flags = orc.F_LOG_SCALES | orc.F_LOGIT_OPAC
+    pose = orc.make_pose(kf["q"], kf["t"])
+    p = state["p"]
+    lo = p["logit_opacities"].reshape(-1)
+    o = orc.render_full(ocam, p["means3D"], p["log_scales"], None, lo, p["rgb_colors"], ch=5, flags=flags, pose=pose)
+    v_render, losses = orc.loss_l1(ocam, 1, o["render"], o["alpha"], kf["rgb"], kf["depth"])
+    v_rec = orc.blend_bwd(ocam, 5, o["rec"], o["vals"], o["ranges"], o["alpha"], o["last"], v_render)
+    g = orc.preprocess_bwd(ocam, p["means3D"], p["log_scales"], None, lo, p["rgb_colors"], o["radii"], o["rec"],
+                           v_rec, ch=5, flags=flags, pose=pose)
+    state["step"] += 1
+    lrs = dict(means3D=1e-4, rgb_colors=2.5e-3, logit_opacities=0.05, log_scales=1e-3)
+    for k, gk in (("means3D", g["means"]), ("rgb_colors", g["colors"]), ("logit_opacities", g["opacities"]),
+                  ("log_scales", g["scales"])):
+        orc.adam(p[k].reshape(-1), gk.reshape(-1), state["m"][k].reshape(-1), state["v"][k].reshape(-1), lrs[k],
+                 eps=1e-15, step=state["step"])
+    return float(losses[0])
+
+
+def oracle_state(params):
+    p = {k: np.ascontiguousarray(v).copy() for k, v in params.items()}
+    return dict(p=p, m={k: np.zeros_like(v) for k, v in p.items()}, v={k: np.zeros_like(v) for k, v in p.items()},
+                step=0)
+
+
+def cpu_baseline(syn, params, kfs, sample_steps=1):
+    from oracle import oracle as orc
+    W, H, fx, fy, cx, cy = syn.SHAPES[SHAPE][:6]
+    ocam = orc.make_camera(W, H, fx, fy, cx, cy)
+    state = oracle_state(params)
+    t0 = time.perf_counter()
+    for i in range(sample_steps):
+        oracle_map_iteration(orc, ocam, state, kfs[i % len(kfs)])
+    dt = time.perf_counter() - t0
+    return {"value": sample_steps / dt, "unit": "iters/s", "cores": orc.lib().orc_num_threads(), "kind": "port",
+            "sample": f"{sample_steps} full-size mapping iteration(s) of the same workload on the CPU oracle "
+                      f"(C++/OpenMP, {dt:.1f} s)"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path for the hot path, timed on the host cores.  The
+    reference's own rasterizer is CUDA-only and its Python rasterizer module is not vendored,
+    so this is the oracle port (kind "port"), all host threads, same config/metric/unit."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    from oracle import oracle as orc
+    orc.build()
+    syn, params, kfs = build_workload(SHAPE, N_GAUSS, WINDOW)
+    W, H, fx, fy, cx, cy = syn.SHAPES[SHAPE][:6]
+    ocam = orc.make_camera(W, H, fx, fy, cx, cy)
+    state = oracle_state(params)
+    steps = max(1, min(args.steps, 3))
+    warm = 1 if args.warmup > 0 else 0
+    for i in range(warm):
+        oracle_map_iteration(orc, ocam, state, kfs[i % len(kfs)])
+    t0 = time.perf_counter()
+    for i in range(steps):
+        oracle_map_iteration(orc, ocam, state, kfs[(i + warm) % len(kfs)])
+    dt = time.perf_counter() - t0
+    val = steps / dt
+    cores = orc.lib().orc_num_threads()
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "iters/s", "n_gpus": world, "steps": steps,
+        "warmup": warm, "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{SHAPE}-shaped {W}x{H}, N={params['means3D'].shape[0]} isotropic Gaussians, "
+                               f"{WINDOW}-keyframe window (bounded: {steps} timed iterations)",
+                   "loss": "masked L1 colour+depth"},
+        "cpu_baseline": {"value": val, "unit": "iters/s", "cores": cores, "kind": "port",
+                         "sample": f"{steps} full-size mapping iterations, {dt:.1f} s"},
+        "e2e": {"value": val, "unit": "iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

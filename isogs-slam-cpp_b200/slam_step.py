@@ -1,0 +1,235 @@
+"""The tracking / mapping step around the rasterizer (north_star (4)-(5)), as fused device ops:
+
+  map_step   = transform_to_frame + activations + render(rgb, depth, depth^2, silhouette) + masked-L1
+               loss + backward + (optional gradient all-reduce) + fused Adam on all Gaussian params
+  track_step = same forward with the frame pose on the device, sum-L1 loss with the silhouette
+               mask, backward chained to the 7-dof pose, fused Adam on the pose only
+
+Mirrors get_loss + loss.backward() + optimizer.step() of python_ordinary/scripts/splatam.py:494-760,
+1247-1317 (tracking), 1412-1476 (mapping) with SSIM / flat / iso terms left out.
+Parameters live in a capacity-doubling SoA pool (cpp/include/core/gaussian_model.hpp:18-124
+without the unused 48-slot SH block).  torch is used for memory, streams and NCCL only.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib, raster
+from ._lib import REC, check, lib
+from .raster import _ptr, _stream
+
+PARAM_ORDER = ("means3D", "rgb_colors", "unnorm_rotations", "logit_opacities", "log_scales")
+
+# reference learning rates (python_ordinary/configs/replica/splatam.py:88-96,109-117)
+MAPPING_LRS = dict(means3D=1e-4, rgb_colors=2.5e-3, unnorm_rotations=1e-3, logit_opacities=0.05, log_scales=1e-3)
+TRACKING_LRS = dict(cam_unnorm_rots=4e-4, cam_trans=2e-3)
+
+
+class GaussianMap:
+    """Replicated Gaussian map: parameters, Adam moments and one flat gradient buffer."""
+
+    def __init__(self, params, capacity=None, device="cuda"):
+        n = params["means3D"].shape[0]
+        self.isotropic = params["log_scales"].shape[1] == 1
+        self.sd = 1 if self.isotropic else 3
+        self.widths = dict(means3D=3, rgb_colors=3, unnorm_rotations=4, logit_opacities=1, log_scales=self.sd)
+        self.capacity = int(capacity or n)
+        self.count = n
+        self.device = torch.device(device)
+        self.p, self.m, self.v = {}, {}, {}
+        for k in PARAM_ORDER:
+            w = self.widths[k]
+            buf = torch.zeros((self.capacity, w), dtype=torch.float32, device=self.device)
+            src = params[k]
+            src = torch.from_numpy(src) if not torch.is_tensor(src) else src
+            buf[:n] = src.reshape(n, w).to(self.device)
+            self.p[k] = buf
+            self.m[k] = torch.zeros_like(buf)
+            self.v[k] = torch.zeros_like(buf)
+        # one contiguous gradient buffer so a single all-reduce covers every parameter group
+        self.grad_names = [k for k in PARAM_ORDER if not (self.isotropic and k == "unnorm_rotations")]
+        total = sum(self.widths[k] for k in self.grad_names) * self.capacity
+        self.grad_flat = torch.zeros((total,), dtype=torch.float32, device=self.device)
+        self._carve()
+        self.step_count = 0
+
+    def _carve(self):
+        self.g, off = {}, 0
+        for k in self.grad_names:
+            sz = self.widths[k] * self.count
+            self.g[k] = self.grad_flat[off:off + sz].view(self.count, self.widths[k])
+            off += sz
+        self.grad_used = off
+
+    def view(self, k):
+        return self.p[k][:self.count]
+
+    def reset_optimizer(self):
+        """The reference re-creates Adam for every tracking frame / mapping call (splatam.py:1237,1406)."""
+        for k in PARAM_ORDER:
+            self.m[k].zero_()
+            self.v[k].zero_()
+        self.step_count = 0
+
+    def set_count(self, n):
+        self.count = int(n)
+        self._carve()
+
+
+class StepWorkspace:
+    """Per-(resolution, N) scratch that is reused across iterations (no per-step allocation)."""
+
+    def __init__(self, cam, n_cap, device):
+        self.cam = cam
+        self.device = device
+        H, W = cam.height, cam.width
+        f32, i32 = torch.float32, torch.int32
+        self.rec = torch.empty((n_cap, REC), dtype=f32, device=device)
+        self.v_rec = torch.empty((n_cap, REC), dtype=f32, device=device)
+        self.radii = torch.empty((n_cap, 2), dtype=i32, device=device)
+        self.tiles = torch.empty((n_cap,), dtype=i32, device=device)
+        self.cum = torch.empty((n_cap,), dtype=i32, device=device)
+        self.n_cap = n_cap
+        self.scan_b, _ = _lib.temp_bytes(n_cap, 0)
+        self.scan_tmp = torch.empty((self.scan_b,), dtype=torch.uint8, device=device)
+        self.ranges = torch.empty((cam.n_tiles + 1,), dtype=i32, device=device)
+        self.render = torch.empty((5, H, W), dtype=f32, device=device)
+        self.v_render = torch.empty((5, H, W), dtype=f32, device=device)
+        self.alpha = torch.empty((H, W), dtype=f32, device=device)
+        self.last = torch.empty((H, W), dtype=i32, device=device)
+        self.small = torch.zeros((32,), dtype=f32, device=device)  # losses[4] | v_pose[7] | pose_acc[16]
+        self.losses, self.v_pose, self.pose_acc = self.small[0:4], self.small[4:11], self.small[11:27]
+        self.isect_cap = 0
+        self._grow_isects(max(1024, 3 * n_cap))
+        self.M = 0
+
+    def _grow_isects(self, cap):
+        dev = self.device
+        self.isect_cap = int(cap)
+        self.ku = torch.empty((cap,), dtype=torch.int64, device=dev)
+        self.ks = torch.empty((cap,), dtype=torch.int64, device=dev)
+        self.vu = torch.empty((cap,), dtype=torch.int32, device=dev)
+        self.vs = torch.empty((cap,), dtype=torch.int32, device=dev)
+        _, self.sort_b = _lib.temp_bytes(0, cap)
+        self.sort_tmp = torch.empty((self.sort_b,), dtype=torch.uint8, device=dev)
+
+
+def render_forward(ws, gmap, pose=None, pose_dev=None, ch=5, marks=None):
+    """preprocess (raw params, fused activations + frame transform) -> bin -> blend.  One host sync (M)."""
+    cam, N = ws.cam, gmap.count
+    flags = _lib.F_LOG_SCALES | _lib.F_LOGIT_OPAC
+    L, st = lib(), _stream()
+    m = C.c_int64(0)
+    quats = None if gmap.isotropic else gmap.p["unnorm_rotations"]
+    check(L.isogs_preprocess_fwd(C.byref(cam), C.byref(pose) if pose is not None else None, _ptr(pose_dev), N,
+                                 _ptr(gmap.p["means3D"]), _ptr(gmap.p["log_scales"]), gmap.sd, _ptr(quats),
+                                 _ptr(gmap.p["logit_opacities"]), _ptr(gmap.p["rgb_colors"]), ch, flags,
+                                 _ptr(ws.rec), _ptr(ws.radii), _ptr(ws.tiles), _ptr(ws.cum), _ptr(ws.scan_tmp),
+                                 ws.scan_b, C.byref(m), st))
+    M = int(m.value)
+    _mark(marks, "preprocess_fwd")
+    if M > ws.isect_cap:
+        ws._grow_isects(int(M * 1.25) + 1024)
+    ws.M = M
+    check(L.isogs_tile_bin(C.byref(cam), N, M, _ptr(ws.rec), _ptr(ws.radii), _ptr(ws.cum), _ptr(ws.ku), _ptr(ws.vu),
+                           _ptr(ws.ks), _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.sort_tmp), ws.sort_b, st))
+    _mark(marks, "tile_bin")
+    check(L.isogs_blend_fwd(C.byref(cam), ch, _ptr(ws.rec), _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.render),
+                            _ptr(ws.alpha), _ptr(ws.last), st))
+    return M
+
+
+def render_backward(ws, gmap, pose=None, pose_dev=None, ch=5, want_gaussians=True, want_pose=False, marks=None):
+    cam, N = ws.cam, gmap.count
+    flags = _lib.F_LOG_SCALES | _lib.F_LOGIT_OPAC
+    L, st = lib(), _stream()
+    ws.v_rec[:N].zero_()
+    _mark(marks, "zero_v_rec")
+    if ws.M > 0:
+        check(L.isogs_blend_bwd(C.byref(cam), ch, N, _ptr(ws.rec), _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.alpha),
+                                _ptr(ws.last), _ptr(ws.v_render), None, _ptr(ws.v_rec), st))
+    _mark(marks, "blend_bwd")
+    quats = None if gmap.isotropic else gmap.p["unnorm_rotations"]
+    g = gmap.g if want_gaussians else {}
+    check(L.isogs_preprocess_bwd(C.byref(cam), C.byref(pose) if pose is not None else None, _ptr(pose_dev), N,
+                                 _ptr(gmap.p["means3D"]), _ptr(gmap.p["log_scales"]), gmap.sd, _ptr(quats),
+                                 _ptr(gmap.p["logit_opacities"]), ch, flags, _ptr(ws.radii), _ptr(ws.v_rec),
+                                 _ptr(g.get("means3D")), _ptr(g.get("log_scales")), _ptr(g.get("unnorm_rotations")),
+                                 _ptr(g.get("logit_opacities")), _ptr(g.get("rgb_colors")), None,
+                                 _ptr(ws.v_pose) if want_pose else None, _ptr(ws.pose_acc) if want_pose else None, st))
+    _mark(marks, "preprocess_bwd")
+
+
+def loss_l1(ws, mode, gt_rgb, gt_depth, inv_n_depth=1.0, w_im=0.5, w_depth=1.0, sil_thres=0.99, use_sil=True):
+    check(lib().isogs_loss_l1_fused(C.byref(ws.cam), mode, _ptr(ws.render), _ptr(ws.alpha), _ptr(gt_rgb),
+                                    _ptr(gt_depth), w_im, w_depth, sil_thres, int(use_sil), inv_n_depth,
+                                    _ptr(ws.v_render), _ptr(ws.losses), _stream()))
+
+
+def adam_gaussians(gmap, lrs=MAPPING_LRS, eps=1e-15, beta1=0.9, beta2=0.999):
+    gmap.step_count += 1
+    names = gmap.grad_names
+    arr = (_lib.AdamGroup * len(names))()
+    for i, k in enumerate(names):
+        arr[i].param = gmap.p[k].data_ptr()
+        arr[i].grad = gmap.g[k].data_ptr()
+        arr[i].exp_avg = gmap.m[k].data_ptr()
+        arr[i].exp_avg_sq = gmap.v[k].data_ptr()
+        arr[i].numel = gmap.count * gmap.widths[k]
+        arr[i].lr = lrs[k]
+    check(lib().isogs_adam_fused(arr, len(names), beta1, beta2, eps, gmap.step_count, _stream()))
+
+
+def _mark(marks, name):
+    if marks is not None:
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        marks.append((name, ev))
+
+
+def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, allreduce=None, marks=None):
+    """One mapping iteration on one keyframe (splatam.py:1412-1476, L1 terms).  `pose` is the keyframe's
+    HOST pose (camera_grad=False).  `allreduce(flat_grad_tensor)` is called between backward and Adam.
+    `marks` (a list) receives (stage, cuda event) pairs for per-stage timing."""
+    _mark(marks, "begin")
+    ws.small.zero_()
+    render_forward(ws, gmap, pose=pose, marks=marks)
+    _mark(marks, "blend_fwd")
+    loss_l1(ws, 1, gt_rgb, gt_depth, inv_n_depth)
+    _mark(marks, "loss")
+    render_backward(ws, gmap, pose=pose, want_gaussians=True, marks=marks)
+    if allreduce is not None:
+        allreduce(gmap.grad_flat[:gmap.grad_used])
+        _mark(marks, "allreduce")
+    adam_gaussians(gmap, lrs)
+    _mark(marks, "adam")
+    return ws.losses
+
+
+class PoseState:
+    """cam_unnorm_rots / cam_trans of the frame being tracked, on the device, with Adam moments."""
+
+    def __init__(self, q, t, device="cuda"):
+        self.pose = torch.tensor(list(q) + list(t), dtype=torch.float32, device=device)
+        self.m = torch.zeros_like(self.pose)
+        self.v = torch.zeros_like(self.pose)
+        self.step_count = 0
+
+
+def track_step(ws, gmap, ps, gt_rgb, gt_depth, lrs=TRACKING_LRS, eps=1e-8, use_sil=True, sil_thres=0.99):
+    """One tracking iteration (splatam.py:1247-1290): only the pose gets a gradient and a step."""
+    ws.small.zero_()
+    render_forward(ws, gmap, pose_dev=ps.pose)
+    loss_l1(ws, 0, gt_rgb, gt_depth, 1.0, sil_thres=sil_thres, use_sil=use_sil)
+    render_backward(ws, gmap, pose_dev=ps.pose, want_gaussians=False, want_pose=True)
+    ps.step_count += 1
+    arr = (_lib.AdamGroup * 2)()
+    for i, (off, n, lr) in enumerate(((0, 4, lrs["cam_unnorm_rots"]), (4, 3, lrs["cam_trans"]))):
+        arr[i].param = ps.pose.data_ptr() + 4 * off
+        arr[i].grad = ws.v_pose.data_ptr() + 4 * off
+        arr[i].exp_avg = ps.m.data_ptr() + 4 * off
+        arr[i].exp_avg_sq = ps.v.data_ptr() + 4 * off
+        arr[i].numel = n
+        arr[i].lr = lr
+    check(lib().isogs_adam_fused(arr, 2, 0.9, 0.999, eps, ps.step_count, _stream()))
+    return ws.losses
