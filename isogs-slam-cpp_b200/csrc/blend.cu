@@ -26,18 +26,64 @@ __device__ __forceinline__ float sigma_of(const float4& g0, const float4& g1, fl
     return fmaf(u, dx, (g1.x * dy) * dy);
 }
 
+
+// Each warp owns an 8x4 pixel block of the tile (8 blocks).  While a batch of 256 Gaussians is
+// staged, every thread tests ITS Gaussian's sigma<=L bounding box against the 8 blocks and the
+// warp ballots are published as bit masks; a warp then visits only the Gaussians that can touch
+// its block (about 1/3 of the tile list for ~9x9 px footprints), in sorted order.
+constexpr int NWARP = BLOCK / 32;
+constexpr int RW = 8, RH = 4; // pixel block per warp
+
+struct PixelMap {
+    int px_i, py_i;
+};
+__device__ __forceinline__ PixelMap pixel_of(int tid) {
+    const int wid = tid >> 5, lane = tid & 31;
+    PixelMap p;
+    p.px_i = blockIdx.x * TILE + (wid & 1) * RW + (lane & (RW - 1));
+    p.py_i = blockIdx.y * TILE + (wid >> 1) * RH + (lane >> 3);
+    return p;
+}
+
+// conservative half extents of {sigma <= L}: sqrt(2 L cov_xx), sqrt(2 L cov_yy), padded for rounding
+__device__ __forceinline__ void footprint(const float4& g0, const float4& g1, float& hx, float& hy) {
+    const float a = 2.0f * g0.z, b = g0.w, c = 2.0f * g1.x;
+    const float inv_det = __fdividef(1.0f, fmaf(a, c, -(b * b)));
+    const float twoL = 2.0f * g1.y;
+    hx = fmaf(sqrtf(twoL * c * inv_det), 1.001f, 0.01f);
+    hy = fmaf(sqrtf(twoL * a * inv_det), 1.001f, 0.01f);
+}
+
+// publish, for the Gaussian this thread staged, which of the 8 warp blocks it can touch
+__device__ __forceinline__ void publish_masks(bool have, const float4& g0, const float4& g1,
+                                              uint32_t (*s_mask)[NWARP], int wid, int lane) {
+    float hx = 0.f, hy = 0.f;
+    if (have) footprint(g0, g1, hx, hy);
+    const float x0 = (float)(blockIdx.x * TILE), y0 = (float)(blockIdx.y * TILE);
+    const float lo_x = g0.x - hx - x0, hi_x = g0.x + hx - x0; // tile-local
+    const float lo_y = g0.y - hy - y0, hi_y = g0.y + hy - y0;
+#pragma unroll
+    for (int r = 0; r < NWARP; ++r) {
+        const float rx0 = (float)((r & 1) * RW) + 0.5f, ry0 = (float)((r >> 1) * RH) + 0.5f;
+        const bool hit = have && hi_x >= rx0 && lo_x <= rx0 + (float)(RW - 1) && hi_y >= ry0 &&
+                         lo_y <= ry0 + (float)(RH - 1);
+        const uint32_t m = __ballot_sync(0xffffffffu, hit);
+        if (lane == r) s_mask[r][wid] = m;
+    }
+}
+
 template <int CH>
 __global__ void __launch_bounds__(BLOCK)
 blend_fwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
                  const int32_t* __restrict__ ranges, float* __restrict__ render, float* __restrict__ alpha,
                  int32_t* __restrict__ last) {
     __shared__ Batch sb;
-    const int tid = threadIdx.x;
+    __shared__ uint32_t s_mask[NWARP][NWARP]; // [pixel block][staging warp]
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int tile = blockIdx.y * cam.tw + blockIdx.x;
-    const int px_i = blockIdx.x * TILE + (tid & (TILE - 1));
-    const int py_i = blockIdx.y * TILE + (tid >> 4);
-    const bool inside = px_i < cam.width && py_i < cam.height;
-    const float px = (float)px_i + 0.5f, py = (float)py_i + 0.5f;
+    const PixelMap pm = pixel_of(tid);
+    const bool inside = pm.px_i < cam.width && pm.py_i < cam.height;
+    const float px = (float)pm.px_i + 0.5f, py = (float)pm.py_i + 0.5f;
     const int start = ranges[tile], end = ranges[tile + 1];
 
     float T = 1.0f;
@@ -51,28 +97,36 @@ blend_fwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
         // barrier (protects the staging buffers) + early exit when the whole tile is saturated
         if (__syncthreads_count(done) == BLOCK) break;
         const int idx = b + tid;
-        if (idx < end) {
-            const int g = vals[idx];
-            const float4* r = rec + 3 * (int64_t)g;
-            sb.g0[tid] = __ldg(r);
-            sb.g1[tid] = __ldg(r + 1);
+        const bool have = idx < end;
+        float4 g0 = make_float4(0.f, 0.f, 0.f, 0.f), g1 = g0;
+        if (have) {
+            const float4* r = rec + 3 * (int64_t)vals[idx];
+            g0 = __ldg(r);
+            g1 = __ldg(r + 1);
+            sb.g0[tid] = g0;
+            sb.g1[tid] = g1;
             sb.g2[tid] = __ldg(r + 2);
         }
+        publish_masks(have, g0, g1, s_mask, wid, lane);
         __syncthreads();
-        const int n = min(BLOCK, end - b);
-        if (!done) {
-            for (int t = 0; t < n; ++t) {
-                const float4 g0 = sb.g0[t];
-                const float4 g1 = sb.g1[t];
+        if (__all_sync(0xffffffffu, done)) continue;
+#pragma unroll 1
+        for (int j = 0; j < NWARP; ++j) {
+            uint32_t bits = s_mask[wid][j];
+            while (bits) {
+                const int t = j * 32 + __ffs(bits) - 1;
+                bits &= bits - 1;
+                const float4 g0s = sb.g0[t];
+                const float4 g1s = sb.g1[t];
                 float dx, dy;
-                const float sigma = sigma_of(g0, g1, px, py, dx, dy);
-                if (sigma < 0.f || sigma > g1.y) continue;
-                const float a = fminf(MAX_ALPHA, g1.z * __expf(-sigma));
+                const float sigma = sigma_of(g0s, g1s, px, py, dx, dy);
+                if (done || sigma < 0.f || sigma > g1s.y) continue;
+                const float a = fminf(MAX_ALPHA, g1s.z * __expf(-sigma));
                 const float nT = T * (1.0f - a);
-                if (nT <= T_CUTOFF) { done = true; break; }
+                if (nT <= T_CUTOFF) { done = true; continue; }
                 const float vis = a * T;
                 const float4 g2 = sb.g2[t];
-                acc[0] = fmaf(g1.w, vis, acc[0]);
+                acc[0] = fmaf(g1s.w, vis, acc[0]);
                 acc[1] = fmaf(g2.x, vis, acc[1]);
                 acc[2] = fmaf(g2.y, vis, acc[2]);
                 acc[3] = fmaf(g2.z, vis, acc[3]);
@@ -80,11 +134,12 @@ blend_fwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
                 last_idx = b + t;
                 T = nT;
             }
+            if (__all_sync(0xffffffffu, done)) break;
         }
     }
     if (inside) {
         const int64_t P = (int64_t)cam.width * cam.height;
-        const int64_t pix = (int64_t)py_i * cam.width + px_i;
+        const int64_t pix = (int64_t)pm.py_i * cam.width + pm.px_i;
 #pragma unroll
         for (int k = 0; k < CH; ++k) render[k * P + pix] = (k < 3) ? fmaf(T, cam.bg[k], acc[k]) : acc[k];
         alpha[pix] = 1.0f - T;
@@ -141,16 +196,16 @@ blend_bwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
                  const float* __restrict__ v_alpha, float* __restrict__ v_rec) {
     __shared__ Batch sb;
     __shared__ int s_ids[BLOCK];
-    __shared__ int s_warp_last[BLOCK / 32];
+    __shared__ uint32_t s_mask[NWARP][NWARP];
+    __shared__ int s_warp_last[NWARP];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int tile = blockIdx.y * cam.tw + blockIdx.x;
-    const int px_i = blockIdx.x * TILE + (tid & (TILE - 1));
-    const int py_i = blockIdx.y * TILE + (tid >> 4);
-    const bool inside = px_i < cam.width && py_i < cam.height;
-    const float px = (float)px_i + 0.5f, py = (float)py_i + 0.5f;
+    const PixelMap pm = pixel_of(tid);
+    const bool inside = pm.px_i < cam.width && pm.py_i < cam.height;
+    const float px = (float)pm.px_i + 0.5f, py = (float)pm.py_i + 0.5f;
     const int start = ranges[tile];
     const int64_t P = (int64_t)cam.width * cam.height;
-    const int64_t pix = inside ? (int64_t)py_i * cam.width + px_i : 0;
+    const int64_t pix = inside ? (int64_t)pm.py_i * cam.width + pm.px_i : 0;
 
     const int my_last = inside ? last[pix] : start - 1;
     const float T_final = inside ? 1.0f - alpha[pix] : 1.0f;
@@ -172,67 +227,81 @@ blend_bwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
     __syncthreads();
     int block_last = s_warp_last[0];
 #pragma unroll
-    for (int w = 1; w < BLOCK / 32; ++w) block_last = max(block_last, s_warp_last[w]);
+    for (int w = 1; w < NWARP; ++w) block_last = max(block_last, s_warp_last[w]);
     if (block_last < start) return;
 
     // which component this lane owns after warp_reduce16
     const int comp = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
     const bool writer = ((lane & 1) == 0) && comp < 6 + CH;
 
+    // batches run back to front; inside a batch slot t holds sorted index batch_end - t
     for (int batch_end = block_last; batch_end >= start; batch_end -= BLOCK) {
         __syncthreads();
         const int idx = batch_end - tid;
-        if (idx >= start) {
+        const bool have = idx >= start;
+        float4 g0 = make_float4(0.f, 0.f, 0.f, 0.f), g1 = g0;
+        if (have) {
             const int g = vals[idx];
             s_ids[tid] = g;
             const float4* r = rec + 3 * (int64_t)g;
-            sb.g0[tid] = __ldg(r);
-            sb.g1[tid] = __ldg(r + 1);
+            g0 = __ldg(r);
+            g1 = __ldg(r + 1);
+            sb.g0[tid] = g0;
+            sb.g1[tid] = g1;
             sb.g2[tid] = __ldg(r + 2);
         }
+        publish_masks(have, g0, g1, s_mask, wid, lane);
         __syncthreads();
-        const int n = min(BLOCK, batch_end - start + 1);
-        for (int t = max(0, batch_end - warp_last); t < n; ++t) {
-            const float4 g0 = sb.g0[t];
-            const float4 g1 = sb.g1[t];
-            float dx, dy;
-            const float sigma = sigma_of(g0, g1, px, py, dx, dy);
-            const bool valid = (batch_end - t <= my_last) && !(sigma < 0.f || sigma > g1.y);
-            if (!__any_sync(0xffffffffu, valid)) continue;
-            float v[16];
+        const int t_first = batch_end - warp_last; // slots below this are behind every pixel's last id
+        if (t_first >= BLOCK) continue;
+#pragma unroll 1
+        for (int j = max(0, t_first) >> 5; j < NWARP; ++j) {
+            uint32_t bits = s_mask[wid][j];
+            if (j * 32 < t_first) bits &= ~((1u << (t_first - j * 32)) - 1u);
+            while (bits) {
+                const int t = j * 32 + __ffs(bits) - 1;
+                bits &= bits - 1;
+                const float4 g0s = sb.g0[t];
+                const float4 g1s = sb.g1[t];
+                float dx, dy;
+                const float sigma = sigma_of(g0s, g1s, px, py, dx, dy);
+                const bool valid = (batch_end - t <= my_last) && !(sigma < 0.f || sigma > g1s.y);
+                if (!__any_sync(0xffffffffu, valid)) continue;
+                float v[16];
 #pragma unroll
-            for (int k = 0; k < 16; ++k) v[k] = 0.f;
-            if (valid) {
-                const float4 g2 = sb.g2[t];
-                const float c[5] = {g1.w, g2.x, g2.y, g2.z, g2.w};
-                const float opac = g1.z;
-                const float vis = __expf(-sigma);
-                const float ov = opac * vis;
-                const float a = fminf(MAX_ALPHA, ov);
-                const float ra = __fdividef(1.0f, 1.0f - a);
-                T *= ra;
-                const float fac = a * T;
-                float v_a = 0.f;
+                for (int k = 0; k < 16; ++k) v[k] = 0.f;
+                if (valid) {
+                    const float4 g2 = sb.g2[t];
+                    const float c[5] = {g1s.w, g2.x, g2.y, g2.z, g2.w};
+                    const float opac = g1s.z;
+                    const float vis = __expf(-sigma);
+                    const float ov = opac * vis;
+                    const float a = fminf(MAX_ALPHA, ov);
+                    const float ra = __fdividef(1.0f, 1.0f - a);
+                    T *= ra;
+                    const float fac = a * T;
+                    float v_a = 0.f;
 #pragma unroll
-                for (int k = 0; k < CH; ++k) {
-                    v[6 + k] = fac * vr[k];
-                    v_a = fmaf(fmaf(c[k], T, -(buffer[k] * ra)), vr[k], v_a);
-                    buffer[k] = fmaf(c[k], fac, buffer[k]);
+                    for (int k = 0; k < CH; ++k) {
+                        v[6 + k] = fac * vr[k];
+                        v_a = fmaf(fmaf(c[k], T, -(buffer[k] * ra)), vr[k], v_a);
+                        buffer[k] = fmaf(c[k], fac, buffer[k]);
+                    }
+                    v_a = fmaf(va_eff, ra, v_a);
+                    if (ov <= MAX_ALPHA) {
+                        const float v_sigma = -ov * v_a;
+                        const float ca = 2.0f * g0s.z, cb = g0s.w, cc = 2.0f * g1s.x;
+                        v[0] = v_sigma * fmaf(ca, dx, cb * dy);
+                        v[1] = v_sigma * fmaf(cb, dx, cc * dy);
+                        v[2] = 0.5f * v_sigma * dx * dx;
+                        v[3] = v_sigma * dx * dy;
+                        v[4] = 0.5f * v_sigma * dy * dy;
+                        v[5] = vis * v_a;
+                    }
                 }
-                v_a = fmaf(va_eff, ra, v_a);
-                if (ov <= MAX_ALPHA) {
-                    const float v_sigma = -ov * v_a;
-                    const float ca = 2.0f * g0.z, cb = g0.w, cc = 2.0f * g1.x;
-                    v[0] = v_sigma * fmaf(ca, dx, cb * dy);
-                    v[1] = v_sigma * fmaf(cb, dx, cc * dy);
-                    v[2] = 0.5f * v_sigma * dx * dx;
-                    v[3] = v_sigma * dx * dy;
-                    v[4] = 0.5f * v_sigma * dy * dy;
-                    v[5] = vis * v_a;
-                }
+                warp_reduce16(v, lane);
+                if (writer) atomicAdd(v_rec + (int64_t)s_ids[t] * REC + comp, v[0]);
             }
-            warp_reduce16(v, lane);
-            if (writer) atomicAdd(v_rec + (int64_t)s_ids[t] * REC + comp, v[0]);
         }
     }
 }
