@@ -122,6 +122,15 @@ def test_forward_many_per_tile(pkg, orc):
     assert_forward_parity(o, render, alpha, ctx)
 
 
+@pytest.mark.parametrize("n,lo", [(9000, 2048), (60000, 8192)])
+def test_binning_long_tiles(pkg, orc, n, lo):
+    """Tiles holding > 2048 (64 KB shared-memory sort) and > 8192 (in-place global sort) intersections."""
+    sc = random_scene(n, 48, 32, 50.0, True, seed=77, big=True)
+    _, _, o, render, alpha, ctx = run_both(pkg, orc, sc, 4)
+    assert np.diff(o["ranges"]).max() > lo
+    assert_forward_parity(o, render, alpha, ctx)
+
+
 @pytest.mark.parametrize("iso", [True, False])
 def test_backward_parity(pkg, orc, iso):
     sc = random_scene(5000, 176, 120, 160.0, iso, seed=31)
