@@ -4,13 +4,15 @@
 // RasterizeToPixels3DGSBwd.cu:15-278.
 //
 // Design: warp-autonomous, no CTA barrier.  A CTA is one tile, a warp owns an 8x4
-// pixel block of it and walks the tile's depth-sorted list on its own, 32*NB Gaussians per batch:
-// every lane stages NB Gaussians of the batch into the warp's private shared-memory slab and tests
-// their {sigma <= L} footprints against the warp's EIGHT 2x2 pixel quads; eight ballots per 32
-// Gaussians give every quad (4 lanes) its own hit mask (NB words).  The quads then consume their masks INDEPENDENTLY: in one warp
-// iteration each quad blends a different Gaussian (its next hit), so SplaTAM-sized splats (about
-// 7 px wide) keep ~70 % of the lanes on pixels they really touch instead of ~23 % with one
-// Gaussian per warp iteration.  Backward: the 11 partial gradients are summed over the 4 lanes of
+// pixel block of it and walks the tile's depth-sorted list on its own through a warp-private RING
+// of NW words x 32 Gaussians in shared memory: staging a word, lane L loads Gaussian L and tests
+// its {sigma <= L} footprint against the warp's EIGHT 2x2 pixel quads; eight ballots give every
+// quad (4 lanes) its own 32-bit hit mask.  The quads then consume the ring INDEPENDENTLY, each
+// with its own cursor: in one warp iteration every quad blends a different Gaussian (its next
+// hit).  A depth-sorted list sweeps across the tile, so at any list position only a band of the
+// tile is hit; independent cursors let quads ahead of / behind the band keep working, and a word
+// is retired (and its slot refilled) once every quad has passed it.  Backward: the 11 partial
+// gradients are summed over the 4 lanes of
 // a quad with a transposed 9-shuffle reduction and every lane issues 3 RED.ADD.F32.
 //
 // This file is compiled with FMA contraction ON; the sigma expression uses explicit
@@ -35,13 +37,14 @@ __device__ unsigned long long g_stats[16];
 #define STAT(i, n) do { } while (0)
 #endif
 
-// Warp-private staging slab for one batch of 32*NB Gaussians (dynamic shared memory).
-template <int NB, bool WITH_ID>
-struct __align__(16) WarpStage {
-    float4 g0[32 * NB]; // x, y, 0.5*conic_a, conic_b
-    float4 g1[32 * NB]; // 0.5*conic_c, L (= sigma_max), opacity, c0
-    float4 g2[32 * NB]; // c1, c2, c3 (depth), c4 (depth^2)
-    int id[WITH_ID ? 32 * NB : 4];
+// Warp-private ring of NW words x 32 staged Gaussians (dynamic shared memory).
+template <int NW, bool WITH_ID>
+struct __align__(16) WarpRing {
+    float4 g0[32 * NW]; // x, y, 0.5*conic_a, conic_b
+    float4 g1[32 * NW]; // 0.5*conic_c, L (= sigma_max), opacity, c0
+    float4 g2[32 * NW]; // c1, c2, c3 (depth), c4 (depth^2)
+    uint32_t hits[NW][8]; // per word, per quad: which of the 32 Gaussians can touch the quad
+    int id[WITH_ID ? 32 * NW : 4];
 };
 
 __device__ __forceinline__ float sigma_of(const float4& g0, const float4& g1, float px, float py, float& dx,
@@ -100,29 +103,61 @@ __device__ __forceinline__ uint32_t quad_hits(bool have, const float4& g0, const
     return bits;
 }
 
-// Next hit of this lane's quad: advances (j, bits) over the NB mask words; returns the slot or -1.
-template <int NB>
-__device__ __forceinline__ int next_hit(const uint32_t (&w)[NB], int& j, uint32_t& bits) {
-    if (bits == 0u) {
-#pragma unroll
-        for (int k = 1; k < NB; ++k)
-            if (bits == 0u && j < k) { j = k; bits = w[k]; }
+// One list entry held in registers between its global load and its commit to the ring, so the
+// vals -> rec dependent load chain of word w+1 overlaps the blending of the words before it.
+struct Prefetch {
+    float4 g0, g1, g2;
+    int id;
+    bool have;
+};
+
+// Load list entry (32*word + lane), i.e. sorted index first + dir*(32*word + lane).
+__device__ __forceinline__ void prefetch_word(Prefetch& pf, int word, int first, int dir, int n_entries,
+                                              const float4* __restrict__ rec, const int32_t* __restrict__ vals,
+                                              int lane) {
+    const int e = 32 * word + lane;
+    pf.have = e < n_entries;
+    pf.g0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    pf.g1 = pf.g0;
+    pf.g2 = pf.g0;
+    pf.id = 0;
+    if (pf.have) {
+        pf.id = __ldg(vals + first + dir * e);
+        const float4* r = rec + 3 * (int64_t)pf.id;
+        pf.g0 = __ldg(r);
+        pf.g1 = __ldg(r + 1);
+        pf.g2 = __ldg(r + 2);
     }
-    if (bits == 0u) return -1;
-    const int t = j * 32 + __ffs(bits) - 1;
-    bits &= bits - 1u;
-    return t;
 }
 
-template <int CH, int NB>
+// Commit the prefetched word into ring slot word % NW and publish its per-quad hit masks.
+// Called by the whole warp at a convergent point; the caller guarantees the slot is retired.
+template <int NW, bool WITH_ID>
+__device__ __forceinline__ void commit_word(WarpRing<NW, WITH_ID>& st, const Prefetch& pf, int word, float bx0,
+                                            float by0, int lane) {
+    const unsigned wsl = ((unsigned)word & (NW - 1)) * 32u;
+    const unsigned slot = wsl + lane;
+    __syncwarp(); // every lane has finished reading the slot being overwritten
+    if (pf.have) {
+        st.g0[slot] = pf.g0;
+        st.g1[slot] = pf.g1;
+        st.g2[slot] = pf.g2;
+        if (WITH_ID) st.id[slot] = pf.id;
+    }
+    const uint32_t m = quad_hits(pf.have, pf.g0, pf.g1, bx0, by0, lane);
+    if ((lane & 3) == 0) st.hits[0][(wsl >> 2) + (lane >> 2)] = m;
+    __syncwarp();
+}
+
+template <int CH, int NW>
 __global__ void __launch_bounds__(BLOCK)
 blend_fwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
                  const int32_t* __restrict__ ranges, float* __restrict__ render, float* __restrict__ alpha,
                  int32_t* __restrict__ last) {
     extern __shared__ __align__(16) unsigned char s_raw[];
-    using Stage = WarpStage<NB, false>;
+    using Ring = WarpRing<NW, false>;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    Stage& st = reinterpret_cast<Stage*>(s_raw)[wid];
+    Ring& st = reinterpret_cast<Ring*>(s_raw)[wid];
     const int tile = blockIdx.y * cam.tw + blockIdx.x;
     const PixelMap pm = pixel_of(wid, lane);
     const bool inside = pm.px_i < cam.width && pm.py_i < cam.height;
@@ -130,8 +165,10 @@ blend_fwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
     const float bx0 = (float)(blockIdx.x * TILE + (wid & 1) * RW) + 0.5f;
     const float by0 = (float)(blockIdx.y * TILE + (wid >> 1) * RH) + 0.5f;
     const int start = ranges[tile], end = ranges[tile + 1];
-    const int qshift = lane & 28;
-    constexpr int B = 32 * NB;
+    const int n_entries = end - start;
+    const int n_words = (n_entries + 31) >> 5;
+    const int qshift = lane & 28, q = lane >> 2;
+    constexpr int FAR = 0x3fffffff;
 
     float T = 1.0f;
     float acc[CH];
@@ -140,43 +177,41 @@ blend_fwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
     int last_idx = start - 1;
     bool done = !inside;
 
-    for (int b = start; b < end; b += B) {
-        if (__all_sync(FULL, done)) break;
-        __syncwarp(); // the previous batch is fully consumed
-        uint32_t w[NB];
-#pragma unroll
-        for (int k = 0; k < NB; ++k) {
-            const int slot = k * 32 + lane;
-            const bool have = b + slot < end;
-            float4 g0 = make_float4(0.f, 0.f, 0.f, 0.f), g1 = g0;
-            if (have) {
-                const float4* r = rec + 3 * (int64_t)__ldg(vals + b + slot);
-                g0 = __ldg(r);
-                g1 = __ldg(r + 1);
-                st.g0[slot] = g0;
-                st.g1[slot] = g1;
-                st.g2[slot] = __ldg(r + 2);
-            }
-            w[k] = quad_hits(have, g0, g1, bx0, by0, lane);
+    if (n_words > 0 && !__all_sync(FULL, done)) {
+        int staged = 0, base = 0; // warp-uniform: words [base, staged) are live in the ring
+        Prefetch pf;
+        prefetch_word(pf, 0, start, 1, n_entries, rec, vals, lane);
+        for (; staged < min(NW, n_words); ++staged) {
+            commit_word<NW, false>(st, pf, staged, bx0, by0, lane);
+            prefetch_word(pf, staged + 1, start, 1, n_entries, rec, vals, lane);
         }
-        __syncwarp();
-        STAT(0, 1);
-        int j = 0;
-        uint32_t bits = w[0];
-        bool qdone = ((__ballot_sync(FULL, !done) >> qshift) & 15u) == 0u;
+        static_assert((NW & (NW - 1)) == 0, "NW must be a power of two");
+        const uint32_t* hq = &st.hits[0][q]; // this quad's hit word of ring word w is hq[8 * w]
+        int jq = 0;                          // this quad's cursor (absolute word), what is left of that word,
+        unsigned wsl = 0;                    // and the ring slot of its first entry: (jq % NW) * 32
+        uint32_t bits = hq[0];
+        if (((__ballot_sync(FULL, !done) >> qshift) & 15u) == 0u) { jq = FAR; bits = 0u; }
         while (true) {
-            const int t = qdone ? -1 : next_hit<NB>(w, j, bits);
-            if (!__any_sync(FULL, t >= 0)) break;
-            const int ts = max(t, 0);
-            const float4 g0s = st.g0[ts];
-            const float4 g1s = st.g1[ts];
+            if (bits == 0u && jq + 1 < staged) { // step to the next staged word (one per iteration)
+                ++jq;
+                wsl = (wsl + 32u) & (32u * NW - 1u);
+                bits = hq[wsl >> 2];
+            }
+            const bool act = bits != 0u;
+            // progress of this quad = first word it may still read
+            const int wmin = __reduce_min_sync(FULL, act ? jq : jq + 1);
+            if (wmin >= n_words) break; // every quad is past the end of the list (or saturated)
+            STAT(1, 1);
+            STAT(2, __popc(__ballot_sync(FULL, act)));
+            const int sl = act ? __ffs(bits) - 1 : 0;
+            bits &= bits - 1u;
+            const float4* gp = st.g0 + (wsl + sl);
+            const float4 g0s = gp[0];
+            const float4 g1s = gp[32 * NW];
             float dx, dy;
             const float sigma = sigma_of(g0s, g1s, px, py, dx, dy);
-            STAT(1, 1);
-            STAT(2, __popc(__ballot_sync(FULL, t >= 0)));
-            STAT(3, __popc(__ballot_sync(FULL, t >= 0 && !done && sigma >= 0.f && sigma <= g1s.y)));
             bool newly = false;
-            if (t >= 0 && !done && sigma >= 0.f && sigma <= g1s.y) {
+            if (act && !done && sigma >= 0.f && sigma <= g1s.y) {
                 const float a = fminf(MAX_ALPHA, g1s.z * __expf(-sigma));
                 const float nT = T * (1.0f - a);
                 if (nT <= T_CUTOFF) {
@@ -184,17 +219,28 @@ blend_fwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
                     newly = true;
                 } else {
                     const float vis = a * T;
-                    const float4 g2 = st.g2[ts];
+                    const float4 g2 = gp[64 * NW];
                     acc[0] = fmaf(g1s.w, vis, acc[0]);
                     acc[1] = fmaf(g2.x, vis, acc[1]);
                     acc[2] = fmaf(g2.y, vis, acc[2]);
                     acc[3] = fmaf(g2.z, vis, acc[3]);
                     if (CH == 5) acc[CH - 1] = fmaf(g2.w, vis, acc[CH - 1]);
-                    last_idx = b + ts;
+                    last_idx = start + 32 * jq + sl;
                     T = nT;
                 }
             }
-            if (__any_sync(FULL, newly)) qdone = ((__ballot_sync(FULL, !done) >> qshift) & 15u) == 0u;
+            if (__any_sync(FULL, newly)) {
+                if (((__ballot_sync(FULL, !done) >> qshift) & 15u) == 0u) { jq = FAR; bits = 0u; } // quad saturated
+            }
+            // retire the oldest word once every quad is past it; refill its slot with the next one
+            if (wmin > base) {
+                ++base;
+                if (staged < n_words) {
+                    commit_word<NW, false>(st, pf, staged, bx0, by0, lane);
+                    ++staged;
+                    prefetch_word(pf, staged, start, 1, n_entries, rec, vals, lane);
+                }
+            }
         }
     }
     if (inside) {
@@ -231,28 +277,16 @@ __device__ __forceinline__ void quad_reduce12(float (&v)[12], int lane) {
     }
 }
 
-__device__ __forceinline__ void red_v4(float* a, float x, float y, float z, float w) {
-    asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a), "f"(x), "f"(y), "f"(z), "f"(w)
-                 : "memory");
-}
-__device__ __forceinline__ void red_v2(float* a, float x, float y) {
-    asm volatile("red.relaxed.gpu.global.add.v2.f32 [%0], {%1, %2};" ::"l"(a), "f"(x), "f"(y) : "memory");
-}
-
-// RMODE: how the 11 partial gradients of a (quad, Gaussian) pair reach v_rec.
-//   0  quad reduce (9 shuffles) + 3 scalar RED per lane
-//   1  pair reduce (6 shuffles) + one v4 and one v2 RED per lane
-//   2  no reduce: three v4 RED per contributing lane
-template <int CH, int NB, int RMODE>
+template <int CH, int NW>
 __global__ void __launch_bounds__(BLOCK)
 blend_bwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
                  const int32_t* __restrict__ ranges, const float* __restrict__ alpha,
                  const int32_t* __restrict__ last, const float* __restrict__ v_render,
                  const float* __restrict__ v_alpha, float* __restrict__ v_rec) {
     extern __shared__ __align__(16) unsigned char s_raw[];
-    using Stage = WarpStage<NB, true>;
+    using Ring = WarpRing<NW, true>;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    Stage& st = reinterpret_cast<Stage*>(s_raw)[wid];
+    Ring& st = reinterpret_cast<Ring*>(s_raw)[wid];
     const int tile = blockIdx.y * cam.tw + blockIdx.x;
     const PixelMap pm = pixel_of(wid, lane);
     const bool inside = pm.px_i < cam.width && pm.py_i < cam.height;
@@ -262,14 +296,18 @@ blend_bwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
     const int start = ranges[tile];
     const int64_t P = (int64_t)cam.width * cam.height;
     const int64_t pix = inside ? (int64_t)pm.py_i * cam.width + pm.px_i : 0;
-    const int qshift = lane & 28;
-    constexpr int B = 32 * NB;
+    const int qshift = lane & 28, q = lane >> 2;
 
     const int my_last = inside ? last[pix] : start - 1;
     const int warp_last = __reduce_max_sync(FULL, my_last);
     if (warp_last < start) return; // nothing was blended into this warp's block
     int quad_last = max(my_last, __shfl_xor_sync(FULL, my_last, 1));
     quad_last = max(quad_last, __shfl_xor_sync(FULL, quad_last, 2));
+    // the list is walked back to front: entry e is sorted index warp_last - e
+    const int n_entries = warp_last - start + 1;
+    const int n_words = (n_entries + 31) >> 5;
+    const int e_first = warp_last - quad_last; // entries in front of it lie behind this quad's last contributor
+    const int my_first = warp_last - my_last;  // same, for this pixel
 
     const float T_final = inside ? 1.0f - alpha[pix] : 1.0f;
     float T = T_final;
@@ -289,53 +327,51 @@ blend_bwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
     const int comp0 = 6 * (lane & 1) + 3 * ((lane >> 1) & 1);
     const bool third = comp0 + 2 < 6 + CH;
 
-    // batches run back to front; inside a batch slot t holds sorted index batch_end - t
-    for (int batch_end = warp_last; batch_end >= start; batch_end -= B) {
-        __syncwarp(); // the previous batch is fully consumed
-        uint32_t w[NB];
-        // slots in front of t_first lie behind this quad's last contributor
-        const int t_first = batch_end - quad_last;
-#pragma unroll
-        for (int k = 0; k < NB; ++k) {
-            const int slot = k * 32 + lane;
-            const bool have = batch_end - slot >= start;
-            float4 g0 = make_float4(0.f, 0.f, 0.f, 0.f), g1 = g0;
-            if (have) {
-                const int g = __ldg(vals + batch_end - slot);
-                const float4* r = rec + 3 * (int64_t)g;
-                g0 = __ldg(r);
-                g1 = __ldg(r + 1);
-                st.g0[slot] = g0;
-                st.g1[slot] = g1;
-                st.g2[slot] = __ldg(r + 2);
-                st.id[slot] = g;
-            }
-            uint32_t m = quad_hits(have, g0, g1, bx0, by0, lane);
-            const int cut = t_first - 32 * k;
-            if (cut > 0) m = (cut >= 32) ? 0u : (m & ~((1u << cut) - 1u));
-            w[k] = m;
+    int staged = 0, base = 0; // warp-uniform: words [base, staged) are live in the ring
+    Prefetch pf;
+    prefetch_word(pf, 0, warp_last, -1, n_entries, rec, vals, lane);
+    for (; staged < min(NW, n_words); ++staged) {
+        commit_word<NW, true>(st, pf, staged, bx0, by0, lane);
+        prefetch_word(pf, staged + 1, warp_last, -1, n_entries, rec, vals, lane);
+    }
+    static_assert((NW & (NW - 1)) == 0, "NW must be a power of two");
+    const uint32_t* hq = &st.hits[0][q]; // this quad's hit word of ring word w is hq[8 * w]
+    // hit word of this quad with the entries in front of e_first masked off
+    auto fetch = [&](int w, unsigned wsl_) -> uint32_t {
+        const uint32_t m = hq[wsl_ >> 2];
+        const int cut = e_first - 32 * w;
+        return cut <= 0 ? m : (cut >= 32 ? 0u : (m & ~((1u << cut) - 1u)));
+    };
+    int jq = min(e_first >> 5, staged - 1);
+    unsigned wsl = ((unsigned)jq & (NW - 1)) * 32u;
+    uint32_t bits = fetch(jq, wsl);
+    if (quad_last < start) { jq = 0x3fffffff; bits = 0u; } // nothing was blended into this quad
+    while (true) {
+        if (bits == 0u && jq + 1 < staged) {
+            ++jq;
+            wsl = (wsl + 32u) & (32u * NW - 1u);
+            bits = fetch(jq, wsl);
         }
-        __syncwarp();
-        STAT(8, 1);
-        int j = 0;
-        uint32_t bits = w[0];
-        while (true) {
-            const int t = next_hit<NB>(w, j, bits);
-            if (!__any_sync(FULL, t >= 0)) break;
-            const int ts = max(t, 0);
-            const float4 g0s = st.g0[ts];
-            const float4 g1s = st.g1[ts];
-            float dx, dy;
-            const float sigma = sigma_of(g0s, g1s, px, py, dx, dy);
-            const bool valid = t >= 0 && (batch_end - ts <= my_last) && sigma >= 0.f && sigma <= g1s.y;
-            const uint32_t vb = __ballot_sync(FULL, valid);
-            STAT(9, 1);
-            STAT(10, __popc(__ballot_sync(FULL, t >= 0)));
-            STAT(11, __popc(vb));
-            if (vb == 0u) continue;
+        const bool act = bits != 0u;
+        const int wmin = __reduce_min_sync(FULL, act ? jq : jq + 1);
+        if (wmin >= n_words) break;
+        const int s = act ? __ffs(bits) - 1 : 0;
+        bits &= bits - 1u;
+        const unsigned slot = wsl + s;
+        const float4* gp = st.g0 + slot;
+        const float4 g0s = gp[0];
+        const float4 g1s = gp[32 * NW];
+        float dx, dy;
+        const float sigma = sigma_of(g0s, g1s, px, py, dx, dy);
+        const bool valid = act && (32 * jq + s >= my_first) && sigma >= 0.f && sigma <= g1s.y;
+        const uint32_t vb = __ballot_sync(FULL, valid);
+        STAT(9, 1);
+        STAT(10, __popc(__ballot_sync(FULL, act)));
+        STAT(11, __popc(vb));
+        if (vb != 0u) {
             STAT(12, 1);
             // branch-free body: an invalid lane runs with sigma = 0 and contributes exact zeros
-            const float4 g2 = st.g2[ts];
+            const float4 g2 = gp[64 * NW];
             const float opac = g1s.z;
             const float vis = __expf(valid ? -sigma : 0.f);
             const float ov = opac * vis;
@@ -366,64 +402,20 @@ blend_bwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
             for (int k = 0; k < CH; ++k) v[6 + k] = fac * vr[k];
 #pragma unroll
             for (int k = 6 + CH; k < 12; ++k) v[k] = 0.f;
-            if (RMODE == 0) {
-                quad_reduce12(v, lane);
-                if ((vb >> qshift) & 15u) {
-                    float* dst = v_rec + (int64_t)st.id[ts] * REC + comp0;
-                    atomicAdd(dst, v[0]);
-                    atomicAdd(dst + 1, v[1]);
-                    if (third) atomicAdd(dst + 2, v[2]);
-                }
-            } else if (RMODE == 1) {
-                const bool up = lane & 1;
-#pragma unroll
-                for (int k = 0; k < 6; ++k) {
-                    const float send = up ? v[k] : v[k + 6];
-                    const float keep = up ? v[k + 6] : v[k];
-                    v[k] = keep + __shfl_xor_sync(FULL, send, 1);
-                }
-                if ((vb >> (lane & 30)) & 3u) {
-                    float* dst = v_rec + (int64_t)st.id[ts] * REC;
-                    if (!up) {
-                        red_v4(dst, v[0], v[1], v[2], v[3]);
-                        red_v2(dst + 4, v[4], v[5]);
-                    } else {
-                        red_v2(dst + 6, v[0], v[1]);
-                        red_v4(dst + 8, v[2], v[3], v[4], v[5]);
-                    }
-                }
-            } else if (RMODE == 3) {
-                // quad reduce that leaves lane 0 with comps 0-3, lane 1 with 4-7, lane 2 with 8-9 and
-                // lane 3 with 10-11, so a quad issues two v4 and one or two v2 REDs (REDG throughput
-                // is per lane-op, and a v4 lane-op costs ~1.7x a scalar one)
-                const bool up = lane & 1, hi = lane & 2;
-                constexpr int A[6] = {0, 1, 2, 3, 8, 9}, Bc[6] = {4, 5, 6, 7, 10, 11};
-                float w6[6];
-#pragma unroll
-                for (int k = 0; k < 6; ++k) {
-                    const float send = up ? v[A[k]] : v[Bc[k]];
-                    const float keep = up ? v[Bc[k]] : v[A[k]];
-                    w6[k] = keep + __shfl_xor_sync(FULL, send, 1);
-                }
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float send = hi ? w6[k] : (k < 2 ? w6[4 + k] : 0.f);
-                    const float r = __shfl_xor_sync(FULL, send, 2);
-                    if (k < 2) w6[4 + k] += hi ? r : 0.f;
-                    w6[k] += hi ? 0.f : r;
-                }
-                if ((vb >> qshift) & 15u) {
-                    float* dst = v_rec + (int64_t)st.id[ts] * REC;
-                    if (!hi) red_v4(dst + 4 * (lane & 1), w6[0], w6[1], w6[2], w6[3]);
-                    else if (CH == 5 || !up) red_v2(dst + 8 + 2 * (lane & 1), w6[4], w6[5]);
-                }
-            } else {
-                if (valid) {
-                    float* dst = v_rec + (int64_t)st.id[ts] * REC;
-                    red_v4(dst, v[0], v[1], v[2], v[3]);
-                    red_v4(dst + 4, v[4], v[5], v[6], v[7]);
-                    red_v4(dst + 8, v[8], v[9], v[10], 0.f);
-                }
+            quad_reduce12(v, lane);
+            if ((vb >> qshift) & 15u) {
+                float* dst = v_rec + (int64_t)st.id[slot] * REC + comp0;
+                atomicAdd(dst, v[0]);
+                atomicAdd(dst + 1, v[1]);
+                if (third) atomicAdd(dst + 2, v[2]);
+            }
+        }
+        if (wmin > base) {
+            ++base;
+            if (staged < n_words) {
+                commit_word<NW, true>(st, pf, staged, bx0, by0, lane);
+                ++staged;
+                prefetch_word(pf, staged, warp_last, -1, n_entries, rec, vals, lane);
             }
         }
     }
@@ -434,7 +426,7 @@ blend_bwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
 using namespace isogs;
 
 namespace {
-constexpr int NB_BWD = 4;
+constexpr int NW_FWD = 4, NW_BWD = 4;
 
 template <typename K>
 int set_smem(K kernel, size_t bytes) {
@@ -459,27 +451,22 @@ extern "C" int isogs_blend_fwd(const isogs_camera* cam, int ch, const float* rec
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
     dim3 grid(dc.tw, dc.th);
-    static const int nb = [] { const char* e = getenv("ISOGS_NBF"); return e ? atoi(e) : 1; }();
-#define ISOGS_LAUNCH_FWD(CHN, NBF)                                                                          \
-    do {                                                                                                   \
-        constexpr size_t smem = sizeof(WarpStage<NBF, false>) * NWARP;                                     \
-        static thread_local int attr_dev = -1;                                                             \
-        int dev = 0;                                                                                       \
-        ISOGS_CUDA(cudaGetDevice(&dev));                                                                   \
-        if (attr_dev != dev) {                                                                             \
-            int rc = set_smem(blend_fwd_kernel<CHN, NBF>, smem);                                           \
-            if (rc != 0) return rc;                                                                        \
-            attr_dev = dev;                                                                                \
-        }                                                                                                  \
-        blend_fwd_kernel<CHN, NBF><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals_sorted,     \
-                                                                   tile_ranges, render, alpha, last);      \
-    } while (0)
-    if (ch == 4) {
-        if (nb == 4) ISOGS_LAUNCH_FWD(4, 4); else if (nb == 2) ISOGS_LAUNCH_FWD(4, 2); else ISOGS_LAUNCH_FWD(4, 1);
-    } else {
-        if (nb == 4) ISOGS_LAUNCH_FWD(5, 4); else if (nb == 2) ISOGS_LAUNCH_FWD(5, 2); else ISOGS_LAUNCH_FWD(5, 1);
+    constexpr size_t smem = sizeof(WarpRing<NW_FWD, false>) * NWARP;
+    static thread_local int attr_dev = -1;
+    int dev = 0;
+    ISOGS_CUDA(cudaGetDevice(&dev));
+    if (attr_dev != dev) {
+        int rc = set_smem(blend_fwd_kernel<4, NW_FWD>, smem);
+        if (rc == 0) rc = set_smem(blend_fwd_kernel<5, NW_FWD>, smem);
+        if (rc != 0) return rc;
+        attr_dev = dev;
     }
-#undef ISOGS_LAUNCH_FWD
+    if (ch == 4)
+        blend_fwd_kernel<4, NW_FWD><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals_sorted, tile_ranges,
+                                                                    render, alpha, last);
+    else
+        blend_fwd_kernel<5, NW_FWD><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals_sorted, tile_ranges,
+                                                                    render, alpha, last);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
 }
@@ -494,32 +481,22 @@ extern "C" int isogs_blend_bwd(const isogs_camera* cam, int ch, int64_t N, const
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
     dim3 grid(dc.tw, dc.th);
-    constexpr size_t smem = sizeof(WarpStage<NB_BWD, true>) * NWARP;
-    static const int rmode = [] { const char* e = getenv("ISOGS_RED"); return e ? atoi(e) : 0; }();
+    constexpr size_t smem = sizeof(WarpRing<NW_BWD, true>) * NWARP;
     static thread_local int attr_dev = -1;
     int dev = 0;
     ISOGS_CUDA(cudaGetDevice(&dev));
     if (attr_dev != dev) {
-        int rc = set_smem(blend_bwd_kernel<4, NB_BWD, 0>, smem);
-        if (rc == 0) rc = set_smem(blend_bwd_kernel<5, NB_BWD, 0>, smem);
-        if (rc == 0) rc = set_smem(blend_bwd_kernel<4, NB_BWD, 1>, smem);
-        if (rc == 0) rc = set_smem(blend_bwd_kernel<5, NB_BWD, 1>, smem);
-        if (rc == 0) rc = set_smem(blend_bwd_kernel<4, NB_BWD, 2>, smem);
-        if (rc == 0) rc = set_smem(blend_bwd_kernel<5, NB_BWD, 2>, smem);
-        if (rc == 0) rc = set_smem(blend_bwd_kernel<4, NB_BWD, 3>, smem);
-        if (rc == 0) rc = set_smem(blend_bwd_kernel<5, NB_BWD, 3>, smem);
+        int rc = set_smem(blend_bwd_kernel<4, NW_BWD>, smem);
+        if (rc == 0) rc = set_smem(blend_bwd_kernel<5, NW_BWD>, smem);
         if (rc != 0) return rc;
         attr_dev = dev;
     }
-#define ISOGS_LAUNCH_BWD(CHN, RM)                                                                              \
-    blend_bwd_kernel<CHN, NB_BWD, RM><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals_sorted, tile_ranges, \
-                                                                      alpha, last, v_render, v_alpha, v_rec)
-    if (ch == 4) {
-        if (rmode == 1) ISOGS_LAUNCH_BWD(4, 1); else if (rmode == 2) ISOGS_LAUNCH_BWD(4, 2); else if (rmode == 3) ISOGS_LAUNCH_BWD(4, 3); else ISOGS_LAUNCH_BWD(4, 0);
-    } else {
-        if (rmode == 1) ISOGS_LAUNCH_BWD(5, 1); else if (rmode == 2) ISOGS_LAUNCH_BWD(5, 2); else if (rmode == 3) ISOGS_LAUNCH_BWD(5, 3); else ISOGS_LAUNCH_BWD(5, 0);
-    }
-#undef ISOGS_LAUNCH_BWD
+    if (ch == 4)
+        blend_bwd_kernel<4, NW_BWD><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals_sorted, tile_ranges,
+                                                                    alpha, last, v_render, v_alpha, v_rec);
+    else
+        blend_bwd_kernel<5, NW_BWD><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals_sorted, tile_ranges,
+                                                                    alpha, last, v_render, v_alpha, v_rec);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
 }
