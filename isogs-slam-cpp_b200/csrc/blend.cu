@@ -68,35 +68,39 @@ __device__ __forceinline__ PixelMap pixel_of(int wid, int lane) {
 }
 
 // Hit mask of 32 staged Gaussians (one per lane) against THIS lane's quad.  The footprint test is
-// conservative: axis-aligned half extents sqrt(2 L cov_xx), sqrt(2 L cov_yy) AND the bounding
-// circle sqrt(2 L lambda_max), each padded for rounding, against the quad's pixel-centre square.
+// conservative and works on SQUARED distances (no square root): squared axis-aligned half extents
+// 2 L cov_xx, 2 L cov_yy AND the squared bounding-circle radius 2 L (max(cov_xx, cov_yy) + |cov_xy|)
+// (Gershgorin bound on lambda_max), each padded for rounding, against the quad's pixel-centre square.
 __device__ __forceinline__ uint32_t quad_hits(bool have, const float4& g0, const float4& g1, float bx0, float by0,
                                               int lane) {
-    float hx = -1.f, hy = -1.f, R2 = -1.f;
+    float hx2 = -1.f, hy2 = -1.f, R2 = -1.f;
     if (have) {
         const float a = 2.0f * g0.z, b = g0.w, c = 2.0f * g1.x;
         const float inv_det = __fdividef(1.0f, fmaf(a, c, -(b * b)));
-        const float twoL = 2.0f * g1.y;
-        const float cxx = c * inv_det, cyy = a * inv_det, cxy = b * inv_det;
-        hx = fmaf(sqrtf(twoL * cxx), 1.001f, 0.01f);
-        hy = fmaf(sqrtf(twoL * cyy), 1.001f, 0.01f);
-        const float mid = 0.5f * (cxx + cyy), dif = 0.5f * (cxx - cyy);
-        const float lam = mid + sqrtf(fmaf(dif, dif, cxy * cxy));
-        const float R = fmaf(sqrtf(twoL * lam), 1.001f, 0.01f);
-        R2 = R * R;
+        const float twoL = 2.0f * g1.y * inv_det;
+        const float cxx = c * twoL, cyy = a * twoL, cxy = fabsf(b * twoL); // 2 L cov
+        hx2 = fmaf(cxx, 1.01f, 0.05f);
+        hy2 = fmaf(cyy, 1.01f, 0.05f);
+        R2 = fmaf(fmaxf(cxx, cyy) + cxy, 1.01f, 0.05f);
     }
     const float X = g0.x - bx0, Y = g0.y - by0; // relative to the block's first pixel centre
-    float ddx[4], ddy[2];
+    float ex2[4], ey2[2];
 #pragma unroll
-    for (int c = 0; c < 4; ++c) ddx[c] = fmaxf(fmaxf((float)(2 * c) - X, X - (float)(2 * c + 1)), 0.f);
+    for (int c = 0; c < 4; ++c) {
+        const float e = fmaxf(fmaxf((float)(2 * c) - X, X - (float)(2 * c + 1)), 0.f);
+        ex2[c] = e * e;
+    }
 #pragma unroll
-    for (int r = 0; r < 2; ++r) ddy[r] = fmaxf(fmaxf((float)(2 * r) - Y, Y - (float)(2 * r + 1)), 0.f);
+    for (int r = 0; r < 2; ++r) {
+        const float e = fmaxf(fmaxf((float)(2 * r) - Y, Y - (float)(2 * r + 1)), 0.f);
+        ey2[r] = e * e;
+    }
     uint32_t bits = 0;
     const int myq = lane >> 2;
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
-        const float ex = ddx[q & 3], ey = ddy[q >> 2];
-        const bool hit = ex <= hx && ey <= hy && fmaf(ex, ex, ey * ey) <= R2;
+        const float ex = ex2[q & 3], ey = ey2[q >> 2];
+        const bool hit = ex <= hx2 && ey <= hy2 && ex + ey <= R2;
         const uint32_t m = __ballot_sync(FULL, hit);
         if (myq == q) bits = m;
     }
@@ -443,6 +447,50 @@ extern "C" int isogs_debug_stats(unsigned long long* out16, int reset) {
 }
 #endif
 
+template <int CH, int NW>
+static int launch_fwd(const DevCam& dc, const float* rec, const int32_t* vals, const int32_t* ranges, float* render,
+                      float* alpha, int32_t* last, cudaStream_t stream) {
+    constexpr size_t smem = sizeof(WarpRing<NW, false>) * NWARP;
+    static thread_local int attr_dev = -1;
+    int dev = 0;
+    ISOGS_CUDA(cudaGetDevice(&dev));
+    if (attr_dev != dev) {
+        int rc = set_smem(blend_fwd_kernel<CH, NW>, smem);
+        if (rc != 0) return rc;
+        attr_dev = dev;
+    }
+    dim3 grid(dc.tw, dc.th);
+    blend_fwd_kernel<CH, NW><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals, ranges, render, alpha, last);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
+
+template <int CH, int NW>
+static int launch_bwd(const DevCam& dc, const float* rec, const int32_t* vals, const int32_t* ranges,
+                      const float* alpha, const int32_t* last, const float* v_render, const float* v_alpha,
+                      float* v_rec, cudaStream_t stream) {
+    constexpr size_t smem = sizeof(WarpRing<NW, true>) * NWARP;
+    static thread_local int attr_dev = -1;
+    int dev = 0;
+    ISOGS_CUDA(cudaGetDevice(&dev));
+    if (attr_dev != dev) {
+        int rc = set_smem(blend_bwd_kernel<CH, NW>, smem);
+        if (rc != 0) return rc;
+        attr_dev = dev;
+    }
+    dim3 grid(dc.tw, dc.th);
+    blend_bwd_kernel<CH, NW><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last, v_render,
+                                                             v_alpha, v_rec);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
+
+static int env_nw(const char* name, int dflt) {
+    const char* e = getenv(name);
+    const int v = e ? atoi(e) : dflt;
+    return (v == 2 || v == 4 || v == 8) ? v : dflt;
+}
+
 extern "C" int isogs_blend_fwd(const isogs_camera* cam, int ch, const float* rec, const int32_t* vals_sorted,
                                const int32_t* tile_ranges, float* render, float* alpha, int32_t* last,
                                void* stream_) {
@@ -450,25 +498,11 @@ extern "C" int isogs_blend_fwd(const isogs_camera* cam, int ch, const float* rec
     if (!cam || (ch != 4 && ch != 5)) { set_error("isogs_blend_fwd: ch must be 4 or 5"); return ISOGS_E_ARG; }
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
-    dim3 grid(dc.tw, dc.th);
-    constexpr size_t smem = sizeof(WarpRing<NW_FWD, false>) * NWARP;
-    static thread_local int attr_dev = -1;
-    int dev = 0;
-    ISOGS_CUDA(cudaGetDevice(&dev));
-    if (attr_dev != dev) {
-        int rc = set_smem(blend_fwd_kernel<4, NW_FWD>, smem);
-        if (rc == 0) rc = set_smem(blend_fwd_kernel<5, NW_FWD>, smem);
-        if (rc != 0) return rc;
-        attr_dev = dev;
-    }
-    if (ch == 4)
-        blend_fwd_kernel<4, NW_FWD><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals_sorted, tile_ranges,
-                                                                    render, alpha, last);
-    else
-        blend_fwd_kernel<5, NW_FWD><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals_sorted, tile_ranges,
-                                                                    render, alpha, last);
-    ISOGS_CUDA(cudaGetLastError());
-    return ISOGS_OK;
+    static const int nw = env_nw("ISOGS_NW_FWD", NW_FWD); // ring words per warp (tuning knob)
+#define ISOGS_FWD(CHN, NWN) launch_fwd<CHN, NWN>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, stream)
+    if (ch == 4) return nw == 2 ? ISOGS_FWD(4, 2) : nw == 8 ? ISOGS_FWD(4, 8) : ISOGS_FWD(4, 4);
+    return nw == 2 ? ISOGS_FWD(5, 2) : nw == 8 ? ISOGS_FWD(5, 8) : ISOGS_FWD(5, 4);
+#undef ISOGS_FWD
 }
 
 extern "C" int isogs_blend_bwd(const isogs_camera* cam, int ch, int64_t N, const float* rec,
@@ -480,23 +514,10 @@ extern "C" int isogs_blend_bwd(const isogs_camera* cam, int ch, int64_t N, const
     if (!cam || (ch != 4 && ch != 5)) { set_error("isogs_blend_bwd: ch must be 4 or 5"); return ISOGS_E_ARG; }
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
-    dim3 grid(dc.tw, dc.th);
-    constexpr size_t smem = sizeof(WarpRing<NW_BWD, true>) * NWARP;
-    static thread_local int attr_dev = -1;
-    int dev = 0;
-    ISOGS_CUDA(cudaGetDevice(&dev));
-    if (attr_dev != dev) {
-        int rc = set_smem(blend_bwd_kernel<4, NW_BWD>, smem);
-        if (rc == 0) rc = set_smem(blend_bwd_kernel<5, NW_BWD>, smem);
-        if (rc != 0) return rc;
-        attr_dev = dev;
-    }
-    if (ch == 4)
-        blend_bwd_kernel<4, NW_BWD><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals_sorted, tile_ranges,
-                                                                    alpha, last, v_render, v_alpha, v_rec);
-    else
-        blend_bwd_kernel<5, NW_BWD><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals_sorted, tile_ranges,
-                                                                    alpha, last, v_render, v_alpha, v_rec);
-    ISOGS_CUDA(cudaGetLastError());
-    return ISOGS_OK;
+    static const int nw = env_nw("ISOGS_NW_BWD", NW_BWD);
+#define ISOGS_BWD(CHN, NWN) \
+    launch_bwd<CHN, NWN>(dc, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream)
+    if (ch == 4) return nw == 2 ? ISOGS_BWD(4, 2) : nw == 8 ? ISOGS_BWD(4, 8) : ISOGS_BWD(4, 4);
+    return nw == 2 ? ISOGS_BWD(5, 2) : nw == 8 ? ISOGS_BWD(5, 8) : ISOGS_BWD(5, 4);
+#undef ISOGS_BWD
 }
