@@ -68,7 +68,9 @@ int isogs_temp_bytes(int64_t N, int64_t cap, size_t* scan_bytes, size_t* sort_by
  * ch 4: record colours {c0,c1,c2,z}; ch 5: {c0,c1,c2,z,z*z}.
  * Outputs: rec [N,12], radii [N,2] i32, tiles [N] i32, cum [N] i32 (inclusive scan of tiles).
  * If n_isects_host (PINNED or pageable HOST int64*) is non-null the call copies cum[N-1]
- * there and synchronises the stream (the one sync of a forward, == Intersect.cpp:80). */
+ * there and synchronises the stream (the one sync of a forward, == Intersect.cpp:80).
+ * tiles and cum may both be null (then n_isects_host must be null too): the sync-free pipeline
+ * (isogs_tile_bin_async) counts intersections per tile itself and needs neither. */
 int isogs_preprocess_fwd(const isogs_camera* cam, const isogs_pose* pose, const float* pose_dev,
                          int64_t N, const float* means, const float* scales, int scale_dim,
                          const float* quats, const float* opacities, const float* colors,
@@ -85,6 +87,19 @@ int isogs_tile_bin(const isogs_camera* cam, int64_t N, int64_t M,
                    uint64_t* keys_unsorted, int32_t* vals_unsorted,
                    uint64_t* keys_sorted, int32_t* vals_sorted, int32_t* tile_ranges,
                    void* sort_temp, size_t sort_temp_bytes, void* stream);
+
+/* Sync-free variant of isogs_tile_bin for the fused step: removes the blocking
+ * `n_isects = cum[-1].item()` of gsplat Intersect.cpp:80.  The intersection count is NOT known on
+ * the host; `capacity` is the size of bucket / keys_sorted / vals_sorted.  totals (DEVICE int32[2])
+ * receives {n_isects, overflow}: when n_isects > capacity the tile lists are truncated to the
+ * capacity (no out-of-bounds access), overflow = 1, and the caller must grow the buffers and redo
+ * the step.  bucket [capacity] u64 is scratch; keys_sorted may be null.  Output order is
+ * bit-identical to isogs_tile_bin. */
+int isogs_tile_bin_async(const isogs_camera* cam, int64_t N, int64_t capacity,
+                         const float* rec, const int32_t* radii,
+                         uint64_t* bucket, uint64_t* keys_sorted /*nullable*/, int32_t* vals_sorted,
+                         int32_t* tile_ranges, int32_t* totals,
+                         void* sort_temp, size_t sort_temp_bytes, void* stream);
 
 /* renderCUDA forward: replaces rasterize_to_pixels_3dgs_fwd (Ops.h:223-238;
  * RasterizeToPixels3DGSFwd.cu:17-188).  render [ch,H,W] planar (the Inria API's CHW),

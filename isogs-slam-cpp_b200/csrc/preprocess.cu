@@ -36,7 +36,7 @@ preprocess_fwd_kernel(DevCam cam, DevPose pose, int64_t N, const float* __restri
         r[1] = make_float4(0.f, 0.f, 0.f, 0.f);
         r[2] = make_float4(0.f, 0.f, 0.f, 0.f);
         radii[i] = make_int2(0, 0);
-        tiles[i] = 0;
+        if (tiles) tiles[i] = 0;
         return;
     }
     float z = P.mc[2];
@@ -45,8 +45,10 @@ preprocess_fwd_kernel(DevCam cam, DevPose pose, int64_t N, const float* __restri
     r[2] = make_float4(colors[3 * i + 1], colors[3 * i + 2], z, (ch == 5) ? z * z : 0.0f);
     int rx = (int)P.rx, ry = (int)P.ry;
     radii[i] = make_int2(rx, ry);
-    Rect t = tile_rect(P.mx, P.my, rx, ry, cam.tw, cam.th);
-    tiles[i] = (t.y1 - t.y0) * (t.x1 - t.x0);
+    if (tiles) {
+        Rect t = tile_rect(P.mx, P.my, rx, ry, cam.tw, cam.th);
+        tiles[i] = (t.y1 - t.y0) * (t.x1 - t.x0);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -352,6 +354,10 @@ extern "C" int isogs_preprocess_fwd(const isogs_camera* cam, const isogs_pose* p
         preprocess_fwd_kernel<false><<<grid, block, 0, stream>>>(dc, dp, N, means, scales, quats, opacities, colors,
                                                                   ch, flags, (float4*)rec, (int2*)radii, tiles);
     ISOGS_CUDA(cudaGetLastError());
+    if (!tiles || !cum) { // sync-free pipeline (isogs_tile_bin_async counts per tile itself)
+        if (n_isects_host) { set_error("n_isects_host needs tiles and cum"); return ISOGS_E_ARG; }
+        return ISOGS_OK;
+    }
     size_t need = 0;
     ISOGS_CUDA(cub::DeviceScan::InclusiveSum(nullptr, need, tiles, cum, (int)N, stream));
     if (need > scan_temp_bytes) { set_error("scan temp too small: need %zu have %zu", need, scan_temp_bytes); return ISOGS_E_ARG; }

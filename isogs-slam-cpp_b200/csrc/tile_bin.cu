@@ -68,10 +68,14 @@ tile_count_kernel(int tw, int th, int64_t N, const float4* __restrict__ rec, con
         for (int x = q.x0; x < q.x1; ++x) atomicAdd(counts + (y * tw + x), 1);
 }
 
-// single CTA exclusive scan of counts[0..n) -> ranges[0..n]; also zeroes the cursors
+// single CTA exclusive scan of counts[0..n) -> ranges[0..n]; also zeroes the cursors.
+// capacity >= 0 (sync-free pipeline): `ranges` is clamped to the capacity of the intersection
+// buffers, the unclamped offsets go to `true_ranges` (the scatter places by them and drops what
+// does not fit) and totals[0] = n_isects, totals[1] = 1 if it exceeds the capacity.
 __global__ void __launch_bounds__(1024)
 tile_scan_kernel(int n, const int32_t* __restrict__ counts, int32_t* __restrict__ ranges,
-                 int32_t* __restrict__ cursors) {
+                 int32_t* __restrict__ cursors, int32_t capacity, int32_t* __restrict__ true_ranges,
+                 int32_t* __restrict__ totals) {
     __shared__ int32_t s_warp[32];
     __shared__ int32_t s_carry;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -100,18 +104,28 @@ tile_scan_kernel(int n, const int32_t* __restrict__ counts, int32_t* __restrict_
         __syncthreads();
         const int32_t carry = s_carry;
         const int32_t incl = v + (wid > 0 ? s_warp[wid - 1] : 0) + carry;
-        if (i < n) { ranges[i] = incl - c; cursors[i] = 0; }
+        if (i < n) {
+            const int32_t ex = incl - c;
+            ranges[i] = capacity >= 0 ? min(ex, capacity) : ex;
+            if (true_ranges) true_ranges[i] = ex;
+            cursors[i] = 0;
+        }
         __syncthreads();
         if (tid == 1023) s_carry = incl;
         __syncthreads();
     }
-    if (tid == 0) ranges[n] = s_carry;
+    if (tid == 0) {
+        const int32_t total = s_carry;
+        ranges[n] = capacity >= 0 ? min(total, capacity) : total;
+        if (true_ranges) true_ranges[n] = total;
+        if (totals) { totals[0] = total; totals[1] = (capacity >= 0 && total > capacity) ? 1 : 0; }
+    }
 }
 
 __global__ void __launch_bounds__(256)
 tile_scatter_kernel(int tw, int th, int64_t N, const float4* __restrict__ rec, const int2* __restrict__ radii,
                     const int32_t* __restrict__ ranges, int32_t* __restrict__ cursors,
-                    uint64_t* __restrict__ bucket) {
+                    uint64_t* __restrict__ bucket, int32_t capacity) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
     int2 rad = radii[i];
@@ -124,7 +138,7 @@ tile_scatter_kernel(int tw, int th, int64_t N, const float4* __restrict__ rec, c
         for (int x = q.x0; x < q.x1; ++x) {
             const int t = y * tw + x;
             const int slot = ranges[t] + atomicAdd(cursors + t, 1);
-            bucket[slot] = v;
+            if (slot < capacity) bucket[slot] = v;
         }
 }
 
@@ -160,7 +174,7 @@ tile_count_smem_kernel(int tw, int th, int n_tiles, int64_t N, const float4* __r
 __global__ void __launch_bounds__(BIN_THREADS)
 tile_scatter_smem_kernel(int tw, int th, int n_tiles, int64_t N, const float4* __restrict__ rec,
                          const int2* __restrict__ radii, const int32_t* __restrict__ ranges,
-                         int32_t* __restrict__ cursors, uint64_t* __restrict__ bucket) {
+                         int32_t* __restrict__ cursors, uint64_t* __restrict__ bucket, int32_t capacity) {
     extern __shared__ int32_t s_bins[];
     for (int b = threadIdx.x; b < n_tiles; b += BIN_THREADS) s_bins[b] = 0;
     __syncthreads();
@@ -190,11 +204,13 @@ tile_scatter_smem_kernel(int tw, int th, int n_tiles, int64_t N, const float4* _
     for (int c = 0; c < BIN_KEEP; ++c)
         if (c < ncell) {
             const int t = (q.y0 + c / w) * tw + q.x0 + c % w;
-            bucket[ranges[t] + s_bins[t] + rank[c]] = v;
+            const int slot = ranges[t] + s_bins[t] + rank[c];
+            if (slot < capacity) bucket[slot] = v;
         }
     for (int c = BIN_KEEP; c < ncell; ++c) {
         const int t = (q.y0 + c / w) * tw + q.x0 + c % w;
-        bucket[ranges[t] + atomicAdd(cursors + t, 1)] = v;
+        const int slot = ranges[t] + atomicAdd(cursors + t, 1);
+        if (slot < capacity) bucket[slot] = v;
     }
 }
 
@@ -273,6 +289,55 @@ inline int sort_end_bit(int n_tiles) {
 
 using namespace isogs;
 
+// counting sort by tile + per-tile sort (see the kernels above); scratch = counts | cursors | true ranges.
+// clamp=false: `capacity` is the exact intersection count M.  clamp=true (sync-free pipeline):
+// `capacity` is the size of the intersection buffers, M is not known on the host; totals (DEVICE
+// int32[2]) receives {M, overflow flag}.
+static int counting_bin(int tw, int th, int64_t N, int32_t capacity, bool clamp, const float* rec,
+                        const int32_t* radii, uint64_t* bucket, uint64_t* keys_sorted, int32_t* vals_sorted,
+                        int32_t* tile_ranges, void* sort_temp, size_t sort_temp_bytes, int32_t* totals,
+                        cudaStream_t stream) {
+    const int n_tiles = tw * th;
+    const size_t need_scratch = sizeof(int32_t) * 3 * (size_t)(n_tiles + 1);
+    if (need_scratch > sort_temp_bytes) { set_error("sort temp too small for %d tiles", n_tiles); return ISOGS_E_ARG; }
+    int32_t* counts = (int32_t*)sort_temp;
+    int32_t* cursors = counts + (n_tiles + 1);
+    int32_t* true_ranges = cursors + (n_tiles + 1);
+    ISOGS_CUDA(cudaMemsetAsync(counts, 0, sizeof(int32_t) * (n_tiles + 1), stream));
+    const int block = 256;
+    const unsigned gN = (unsigned)((N + block - 1) / block);
+    const bool smem_bins = n_tiles <= 11264; // 44 KB of bins fits the default 48 KB dynamic limit
+    const unsigned gB = (unsigned)((N + BIN_THREADS - 1) / BIN_THREADS);
+    const size_t bin_bytes = sizeof(int32_t) * (size_t)n_tiles;
+    if (smem_bins)
+        tile_count_smem_kernel<<<gB, BIN_THREADS, bin_bytes, stream>>>(tw, th, n_tiles, N, (const float4*)rec,
+                                                                       (const int2*)radii, counts);
+    else
+        tile_count_kernel<<<gN, block, 0, stream>>>(tw, th, N, (const float4*)rec, (const int2*)radii, counts);
+    tile_scan_kernel<<<1, 1024, 0, stream>>>(n_tiles, counts, tile_ranges, cursors, clamp ? capacity : -1,
+                                             clamp ? true_ranges : nullptr, totals);
+    const int32_t* place = clamp ? true_ranges : tile_ranges;
+    if (smem_bins)
+        tile_scatter_smem_kernel<<<gB, BIN_THREADS, bin_bytes, stream>>>(tw, th, n_tiles, N, (const float4*)rec,
+                                                                         (const int2*)radii, place, cursors, bucket,
+                                                                         capacity);
+    else
+        tile_scatter_kernel<<<gN, block, 0, stream>>>(tw, th, N, (const float4*)rec, (const int2*)radii, place, cursors,
+                                                      bucket, capacity);
+    static bool attr_set = false;
+    if (!attr_set) {
+        ISOGS_CUDA(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        SORT_SMEM_MAX * (int)sizeof(uint64_t)));
+        attr_set = true;
+    }
+    tile_sort_kernel<<<n_tiles, 256, SORT_SMEM_SMALL * sizeof(uint64_t), stream>>>(
+        0, SORT_SMEM_SMALL, tile_ranges, bucket, keys_sorted, vals_sorted);
+    tile_sort_kernel<<<n_tiles, 256, SORT_SMEM_MAX * sizeof(uint64_t), stream>>>(
+        SORT_SMEM_SMALL, 0x7fffffff, tile_ranges, bucket, keys_sorted, vals_sorted);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
+
 extern "C" int isogs_temp_bytes(int64_t N, int64_t cap, size_t* scan_bytes, size_t* sort_bytes) {
     if (N < 0 || cap < 0 || N >= (1ll << 31) || cap >= (1ll << 31)) { set_error("isogs_temp_bytes: bad sizes"); return ISOGS_E_ARG; }
     if (scan_bytes) {
@@ -306,42 +371,9 @@ extern "C" int isogs_tile_bin(const isogs_camera* cam, int64_t N, int64_t M, con
     const int block = 256;
     const unsigned gN = (unsigned)((N + block - 1) / block);
     static const bool use_cub = [] { const char* e = getenv("ISOGS_BIN"); return e && e[0] == 'c'; }();
-    if (!use_cub) {
-        // counting sort by tile + per-tile sort (see the kernels above); scratch = counts | cursors
-        const size_t need_scratch = sizeof(int32_t) * 2 * (size_t)(n_tiles + 1);
-        if (need_scratch > sort_temp_bytes) { set_error("sort temp too small for %d tiles", n_tiles); return ISOGS_E_ARG; }
-        int32_t* counts = (int32_t*)sort_temp;
-        int32_t* cursors = counts + (n_tiles + 1);
-        ISOGS_CUDA(cudaMemsetAsync(counts, 0, sizeof(int32_t) * (n_tiles + 1), stream));
-        const bool smem_bins = n_tiles <= 11264; // 44 KB of bins fits the default 48 KB dynamic limit
-        const unsigned gB = (unsigned)((N + BIN_THREADS - 1) / BIN_THREADS);
-        const size_t bin_bytes = sizeof(int32_t) * (size_t)n_tiles;
-        if (smem_bins)
-            tile_count_smem_kernel<<<gB, BIN_THREADS, bin_bytes, stream>>>(tw, th, n_tiles, N, (const float4*)rec,
-                                                                           (const int2*)radii, counts);
-        else
-            tile_count_kernel<<<gN, block, 0, stream>>>(tw, th, N, (const float4*)rec, (const int2*)radii, counts);
-        tile_scan_kernel<<<1, 1024, 0, stream>>>(n_tiles, counts, tile_ranges, cursors);
-        if (smem_bins)
-            tile_scatter_smem_kernel<<<gB, BIN_THREADS, bin_bytes, stream>>>(tw, th, n_tiles, N, (const float4*)rec,
-                                                                             (const int2*)radii, tile_ranges, cursors,
-                                                                             keys_unsorted);
-        else
-            tile_scatter_kernel<<<gN, block, 0, stream>>>(tw, th, N, (const float4*)rec, (const int2*)radii,
-                                                          tile_ranges, cursors, keys_unsorted);
-        static bool attr_set = false;
-        if (!attr_set) {
-            ISOGS_CUDA(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            SORT_SMEM_MAX * (int)sizeof(uint64_t)));
-            attr_set = true;
-        }
-        tile_sort_kernel<<<n_tiles, 256, SORT_SMEM_SMALL * sizeof(uint64_t), stream>>>(
-            0, SORT_SMEM_SMALL, tile_ranges, keys_unsorted, keys_sorted, vals_sorted);
-        tile_sort_kernel<<<n_tiles, 256, SORT_SMEM_MAX * sizeof(uint64_t), stream>>>(
-            SORT_SMEM_SMALL, 0x7fffffff, tile_ranges, keys_unsorted, keys_sorted, vals_sorted);
-        ISOGS_CUDA(cudaGetLastError());
-        return ISOGS_OK;
-    }
+    if (!use_cub)
+        return counting_bin(tw, th, N, (int32_t)M, /*clamp=*/false, rec, radii, keys_unsorted, keys_sorted, vals_sorted,
+                            tile_ranges, sort_temp, sort_temp_bytes, nullptr, stream);
     emit_keys_kernel<<<gN, block, 0, stream>>>(
         tw, th, N, (const float4*)rec, (const int2*)radii, cum, keys_unsorted, vals_unsorted);
     ISOGS_CUDA(cudaGetLastError());
@@ -355,4 +387,23 @@ extern "C" int isogs_tile_bin(const isogs_camera* cam, int64_t N, int64_t M, con
     tile_ranges_kernel<<<(unsigned)((M + block - 1) / block), block, 0, stream>>>(M, n_tiles, keys_sorted, tile_ranges);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
+}
+
+extern "C" int isogs_tile_bin_async(const isogs_camera* cam, int64_t N, int64_t capacity, const float* rec,
+                                    const int32_t* radii, uint64_t* bucket, uint64_t* keys_sorted,
+                                    int32_t* vals_sorted, int32_t* tile_ranges, int32_t* totals, void* sort_temp,
+                                    size_t sort_temp_bytes, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!cam || N < 0 || capacity < 0 || capacity >= (1ll << 31) || !totals) {
+        set_error("isogs_tile_bin_async: bad argument");
+        return ISOGS_E_ARG;
+    }
+    const int tw = (cam->width + TILE - 1) / TILE, th = (cam->height + TILE - 1) / TILE;
+    if (N == 0) {
+        ISOGS_CUDA(cudaMemsetAsync(tile_ranges, 0, sizeof(int32_t) * (tw * th + 1), stream));
+        ISOGS_CUDA(cudaMemsetAsync(totals, 0, sizeof(int32_t) * 2, stream));
+        return ISOGS_OK;
+    }
+    return counting_bin(tw, th, N, (int32_t)capacity, /*clamp=*/true, rec, radii, bucket, keys_sorted, vals_sorted,
+                        tile_ranges, sort_temp, sort_temp_bytes, totals, stream);
 }

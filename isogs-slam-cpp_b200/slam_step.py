@@ -101,42 +101,69 @@ class StepWorkspace:
         self.losses, self.v_pose, self.pose_acc = self.small[0:4], self.small[4:11], self.small[11:27]
         self.isect_cap = 0
         self._grow_isects(max(1024, 3 * n_cap))
-        self.M = 0
+        # device-side intersection count {n_isects, overflow} + its lagged pinned mirror
+        self.totals = torch.zeros((2,), dtype=i32, device=device)
+        self.totals_host = torch.zeros((2,), dtype=i32).pin_memory()
+        self._totals_ev = None
+
+    @property
+    def M(self):
+        """Intersection count of the last forward (synchronises; for reports and tests only)."""
+        return int(self.totals[0].item())
+
+    def post_totals(self):
+        """Queue an async copy of {n_isects, overflow} to pinned memory (no sync)."""
+        self.totals_host.copy_(self.totals, non_blocking=True)
+        self._totals_ev = torch.cuda.Event()
+        self._totals_ev.record()
+
+    def check_overflow(self, wait=False):
+        """Look at the PREVIOUS forward's count if its copy has landed.  On overflow the tile lists of
+        that forward were truncated (never out of bounds): grow the buffers and report it."""
+        ev = self._totals_ev
+        if ev is None or not (wait or ev.query()):
+            return False
+        if wait:
+            ev.synchronize()
+        self._totals_ev = None
+        n, over = int(self.totals_host[0]), int(self.totals_host[1])
+        if over:
+            self._grow_isects(int(n * 1.25) + 1024)
+            import warnings
+            warnings.warn(f"tile-intersection buffers overflowed (needed {n}); grown to {self.isect_cap}. "
+                          "The affected step rendered truncated tile lists.")
+            return True
+        return False
 
     def _grow_isects(self, cap):
         dev = self.device
         self.isect_cap = int(cap)
-        self.ku = torch.empty((cap,), dtype=torch.int64, device=dev)
-        self.ks = torch.empty((cap,), dtype=torch.int64, device=dev)
-        self.vu = torch.empty((cap,), dtype=torch.int32, device=dev)
-        self.vs = torch.empty((cap,), dtype=torch.int32, device=dev)
+        self.ku = torch.empty((cap,), dtype=torch.int64, device=dev)   # (depth | id) tile buckets (scratch)
+        self.vs = torch.empty((cap,), dtype=torch.int32, device=dev)   # depth-sorted Gaussian ids per tile
         _, self.sort_b = _lib.temp_bytes(0, cap)
         self.sort_tmp = torch.empty((self.sort_b,), dtype=torch.uint8, device=dev)
 
 
 def render_forward(ws, gmap, pose=None, pose_dev=None, ch=5, marks=None):
-    """preprocess (raw params, fused activations + frame transform) -> bin -> blend.  One host sync (M)."""
+    """preprocess (raw params, fused activations + frame transform) -> bin -> blend, with NO host sync:
+    the intersection count stays on the device (ws.totals) and is checked one step late
+    (StepWorkspace.check_overflow), replacing the blocking `.item()` of gsplat Intersect.cpp:80."""
     cam, N = ws.cam, gmap.count
     flags = _lib.F_LOG_SCALES | _lib.F_LOGIT_OPAC
     L, st = lib(), _stream()
-    m = C.c_int64(0)
+    ws.check_overflow()
     quats = None if gmap.isotropic else gmap.p["unnorm_rotations"]
     check(L.isogs_preprocess_fwd(C.byref(cam), C.byref(pose) if pose is not None else None, _ptr(pose_dev), N,
                                  _ptr(gmap.p["means3D"]), _ptr(gmap.p["log_scales"]), gmap.sd, _ptr(quats),
                                  _ptr(gmap.p["logit_opacities"]), _ptr(gmap.p["rgb_colors"]), ch, flags,
-                                 _ptr(ws.rec), _ptr(ws.radii), _ptr(ws.tiles), _ptr(ws.cum), _ptr(ws.scan_tmp),
-                                 ws.scan_b, C.byref(m), st))
-    M = int(m.value)
+                                 _ptr(ws.rec), _ptr(ws.radii), None, None, None, 0, None, st))
     _mark(marks, "preprocess_fwd")
-    if M > ws.isect_cap:
-        ws._grow_isects(int(M * 1.25) + 1024)
-    ws.M = M
-    check(L.isogs_tile_bin(C.byref(cam), N, M, _ptr(ws.rec), _ptr(ws.radii), _ptr(ws.cum), _ptr(ws.ku), _ptr(ws.vu),
-                           _ptr(ws.ks), _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.sort_tmp), ws.sort_b, st))
+    check(L.isogs_tile_bin_async(C.byref(cam), N, ws.isect_cap, _ptr(ws.rec), _ptr(ws.radii), _ptr(ws.ku), None,
+                                 _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.totals), _ptr(ws.sort_tmp), ws.sort_b, st))
     _mark(marks, "tile_bin")
     check(L.isogs_blend_fwd(C.byref(cam), ch, _ptr(ws.rec), _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.render),
                             _ptr(ws.alpha), _ptr(ws.last), st))
-    return M
+    ws.post_totals()
 
 
 def render_backward(ws, gmap, pose=None, pose_dev=None, ch=5, want_gaussians=True, want_pose=False, marks=None):
@@ -145,7 +172,7 @@ def render_backward(ws, gmap, pose=None, pose_dev=None, ch=5, want_gaussians=Tru
     L, st = lib(), _stream()
     ws.v_rec[:N].zero_()
     _mark(marks, "zero_v_rec")
-    if ws.M > 0:
+    if N > 0:
         check(L.isogs_blend_bwd(C.byref(cam), ch, N, _ptr(ws.rec), _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.alpha),
                                 _ptr(ws.last), _ptr(ws.v_render), None, _ptr(ws.v_rec), st))
     _mark(marks, "blend_bwd")
