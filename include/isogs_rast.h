@@ -157,6 +157,12 @@ typedef struct isogs_adam_group {
 int isogs_adam_fused(const isogs_adam_group* groups /*HOST*/, int n_groups, float beta1, float beta2,
                      float eps, int step, void* stream);
 
+/* best-candidate selection of the tracking loop (python_ordinary/scripts/splatam.py:1287-1290),
+ * on the device so the loop needs no host sync: if losses[0] (evaluated BEFORE this iteration's
+ * Adam step) < best[7], then best[0..6] = pose (the values AFTER the step) and best[7] = losses[0].
+ * best: DEVICE float[8] = {q[4], t[3], min_loss}; initialise best[7] to 1e20 (splatam.py:1242). */
+int isogs_pose_keep_best(const float* losses, const float* pose, float* best, void* stream);
+
 /* silhouette-driven prune compaction: replaces prune_gaussians + remove_points
  * (python_ordinary/utils/slam_external.py:139-188) and GaussianModel::prune
  * (cpp/src/core/gaussian_model.cpp:291-331).  keep[i] = !(sigmoid(logit_o) < opac_thres ||

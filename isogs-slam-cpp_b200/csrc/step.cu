@@ -233,9 +233,28 @@ __global__ void densify_count_kernel(int64_t P, const int32_t* __restrict__ scan
     }
 }
 
+// keep the best tracking candidate (splatam.py:1287-1290): the pose AFTER this iteration's Adam step
+// is saved when the loss evaluated BEFORE the step is the smallest seen so far
+__global__ void pose_keep_best_kernel(const float* __restrict__ losses, const float* __restrict__ pose,
+                                      float* __restrict__ best) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const float loss = losses[0];
+    if (loss < best[7]) {
+        best[7] = loss;
+        for (int k = 0; k < 7; ++k) best[k] = pose[k];
+    }
+}
+
 } // namespace isogs
 
 using namespace isogs;
+
+extern "C" int isogs_pose_keep_best(const float* losses, const float* pose, float* best, void* stream_) {
+    if (!losses || !pose || !best) { set_error("isogs_pose_keep_best: null argument"); return ISOGS_E_ARG; }
+    pose_keep_best_kernel<<<1, 32, 0, (cudaStream_t)stream_>>>(losses, pose, best);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
 
 extern "C" int isogs_loss_l1_fused(const isogs_camera* cam, int mode, const float* render, const float* alpha,
                                    const float* gt_rgb, const float* gt_depth, float w_im, float w_depth,

@@ -240,7 +240,29 @@ class PoseState:
         self.pose = torch.tensor(list(q) + list(t), dtype=torch.float32, device=device)
         self.m = torch.zeros_like(self.pose)
         self.v = torch.zeros_like(self.pose)
+        # best candidate {q, t, min loss} (splatam.py:1240-1242,1287-1290), kept on the device
+        self.best = torch.tensor(list(q) + list(t) + [1e20], dtype=torch.float32, device=device)
         self.step_count = 0
+
+    def best_pose(self):
+        """(q, t) of the best candidate -- what the reference writes back (splatam.py:1321-1323)."""
+        b = self.best.cpu().numpy()
+        return b[:4].copy(), b[4:7].copy()
+
+
+def init_camera_pose(prev1, prev2=None, forward_prop=True):
+    """initialize_camera_pose (splatam.py:844-863): constant-velocity initialisation of the next frame's
+    pose from the two previous (q, t) pairs; HOST arithmetic on 7 floats."""
+    import numpy as np
+    q1, t1 = (np.asarray(a, dtype=np.float32) for a in prev1)
+    if prev2 is None or not forward_prop:
+        return q1.copy(), t1.copy()
+    q2, t2 = (np.asarray(a, dtype=np.float32) for a in prev2)
+    n1 = q1 / max(float(np.linalg.norm(q1)), 1e-12)
+    n2 = q2 / max(float(np.linalg.norm(q2)), 1e-12)
+    q = n1 + (n1 - n2)
+    q = q / max(float(np.linalg.norm(q)), 1e-12)
+    return q.astype(np.float32), (t1 + (t1 - t2)).astype(np.float32)
 
 
 def track_step(ws, gmap, ps, gt_rgb, gt_depth, lrs=TRACKING_LRS, eps=1e-8, use_sil=True, sil_thres=0.99):
@@ -259,4 +281,5 @@ def track_step(ws, gmap, ps, gt_rgb, gt_depth, lrs=TRACKING_LRS, eps=1e-8, use_s
         arr[i].numel = n
         arr[i].lr = lr
     check(lib().isogs_adam_fused(arr, 2, 0.9, 0.999, eps, ps.step_count, _stream()))
+    check(lib().isogs_pose_keep_best(_ptr(ws.losses), _ptr(ps.pose), _ptr(ps.best), _stream()))
     return ws.losses

@@ -1,0 +1,115 @@
+"""TEST INFRASTRUCTURE: the tracking / mapping iteration of python_ordinary/scripts/splatam.py
+(1247-1290, 1412-1476; L1 terms) executed with the CPU oracle.  Used by the GPU parity tests as the
+checker for slam_step.map_step / track_step and for the 50-frame ATE comparison."""
+import numpy as np
+
+MAP_LRS = dict(means3D=1e-4, rgb_colors=2.5e-3, logit_opacities=0.05, log_scales=1e-3)
+
+
+def new_state(params):
+    p = {k: np.ascontiguousarray(v, dtype=np.float32).copy() for k, v in params.items()}
+    return dict(p=p, m={k: np.zeros_like(v) for k, v in p.items()}, v={k: np.zeros_like(v) for k, v in p.items()},
+                step=0)
+
+
+def reset_optimizer(state):
+    for k in state["m"]:
+        state["m"][k][...] = 0
+        state["v"][k][...] = 0
+    state["step"] = 0
+
+
+def _flags(orc):
+    return orc.F_LOG_SCALES | orc.F_LOGIT_OPAC
+
+
+def map_iteration(orc, ocam, state, q, t, gt_rgb, gt_depth, grads_out=None, extra_grads=None):
+    """One mapping iteration on one keyframe.  extra_grads: list of gradient dicts from OTHER ranks of the
+    data-parallel schedule (averaged with this one before Adam)."""
+    p = state["p"]
+    pose = orc.make_pose(q, t)
+    lo = p["logit_opacities"].reshape(-1)
+    o = orc.render_full(ocam, p["means3D"], p["log_scales"], None, lo, p["rgb_colors"], ch=5, flags=_flags(orc),
+                        pose=pose)
+    v_render, losses = orc.loss_l1(ocam, 1, o["render"], o["alpha"], gt_rgb, gt_depth)
+    v_rec = orc.blend_bwd(ocam, 5, o["rec"], o["vals"], o["ranges"], o["alpha"], o["last"], v_render)
+    g = orc.preprocess_bwd(ocam, p["means3D"], p["log_scales"], None, lo, p["rgb_colors"], o["radii"], o["rec"], v_rec,
+                           ch=5, flags=_flags(orc), pose=pose)
+    grads = dict(means3D=g["means"], rgb_colors=g["colors"], logit_opacities=g["opacities"], log_scales=g["scales"])
+    if grads_out is not None:
+        grads_out.update({k: np.array(v, copy=True) for k, v in grads.items()})
+    if extra_grads:
+        n = 1 + len(extra_grads)
+        grads = {k: (sum([v.reshape(-1)] + [e[k].reshape(-1) for e in extra_grads]) / n).astype(np.float32)
+                 for k, v in grads.items()}
+    state["step"] += 1
+    for k, lr in MAP_LRS.items():
+        orc.adam(p[k].reshape(-1), np.ascontiguousarray(grads[k]).reshape(-1), state["m"][k].reshape(-1),
+                 state["v"][k].reshape(-1), lr, eps=1e-15, step=state["step"])
+    return float(losses[0])
+
+
+def gradients_only(orc, ocam, params, q, t, gt_rgb, gt_depth):
+    g = {}
+    st = new_state(params)
+    map_iteration(orc, ocam, st, q, t, gt_rgb, gt_depth, grads_out=g)
+    return g
+
+
+class TrackState:
+    def __init__(self, q, t):
+        self.pose = np.array(list(q) + list(t), dtype=np.float32)
+        self.m = np.zeros(7, np.float32)
+        self.v = np.zeros(7, np.float32)
+        self.step = 0
+        self.best = self.pose.copy()
+        self.best_loss = 1e20
+
+
+def track_iteration(orc, ocam, params, ts, gt_rgb, gt_depth, lr_rot=4e-4, lr_trans=2e-3, use_sil=True):
+    """One tracking iteration: sum-L1 with the silhouette mask, pose gradient, Adam on the 7 pose floats,
+    best candidate kept as in splatam.py:1287-1290."""
+    pose = orc.make_pose(ts.pose[:4], ts.pose[4:])
+    lo = params["logit_opacities"].reshape(-1)
+    o = orc.render_full(ocam, params["means3D"], params["log_scales"], None, lo, params["rgb_colors"], ch=5,
+                        flags=_flags(orc), pose=pose)
+    v_render, losses = orc.loss_l1(ocam, 0, o["render"], o["alpha"], gt_rgb, gt_depth, use_sil=use_sil)
+    v_rec = orc.blend_bwd(ocam, 5, o["rec"], o["vals"], o["ranges"], o["alpha"], o["last"], v_render)
+    g = orc.preprocess_bwd(ocam, params["means3D"], params["log_scales"], None, lo, params["rgb_colors"], o["radii"],
+                           o["rec"], v_rec, ch=5, flags=_flags(orc), pose=pose)
+    gp = np.ascontiguousarray(g["pose"], dtype=np.float32)
+    ts.step += 1
+    orc.adam(ts.pose[:4], gp[:4], ts.m[:4], ts.v[:4], lr_rot, eps=1e-8, step=ts.step)
+    orc.adam(ts.pose[4:], gp[4:], ts.m[4:], ts.v[4:], lr_trans, eps=1e-8, step=ts.step)
+    loss = float(np.float32(losses[0]))
+    if loss < ts.best_loss:
+        ts.best_loss = loss
+        ts.best = ts.pose.copy()
+    return loss, gp
+
+
+def ate_rmse(est_t, gt_t):
+    """Horn-aligned translational RMSE (python_ordinary/utils/eval_helpers.py:24-78: align + evaluate_ate).
+    est_t, gt_t: [n,3] camera centres."""
+    est, gt = np.asarray(est_t, np.float64).T, np.asarray(gt_t, np.float64).T
+    mu_e, mu_g = est.mean(1, keepdims=True), gt.mean(1, keepdims=True)
+    Wm = (est - mu_e) @ (gt - mu_g).T
+    U, _, Vt = np.linalg.svd(Wm.T)
+    S = np.eye(3)
+    if np.linalg.det(U) * np.linalg.det(Vt) < 0:
+        S[2, 2] = -1
+    R = U @ S @ Vt
+    tr = mu_g - R @ mu_e
+    err = R @ est + tr - gt
+    return float(np.sqrt((err ** 2).sum(0).mean()))
+
+
+def pose_to_centre(q, t):
+    """camera centre of the w2c pose (q, t): c = -R^T t."""
+    q = np.asarray(q, np.float64)
+    q = q / np.linalg.norm(q)
+    w, x, y, z = q
+    R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+                  [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                  [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
+    return -R.T @ np.asarray(t, np.float64)

@@ -1,0 +1,445 @@
+"""GPU parity of the step kernels around the rasterizer (north_star (5)) and of the fused
+map / track steps, all through the C ABI, against the CPU oracle or the reference's own torch
+expressions.  Bars: bit-exact for index / byte work (compaction, tile lists), <= 1e-3 relative for
+floating-point gradients and optimizer steps, <= 1e-4 for images / losses."""
+import ctypes as C
+import importlib
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def t(a, dtype=torch.float32):
+    return torch.from_numpy(np.ascontiguousarray(a)).to("cuda", dtype)
+
+
+def relerr(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.abs(a - b).max() / (np.abs(b).max() + 1e-30))
+
+
+@pytest.fixture(scope="module")
+def ss(pkg):
+    return importlib.import_module("isogs_slam_cpp_b200.slam_step")
+
+
+def _ptr(x):
+    return None if x is None else C.c_void_p(x.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+# ---------------------------------------------------------------------------------------------
+# fused masked-L1 loss (splatam.py:534-570,747-749)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("mode,use_sil", [(0, True), (0, False), (1, True)])
+def test_loss_kernel_matches_oracle(pkg, orc, mode, use_sil):
+    W, H = 96, 64
+    rng = np.random.RandomState(5)
+    render = rng.rand(5, H, W).astype(np.float32)
+    render[3] *= 3.0
+    render[4] = render[3] ** 2 + 0.01 * rng.rand(H, W).astype(np.float32)
+    alpha = rng.rand(H, W).astype(np.float32)
+    alpha[:, : W // 2] = 0.995 + 0.005 * rng.rand(H, W // 2).astype(np.float32)
+    gt_rgb = rng.rand(3, H, W).astype(np.float32)
+    gt_depth = (3.0 * rng.rand(H, W)).astype(np.float32)
+    gt_depth[rng.rand(H, W) < 0.1] = 0.0  # holes
+    render[3, 3, 5] = np.nan              # the nan mask of splatam.py:549-550
+    ocam = orc.make_camera(W, H, 80.0, 80.0, W / 2, H / 2)
+    gcam = pkg.make_camera(W, H, 80.0, 80.0, W / 2, H / 2)
+    ov, ol = orc.loss_l1(ocam, mode, render, alpha, gt_rgb, gt_depth, 0.5, 1.0, 0.99, use_sil)
+    n_valid = int((gt_depth > 0).sum())
+    inv_nd = 1.0 / n_valid if mode == 1 else 1.0
+    v_render = torch.empty((5, H, W), dtype=torch.float32, device="cuda")
+    losses = torch.zeros((4,), dtype=torch.float32, device="cuda")
+    d_render, d_alpha, d_rgb, d_depth = t(render), t(alpha), t(gt_rgb), t(gt_depth)  # keep alive across the call
+    pkg._lib.check(pkg.lib().isogs_loss_l1_fused(C.byref(gcam), mode, _ptr(d_render), _ptr(d_alpha), _ptr(d_rgb),
+                                                 _ptr(d_depth), 0.5, 1.0, 0.99, int(use_sil), inv_nd,
+                                                 _ptr(v_render), _ptr(losses), _stream()))
+    torch.cuda.synchronize()
+    gl = losses.cpu().numpy()
+    assert int(gl[3]) == n_valid
+    assert abs(gl[0] - ol[0]) <= 1e-4 * max(1.0, abs(ol[0])), (gl, ol)
+    assert abs(gl[1] - ol[1]) <= 1e-4 * max(1.0, abs(ol[1]))
+    assert abs(gl[2] - ol[2]) <= 1e-4 * max(1.0, abs(ol[2]))
+    gv = v_render.cpu().numpy()
+    assert np.all(gv[4] == 0.0), "depth^2 feeds only the detached uncertainty (splatam.py:537-539)"
+    assert np.allclose(gv[:4], ov[:4], rtol=1e-5, atol=1e-9)
+
+
+# ---------------------------------------------------------------------------------------------
+# fused multi-tensor Adam (torch.optim.Adam semantics, splatam.py:402-408)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("eps", [1e-8, 1e-15])
+def test_adam_kernel_matches_torch(pkg, eps):
+    rng = np.random.RandomState(9)
+    shapes = [(1000, 3), (1000, 3), (1000, 1), (1000, 1), (7,)]
+    lrs = [1e-4, 2.5e-3, 0.05, 0.0, 4e-4]  # one lr == 0 group: must stay untouched
+    ps = [rng.randn(*s).astype(np.float32) for s in shapes]
+    tp = [torch.nn.Parameter(torch.from_numpy(p.copy())) for p in ps]
+    opt = torch.optim.Adam([dict(params=[p], lr=lr) for p, lr in zip(tp, lrs)], lr=0.0, eps=eps)
+    gp = [t(p) for p in ps]
+    gm = [torch.zeros_like(p) for p in gp]
+    gv = [torch.zeros_like(p) for p in gp]
+    for step in range(1, 6):
+        grads = [(rng.randn(*s) * 10.0 ** rng.randint(-6, 1)).astype(np.float32) for s in shapes]
+        for p, g in zip(tp, grads):
+            p.grad = torch.from_numpy(g.copy())
+        opt.step()
+        gg = [t(g) for g in grads]
+        arr = (pkg._lib.AdamGroup * len(shapes))()
+        for i in range(len(shapes)):
+            arr[i].param, arr[i].grad = gp[i].data_ptr(), gg[i].data_ptr()
+            arr[i].exp_avg, arr[i].exp_avg_sq = gm[i].data_ptr(), gv[i].data_ptr()
+            arr[i].numel, arr[i].lr = gp[i].numel(), lrs[i]
+        pkg._lib.check(pkg.lib().isogs_adam_fused(arr, len(shapes), 0.9, 0.999, eps, step, _stream()))
+    torch.cuda.synchronize()
+    for i, (a, b) in enumerate(zip(gp, tp)):
+        d = (a.cpu() - b.detach()).abs().max().item()
+        upd = (b.detach() - torch.from_numpy(ps[i])).abs().max().item()
+        assert d <= 1e-3 * upd + 1e-7, (i, d, upd)
+    assert np.array_equal(gp[3].cpu().numpy(), ps[3]), "lr == 0 group must not move"
+
+
+# ---------------------------------------------------------------------------------------------
+# prune mask + order-preserving compaction (slam_external.py:139-188)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("sd", [1, 3])
+def test_prune_and_compact_bit_exact(pkg, orc, sd):
+    N = 70001
+    rng = np.random.RandomState(11)
+    logit_o = (rng.randn(N) * 4.0).astype(np.float32)
+    log_s = (rng.randn(N, sd) * 1.5 - 3.0).astype(np.float32)
+    thr_o, max_scale = 0.005, 0.1 * 3.0
+    keep = torch.empty((N,), dtype=torch.uint8, device="cuda")
+    L = pkg.lib()
+    d_lo, d_ls = t(logit_o), t(log_s)
+    pkg._lib.check(L.isogs_prune_mask(N, _ptr(d_lo), _ptr(d_ls), sd, thr_o, max_scale, _ptr(keep), _stream()))
+    sig = 1.0 / (1.0 + np.exp(-logit_o.astype(np.float64)))
+    big = np.exp(log_s.astype(np.float64)).max(1) > max_scale
+    ref_keep = ~((sig < thr_o) | big)
+    edge = (np.abs(sig - thr_o) < 1e-6) | (np.abs(np.exp(log_s.astype(np.float64)).max(1) - max_scale) < 1e-5)
+    gk = keep.cpu().numpy().astype(bool)
+    assert np.array_equal(gk[~edge], ref_keep[~edge])
+    assert 0.05 < gk.mean() < 0.99
+    # compaction of several row-major tensors of different widths in ONE launch
+    rows_np = [rng.randn(N, w).astype(np.float32) for w in (3, 3, 4, 1, sd, 1)]
+    rows_in = [t(r) for r in rows_np]
+    rows_out = [torch.zeros_like(r) for r in rows_in]
+    arr = (pkg._lib.Rows * len(rows_in))()
+    for i, (a, b) in enumerate(zip(rows_in, rows_out)):
+        arr[i].inp, arr[i].out, arr[i].width = a.data_ptr(), b.data_ptr(), a.shape[1]
+    scan = torch.empty((N,), dtype=torch.int32, device="cuda")
+    sb, _ = pkg._lib.temp_bytes(N, 0)
+    tmp = torch.empty((sb,), dtype=torch.uint8, device="cuda")
+    cnt = torch.zeros((1,), dtype=torch.int32, device="cuda")
+    pkg._lib.check(L.isogs_compact(N, _ptr(keep), arr, len(rows_in), _ptr(scan), _ptr(tmp), sb, _ptr(cnt), _stream()))
+    torch.cuda.synchronize()
+    n_new = int(cnt.item())
+    assert n_new == int(gk.sum())
+    for r_np, r_out in zip(rows_np, rows_out):
+        ref = orc.compact_rows(gk.astype(np.uint8), r_np)
+        assert np.array_equal(r_out[:n_new].cpu().numpy().view(np.uint32), ref.view(np.uint32).reshape(n_new, -1))
+    # edge cases: keep nothing / keep everything
+    for val, expect in ((0, 0), (1, N)):
+        keep.fill_(val)
+        pkg._lib.check(L.isogs_compact(N, _ptr(keep), arr, len(rows_in), _ptr(scan), _ptr(tmp), sb, _ptr(cnt), _stream()))
+        assert int(cnt.item()) == expect
+
+
+# ---------------------------------------------------------------------------------------------
+# sync-free binning == the host-synchronised path, and a too-small buffer is reported, not overrun
+# ---------------------------------------------------------------------------------------------
+def _scene(syn, shape="tiny"):
+    params, frames, K = syn.make_map(shape)
+    W, H, fx, fy, cx, cy = syn.SHAPES[shape][:6]
+    return params, frames, (W, H, fx, fy, cx, cy)
+
+
+def test_tile_bin_async_matches_sync_and_reports_overflow(pkg, syn):
+    params, frames, (W, H, fx, fy, cx, cy) = _scene(syn)
+    cam = pkg.make_camera(W, H, fx, fy, cx, cy)
+    flags = pkg._lib.F_LOG_SCALES | pkg._lib.F_LOGIT_OPAC
+    means, ls = t(params["means3D"]), t(params["log_scales"])
+    lo, rgb = t(params["logit_opacities"].reshape(-1)), t(params["rgb_colors"])
+    rec, radii, tiles, cum, M = pkg.raster.preprocess(cam, means, ls, None, lo, rgb, ch=5, flags=flags)
+    ks, vs, ranges, _, _ = pkg.raster.tile_bin(cam, rec, radii, cum, M)
+    N = means.shape[0]
+    L = pkg.lib()
+    _, sort_b = pkg._lib.temp_bytes(0, M + 100)
+    tmp = torch.empty((sort_b,), dtype=torch.uint8, device="cuda")
+
+    def run(cap):
+        bucket = torch.empty((max(cap, 1),), dtype=torch.int64, device="cuda")
+        ks2 = torch.full((max(cap, 1),), -1, dtype=torch.int64, device="cuda")
+        vs2 = torch.full((max(cap, 1) + 64,), -7, dtype=torch.int32, device="cuda")  # + guard band
+        rg2 = torch.empty((cam.n_tiles + 1,), dtype=torch.int32, device="cuda")
+        tot = torch.zeros((2,), dtype=torch.int32, device="cuda")
+        pkg._lib.check(L.isogs_tile_bin_async(C.byref(cam), N, cap, _ptr(rec), _ptr(radii), _ptr(bucket), _ptr(ks2),
+                                              _ptr(vs2), _ptr(rg2), _ptr(tot), _ptr(tmp), sort_b, _stream()))
+        torch.cuda.synchronize()
+        return ks2, vs2, rg2, tot.cpu().numpy()
+
+    ks2, vs2, rg2, tot = run(M + 100)
+    assert tot[0] == M and tot[1] == 0
+    assert torch.equal(rg2, ranges)
+    assert torch.equal(vs2[:M], vs) and torch.equal(ks2[:M], ks), "sorted lists must be bit-identical"
+    # capacity below the need: flagged, ranges clamped, nothing written past the capacity
+    cap = M // 2
+    ks3, vs3, rg3, tot = run(cap)
+    assert tot[0] == M and tot[1] == 1
+    assert int(rg3.max()) == cap and int(rg3[-1]) == cap
+    assert torch.all(vs3[cap:] == -7), "write past the capacity"
+    full = ranges.cpu().numpy()
+    whole = np.nonzero(full[1:] <= cap)[0]  # tiles that fit completely keep their exact lists
+    t0 = int(whole[-1])
+    assert torch.equal(vs3[: full[t0 + 1]], vs[: full[t0 + 1]])
+
+
+# ---------------------------------------------------------------------------------------------
+# silhouette-driven densification (splatam.py:799-841,298-348,763-796)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("sd", [1, 3])
+def test_backproject_append_matches_reference_rule(pkg, syn, sd):
+    W, H, fx, fy, cx, cy = syn.SHAPES["tiny"][:6]
+    traj = syn.trajectory(6, step=3.0)
+    color, depth, _ = syn.render_frame("tiny", traj[5], seed=5)
+    rng = np.random.RandomState(3)
+    alpha = rng.rand(H, W).astype(np.float32)
+    render_depth = (depth[0] + rng.randn(H, W).astype(np.float32) * 0.2).astype(np.float32)
+    sil_thres, err_thres = 0.5, 0.3
+    q, tr = syn.w2c_to_pose(traj[5])
+    cam, pose = pkg.make_camera(W, H, fx, fy, cx, cy), pkg.make_pose(q, tr)
+    cap, n0 = W * H + 10, 7
+    means = torch.zeros((cap, 3), device="cuda"); rgb = torch.zeros((cap, 3), device="cuda")
+    quats = torch.zeros((cap, 4), device="cuda"); lo = torch.full((cap,), 9.0, device="cuda")
+    ls = torch.zeros((cap, sd), device="cuda")
+    cnt = torch.tensor([n0], dtype=torch.int32, device="cuda")
+    scan = torch.empty((2 * W * H,), dtype=torch.int32, device="cuda")
+    sb, _ = pkg._lib.temp_bytes(W * H, 0)
+    tmp = torch.empty((sb,), dtype=torch.uint8, device="cuda")
+    d_color, d_depth, d_rd, d_alpha = t(color), t(depth[0]), t(render_depth), t(alpha)
+    pkg._lib.check(pkg.lib().isogs_backproject_append(
+        C.byref(cam), C.byref(pose), _ptr(d_color), _ptr(d_depth), _ptr(d_rd), _ptr(d_alpha),
+        sil_thres, err_thres, _ptr(means), _ptr(rgb), _ptr(quats), _ptr(lo), _ptr(ls), sd, 0.01, 1234, cap,
+        _ptr(scan), _ptr(tmp), sb, _ptr(cnt), _stream()))
+    torch.cuda.synchronize()
+    gd = depth[0]
+    err = np.abs(gd - render_depth) * (gd > 0)
+    sel = ((alpha < sil_thres) | ((render_depth > gd) & (err > err_thres))) & (gd > 0)  # splatam.py:807-827
+    n_new = int(sel.sum())
+    assert int(cnt.item()) == n0 + n_new and n_new > 100
+    ys, xs = np.nonzero(sel)  # row-major == pixel order
+    z = gd[ys, xs].astype(np.float64)
+    pc = np.stack([(xs - cx) / fx * z, (ys - cy) / fy * z, z], -1)
+    c2w = np.linalg.inv(traj[5].astype(np.float64))
+    pw = pc @ c2w[:3, :3].T + c2w[:3, 3]
+    gm = means[n0:n0 + n_new].cpu().numpy()
+    assert np.abs(gm - pw).max() <= 1e-4
+    assert np.allclose(rgb[n0:n0 + n_new].cpu().numpy(), color[:, ys, xs].T)
+    assert torch.all(lo[n0:n0 + n_new] == 0) and torch.all(lo[:n0] == 9.0)
+    assert torch.all(quats[n0:n0 + n_new, 0] == 1) and torch.all(quats[n0:n0 + n_new, 1:] == 0)
+    ref_ls = np.log(z / ((fx + fy) / 2.0))
+    gls = ls[n0:n0 + n_new].cpu().numpy()
+    if sd == 1:
+        assert np.abs(gls[:, 0] - ref_ls).max() <= 1e-5
+    else:  # IsoGS symmetry-breaking jitter, N(0, 0.01) per axis (splatam.py:771-777)
+        noise = gls - ref_ls[:, None]
+        assert abs(noise.mean()) < 2e-3 and 0.008 < noise.std() < 0.012
+        assert np.abs(noise[:, 0] - noise[:, 1]).max() > 1e-3
+
+
+# ---------------------------------------------------------------------------------------------
+# the drop-in plugin API: GaussianRasterizer(raster_settings)(...) forward + autograd backward
+# ---------------------------------------------------------------------------------------------
+def _setup_camera(w, h, k, w2c, near=0.01, far=100.0):
+    """Restatement of python_ordinary/utils/recon_helpers.py:4-27 (setup_camera)."""
+    from diff_gaussian_rasterization import GaussianRasterizationSettings as Camera
+    fx, fy, cx, cy = k[0][0], k[1][1], k[0][2], k[1][2]
+    w2c = torch.tensor(w2c).cuda().float()
+    cam_center = torch.inverse(w2c)[:3, 3]
+    w2c = w2c.unsqueeze(0).transpose(1, 2)
+    opengl_proj = torch.tensor([[2 * fx / w, 0.0, -(w - 2 * cx) / w, 0.0],
+                                [0.0, 2 * fy / h, -(h - 2 * cy) / h, 0.0],
+                                [0.0, 0.0, far / (far - near), -(far * near) / (far - near)],
+                                [0.0, 0.0, 1.0, 0.0]]).cuda().float().unsqueeze(0).transpose(1, 2)
+    full_proj = w2c.bmm(opengl_proj)
+    return Camera(image_height=h, image_width=w, tanfovx=w / (2 * fx), tanfovy=h / (2 * fy),
+                  bg=torch.tensor([0, 0, 0], dtype=torch.float32, device="cuda"), scale_modifier=1.0,
+                  viewmatrix=w2c, projmatrix=full_proj, sh_degree=0, campos=cam_center, prefiltered=False)
+
+
+@pytest.mark.parametrize("iso", [True, False])
+def test_dropin_rasterizer_forward_backward(pkg, orc, syn, iso):
+    from diff_gaussian_rasterization import GaussianRasterizer as Renderer
+    W, H, f = 144, 96, 120.0
+    cx, cy = 71.5, 47.5
+    rng = np.random.RandomState(21)
+    n = 3000
+    z = 1.0 + 3.0 * rng.rand(n)
+    means = np.stack([(rng.rand(n) * W - cx) / f * z, (rng.rand(n) * H - cy) / f * z, z], -1).astype(np.float32)
+    s = (z / f * (0.6 + 2.0 * rng.rand(n))).astype(np.float32)
+    scales = s[:, None] if iso else (s[:, None] * (0.5 + rng.rand(n, 3))).astype(np.float32)
+    quats = rng.randn(n, 4).astype(np.float32)
+    quats /= np.linalg.norm(quats, axis=1, keepdims=True)
+    opac = (0.05 + 0.9 * rng.rand(n, 1)).astype(np.float32)
+    cols = rng.rand(n, 3).astype(np.float32)
+    w2c = syn.trajectory(4, step=4.0)[3]
+    K = [[f, 0, cx], [0, f, cy], [0, 0, 1]]
+    cam = _setup_camera(W, H, K, w2c)
+    tm = t(means).requires_grad_(True); tc = t(cols).requires_grad_(True); to = t(opac).requires_grad_(True)
+    tsc = t(scales).requires_grad_(True)
+    tq = t(quats).requires_grad_(not iso)
+    m2d = torch.zeros_like(tm, requires_grad=True) + 0
+    m2d.retain_grad()  # splatam.py:528
+    im, radius, depth = Renderer(raster_settings=cam)(means3D=tm, means2D=m2d, colors_precomp=tc,
+                                                      rotations=None if iso else tq, opacities=to, scales=tsc)
+    assert im.shape == (3, H, W) and depth.shape == (1, H, W) and radius.shape == (n,) and radius.dtype == torch.int32
+    ocam = orc.make_camera(W, H, f, f, cx, cy, w2c)
+    o = orc.render_full(ocam, means, scales, None if iso else quats, opac.reshape(-1), cols, ch=4)
+    assert np.abs(im.detach().cpu().numpy() - o["render"][:3]).max() <= 1e-4
+    assert np.abs(depth.detach().cpu().numpy()[0] - o["render"][3]).max() <= 1e-4 * max(1.0, o["render"][3].max())
+    assert np.array_equal(radius.cpu().numpy(), o["radii"].max(1))
+    wts = rng.randn(4, H, W).astype(np.float32)
+    loss = (im * t(wts[:3])).sum() + (depth * t(wts[3:4])).sum()
+    loss.backward()
+    ov = orc.blend_bwd(ocam, 4, o["rec"], o["vals"], o["ranges"], o["alpha"], o["last"], wts)
+    og = orc.preprocess_bwd(ocam, means, scales, None if iso else quats, opac.reshape(-1), cols, o["radii"], o["rec"],
+                            ov, ch=4)
+    assert relerr(tm.grad.cpu().numpy(), og["means"]) <= 1e-3
+    assert relerr(tc.grad.cpu().numpy(), og["colors"]) <= 1e-3
+    assert relerr(to.grad.cpu().numpy().reshape(-1), og["opacities"]) <= 1e-3
+    assert relerr(tsc.grad.cpu().numpy().reshape(og["scales"].shape), og["scales"]) <= 1e-3
+    if not iso:
+        assert relerr(tq.grad.cpu().numpy(), og["quats"]) <= 1e-3
+    g2 = m2d.grad.cpu().numpy()
+    assert g2.shape == (n, 3) and np.abs(g2[:, :2]).max() > 0 and np.all(g2[:, 2] == 0)
+    # errors surface as RuntimeError (gsplat CHECK_INPUT, Common.h:15-17): CPU tensors are rejected
+    with pytest.raises(RuntimeError):
+        Renderer(raster_settings=cam)(means3D=tm.cpu(), means2D=None, colors_precomp=tc.cpu(), rotations=None,
+                                      opacities=to.cpu(), scales=tsc.cpu()[:, :1])
+
+
+# ---------------------------------------------------------------------------------------------
+# fused mapping / tracking steps vs the oracle executing the same iteration
+# ---------------------------------------------------------------------------------------------
+def _frame(syn, shape, w2c, seed):
+    c, d, _ = syn.render_frame(shape, w2c, seed=seed)
+    return np.ascontiguousarray(c), np.ascontiguousarray(d[0])
+
+
+def test_map_step_matches_oracle(pkg, orc, syn, ss):
+    import oracle_slam as osl
+    params, frames, (W, H, fx, fy, cx, cy) = _scene(syn)
+    traj = syn.trajectory(8, step=3.0)
+    ocam, gcam = orc.make_camera(W, H, fx, fy, cx, cy), pkg.make_camera(W, H, fx, fy, cx, cy)
+    st = osl.new_state(params)
+    gmap = ss.GaussianMap(params, device="cuda")
+    ws = ss.StepWorkspace(gcam, gmap.count, torch.device("cuda"))
+    for it in range(3):
+        k = 2 + it
+        rgb, depth = _frame(syn, "tiny", traj[k], k)
+        q, tr = syn.w2c_to_pose(traj[k])
+        g_ref = {}
+        p_before = {kk: v.copy() for kk, v in st["p"].items()}
+        lo = osl.map_iteration(orc, ocam, st, q, tr, rgb, depth, grads_out=g_ref)
+        inv_nd = 1.0 / max(1, int((depth > 0).sum()))
+        losses = ss.map_step(ws, gmap, pkg.make_pose(q, tr), t(rgb), t(depth), inv_nd)
+        torch.cuda.synchronize()
+        assert abs(float(losses[0]) - lo) <= 1e-4 * max(1.0, abs(lo))
+        assert not ws.check_overflow(wait=True)
+        for name in ("means3D", "rgb_colors", "logit_opacities", "log_scales"):
+            assert relerr(gmap.g[name].cpu().numpy().reshape(-1), g_ref[name].reshape(-1)) <= 1e-3, (it, name)
+            upd = np.abs(st["p"][name] - p_before[name]).max()
+            d = np.abs(gmap.view(name).cpu().numpy().reshape(st["p"][name].shape) - st["p"][name]).max()
+            # Adam normalises every element's step to ~lr, so compare against the size of a step
+            assert d <= 0.02 * upd + 1e-7, (it, name, d, upd)
+
+
+def test_track_step_matches_oracle(pkg, orc, syn, ss):
+    import oracle_slam as osl
+    params, frames, (W, H, fx, fy, cx, cy) = _scene(syn)
+    traj = syn.trajectory(8, step=3.0)
+    ocam, gcam = orc.make_camera(W, H, fx, fy, cx, cy), pkg.make_camera(W, H, fx, fy, cx, cy)
+    rgb, depth = _frame(syn, "tiny", traj[3], 3)
+    q0, t0 = syn.w2c_to_pose(traj[2])  # start from the previous frame's pose
+    ts = osl.TrackState(q0, t0)
+    gmap = ss.GaussianMap(params, device="cuda")
+    ws = ss.StepWorkspace(gcam, gmap.count, torch.device("cuda"))
+    ps = ss.PoseState(q0, t0, "cuda")
+    grgb, gdepth = t(rgb), t(depth)
+    for it in range(5):
+        pose_before = ts.pose.copy()
+        lo, gp = osl.track_iteration(orc, ocam, params, ts, rgb, depth)
+        losses = ss.track_step(ws, gmap, ps, grgb, gdepth)
+        torch.cuda.synchronize()
+        assert abs(float(losses[0]) - lo) <= 2e-4 * abs(lo), (it, float(losses[0]), lo)
+        assert relerr(ws.v_pose.cpu().numpy(), gp) <= 1e-3, (it, ws.v_pose.cpu().numpy(), gp)
+        step = np.abs(ts.pose - pose_before).max()
+        assert np.abs(ps.pose.cpu().numpy() - ts.pose).max() <= 0.02 * step + 1e-7
+    bq, bt = ps.best_pose()
+    assert np.abs(np.concatenate([bq, bt]) - ts.best).max() <= 1e-5
+    assert abs(float(ps.best[7]) - ts.best_loss) <= 2e-4 * ts.best_loss
+    # Gaussian parameters must be untouched by tracking
+    assert np.array_equal(gmap.view("means3D").cpu().numpy(), params["means3D"])
+
+
+def test_init_camera_pose(ss):
+    q1, t1 = np.array([0.99, 0.05, 0.02, 0.01], np.float32), np.array([0.1, 0.0, 0.2], np.float32)
+    q2, t2 = np.array([1.0, 0.0, 0.0, 0.0], np.float32), np.array([0.0, 0.0, 0.1], np.float32)
+    q, tr = ss.init_camera_pose((q1, t1), (q2, t2))
+    n1 = torch.nn.functional.normalize(torch.from_numpy(q1), dim=0)
+    n2 = torch.nn.functional.normalize(torch.from_numpy(q2), dim=0)
+    ref = torch.nn.functional.normalize(n1 + (n1 - n2), dim=0).numpy()  # splatam.py:848-851
+    assert np.allclose(q, ref, atol=1e-6) and np.allclose(tr, t1 + (t1 - t2))
+    q, tr = ss.init_camera_pose((q1, t1), None)
+    assert np.array_equal(q, q1) and np.array_equal(tr, t1)
+
+
+# ---------------------------------------------------------------------------------------------
+# ATE after a 50-frame run: ours vs the oracle running the same schedule (north_star: within 1 mm)
+# ---------------------------------------------------------------------------------------------
+def test_ate_50_frames_within_1mm_of_oracle(pkg, orc, syn, ss):
+    import oracle_slam as osl
+    n_frames, iters = 50, 40
+    params, frames0, (W, H, fx, fy, cx, cy) = _scene(syn)
+    traj = syn.trajectory(n_frames, step=1.0)
+    ocam, gcam = orc.make_camera(W, H, fx, fy, cx, cy), pkg.make_camera(W, H, fx, fy, cx, cy)
+    gmap = ss.GaussianMap(params, device="cuda")
+    ws = ss.StepWorkspace(gcam, gmap.count, torch.device("cuda"))
+    ident = (np.array([1, 0, 0, 0], np.float32), np.zeros(3, np.float32))
+    ours, ref, gt = [ident], [ident], [np.zeros(3)]
+    for f in range(1, n_frames):
+        rgb, depth = _frame(syn, "tiny", traj[f], f)
+        grgb, gdepth = t(rgb), t(depth)
+        gt.append(-traj[f][:3, :3].T.astype(np.float64) @ traj[f][:3, 3].astype(np.float64))
+        # ours
+        q, tr = ss.init_camera_pose(ours[-1], ours[-2] if f > 1 else None)
+        ps = ss.PoseState(q, tr, "cuda")
+        for _ in range(iters):
+            ss.track_step(ws, gmap, ps, grgb, gdepth)
+        ours.append(ps.best_pose())
+        # oracle, same schedule
+        q, tr = ss.init_camera_pose(ref[-1], ref[-2] if f > 1 else None)
+        ts = osl.TrackState(q, tr)
+        for _ in range(iters):
+            osl.track_iteration(orc, ocam, params, ts, rgb, depth)
+        ref.append((ts.best[:4].copy(), ts.best[4:].copy()))
+    c_ours = np.array([osl.pose_to_centre(*p) for p in ours])
+    c_ref = np.array([osl.pose_to_centre(*p) for p in ref])
+    gt = np.array(gt)
+    ate_ours, ate_ref = osl.ate_rmse(c_ours, gt), osl.ate_rmse(c_ref, gt)
+    between = float(np.sqrt(((c_ours - c_ref) ** 2).sum(1).mean()))
+    print(f"ATE ours {ate_ours * 1e3:.3f} mm, oracle {ate_ref * 1e3:.3f} mm, ours-vs-oracle rmse {between * 1e3:.4f} mm")
+    # the north_star bar: ATE after the 50-frame run within 1 mm of the oracle's
+    assert abs(ate_ours - ate_ref) <= 1e-3, "ATE differs from the oracle run by more than 1 mm"
+    # frame-by-frame the two runs are NOT expected to be identical: Adam turns every gradient component
+    # into a step of ~lr (2 mm for the translation), and the argmin of the best-candidate rule flips on
+    # ulp-level loss differences (atomic summation order), so 2000 iterations decorrelate at the mm level
+    assert between <= 1e-2, "trajectories differ by more than 1 cm"
+    assert ate_ours <= 0.05, "tracking lost the camera"
