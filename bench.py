@@ -144,17 +144,15 @@ def run_ours(args):
              for _ in range(2)]
     e2e_state = dict(prefetched=-1, last_loss=0.0)
 
-    def allreduce(flat):
-        dist.all_reduce(flat)          # sum; averaged by scaling the learning signal below
-        flat.mul_(1.0 / world)
-    ar = allreduce if world > 1 else None
+    dp = importlib.import_module("isogs_slam_cpp_b200.dp")
+    ar = dp.allreduce_mean_ if world > 1 else None   # ONE all-reduce of the flat gradient buffer per iteration
 
     def step_resident(i, marks=None):
-        k = kfs[(i * world + rank) % WINDOW]
+        k = kfs[dp.keyframe_for(i, rank, world, WINDOW)]
         return ss.map_step(ws, gmap, k["pose"], k["rgb_d"], k["depth_d"], k["inv_nd"], allreduce=ar, marks=marks)
 
     def e2e_prefetch(i):
-        s, k = slots[i % 2], kfs[(i * world + rank) % WINDOW]
+        s, k = slots[i % 2], kfs[dp.keyframe_for(i, rank, world, WINDOW)]
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_event(s["free"])          # the step that last used this slot has finished
             s["rgb"].copy_(k["rgb_h"], non_blocking=True)
@@ -167,7 +165,7 @@ def run_ours(args):
         if e2e_state["prefetched"] < i:
             e2e_prefetch(i)
         e2e_prefetch(i + 1)
-        s, k = slots[i % 2], kfs[(i * world + rank) % WINDOW]
+        s, k = slots[i % 2], kfs[dp.keyframe_for(i, rank, world, WINDOW)]
         cur.wait_event(s["ready"])
         losses = ss.map_step(ws, gmap, k["pose"], s["rgb"], s["depth"], k["inv_nd"], allreduce=ar)
         s["free"].record(cur)
