@@ -279,6 +279,126 @@ tile_sort_kernel(int lo, int hi, const int32_t* __restrict__ ranges, uint64_t* _
     }
 }
 
+// ---- register / shuffle bitonic sort for tiles with <= 2048 intersections (the common case) --------
+// Thread t of 256 holds E consecutive elements (index t*E + r) in registers.  The normalised bitonic
+// network (all comparators ascending; slots >= n hold +inf = ~0, which no (depth, id) pair equals)
+// then needs shared memory only for comparator distances that cross a warp: 6 of its 55 steps at
+// 1024 elements; distances below E are register moves and the rest are warp shuffles.
+__device__ __forceinline__ uint64_t shfl_xor_u64(uint64_t v, int mask) {
+    const uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)v, mask);
+    const uint32_t hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(v >> 32), mask);
+    return ((uint64_t)hi << 32) | lo;
+}
+
+template <int E>
+__device__ __forceinline__ void reg_bitonic_sort(uint64_t (&v)[E], uint64_t* s_x, int tid) {
+    constexpr int N = 256 * E;
+#pragma unroll
+    for (int k = 2; k <= N; k <<= 1) {
+        // flip: element i pairs with i ^ (k - 1); the lower index keeps the minimum
+        if (k <= E) {
+#pragma unroll
+            for (int r = 0; r < E; ++r) {
+                const int pr = r ^ (k - 1);
+                if (r < pr) {
+                    const uint64_t a = v[r], b = v[pr];
+                    v[r] = a < b ? a : b;
+                    v[pr] = a < b ? b : a;
+                }
+            }
+        } else {
+            const int tmask = k / E - 1;             // partner thread = tid ^ tmask, partner slot = E-1-r
+            const bool low = (tid & (k / (2 * E))) == 0;
+            if (k <= 32 * E) {
+                uint64_t o[E];
+#pragma unroll
+                for (int r = 0; r < E; ++r) o[r] = shfl_xor_u64(v[E - 1 - r], tmask);
+#pragma unroll
+                for (int r = 0; r < E; ++r) v[r] = low ? (v[r] < o[r] ? v[r] : o[r]) : (v[r] < o[r] ? o[r] : v[r]);
+            } else {
+                __syncthreads();
+#pragma unroll
+                for (int r = 0; r < E; ++r) s_x[r * 256 + tid] = v[r];
+                __syncthreads();
+#pragma unroll
+                for (int r = 0; r < E; ++r) {
+                    const uint64_t o = s_x[(E - 1 - r) * 256 + (tid ^ tmask)];
+                    v[r] = low ? (v[r] < o ? v[r] : o) : (v[r] < o ? o : v[r]);
+                }
+            }
+        }
+        // halving steps: element i pairs with i + j (bit j of i clear)
+#pragma unroll
+        for (int j = k >> 2; j >= 1; j >>= 1) {
+            if (j < E) {
+#pragma unroll
+                for (int r = 0; r < E; ++r)
+                    if ((r & j) == 0) {
+                        const uint64_t a = v[r], b = v[r + j];
+                        v[r] = a < b ? a : b;
+                        v[r + j] = a < b ? b : a;
+                    }
+            } else {
+                const int tm = j / E;
+                const bool low = (tid & tm) == 0;
+                if (j < 32 * E) {
+#pragma unroll
+                    for (int r = 0; r < E; ++r) {
+                        const uint64_t o = shfl_xor_u64(v[r], tm);
+                        v[r] = low ? (v[r] < o ? v[r] : o) : (v[r] < o ? o : v[r]);
+                    }
+                } else {
+                    __syncthreads();
+#pragma unroll
+                    for (int r = 0; r < E; ++r) s_x[r * 256 + tid] = v[r];
+                    __syncthreads();
+#pragma unroll
+                    for (int r = 0; r < E; ++r) {
+                        const uint64_t o = s_x[r * 256 + (tid ^ tm)];
+                        v[r] = low ? (v[r] < o ? v[r] : o) : (v[r] < o ? o : v[r]);
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <int E>
+__device__ __forceinline__ void tile_sort_regs(int tile, int start, int n, const uint64_t* __restrict__ seg,
+                                               uint64_t* s_x, uint64_t* __restrict__ keys_sorted,
+                                               int32_t* __restrict__ vals_sorted, int tid) {
+    uint64_t v[E];
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const int i = tid * E + r;
+        v[r] = i < n ? seg[i] : ~0ull;
+    }
+    reg_bitonic_sort<E>(v, s_x, tid);
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const int i = tid * E + r;
+        if (i < n) {
+            vals_sorted[start + i] = (int32_t)(uint32_t)v[r];
+            if (keys_sorted) keys_sorted[start + i] = ((uint64_t)tile << 32) | (v[r] >> 32);
+        }
+    }
+}
+
+constexpr int SORT_REG_MAX = 2048;
+__global__ void __launch_bounds__(256)
+tile_sort_reg_kernel(const int32_t* __restrict__ ranges, const uint64_t* __restrict__ bucket,
+                     uint64_t* __restrict__ keys_sorted, int32_t* __restrict__ vals_sorted) {
+    __shared__ uint64_t s_x[SORT_REG_MAX];
+    const int tile = blockIdx.x, tid = threadIdx.x;
+    const int start = ranges[tile], n = ranges[tile + 1] - start;
+    if (n <= 0 || n > SORT_REG_MAX) return;
+    const uint64_t* seg = bucket + start;
+    if (n <= 256) tile_sort_regs<1>(tile, start, n, seg, s_x, keys_sorted, vals_sorted, tid);
+    else if (n <= 512) tile_sort_regs<2>(tile, start, n, seg, s_x, keys_sorted, vals_sorted, tid);
+    else if (n <= 1024) tile_sort_regs<4>(tile, start, n, seg, s_x, keys_sorted, vals_sorted, tid);
+    else tile_sort_regs<8>(tile, start, n, seg, s_x, keys_sorted, vals_sorted, tid);
+}
+
 inline int sort_end_bit(int n_tiles) {
     int bits = 0;
     while ((1ll << bits) <= (long long)n_tiles) ++bits; // floor(log2(n))+1, IntersectTile.cu:151
@@ -330,8 +450,8 @@ static int counting_bin(int tw, int th, int64_t N, int32_t capacity, bool clamp,
                                         SORT_SMEM_MAX * (int)sizeof(uint64_t)));
         attr_set = true;
     }
-    tile_sort_kernel<<<n_tiles, 256, SORT_SMEM_SMALL * sizeof(uint64_t), stream>>>(
-        0, SORT_SMEM_SMALL, tile_ranges, bucket, keys_sorted, vals_sorted);
+    static_assert(SORT_REG_MAX == SORT_SMEM_SMALL, "the two sort kernels split the tiles at the same length");
+    tile_sort_reg_kernel<<<n_tiles, 256, 0, stream>>>(tile_ranges, bucket, keys_sorted, vals_sorted);
     tile_sort_kernel<<<n_tiles, 256, SORT_SMEM_MAX * sizeof(uint64_t), stream>>>(
         SORT_SMEM_SMALL, 0x7fffffff, tile_ranges, bucket, keys_sorted, vals_sorted);
     ISOGS_CUDA(cudaGetLastError());
