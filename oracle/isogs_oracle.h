@@ -22,8 +22,10 @@
  * Parity status: projection / keys / ranges are pinned against the
  * reference's own CPU-runnable transcription (gsplat/cuda/_torch_impl.py,
  * see oracle/pin_against_gsplat.py and tests/golden/).  The blend has no
- * CPU-runnable reference implementation in the tree ("parity unpinned" for the
- * blend forward/backward; pinned by finite differences only).
+ * CPU-runnable reference implementation in the tree: this restatement of it is
+ * verified by finite differences, and the CUDA kernels it checks are
+ * additionally compared on the GPU with the reference's own CUDA kernels
+ * (oracle/build_ref.sh -> oracle/_ref/gsplat_ref.so, tests/test_gpu_vs_gsplat.py).
  */
 #pragma once
 #include <stdint.h>
