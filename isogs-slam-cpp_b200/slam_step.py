@@ -75,6 +75,23 @@ class GaussianMap:
         self.count = int(n)
         self._carve()
 
+    def reserve(self, n):
+        """Capacity-doubling pool (cpp/include/core/gaussian_model.hpp:18-124 pre-allocates 20 M slots; here
+        the pool grows geometrically and keeps parameters + Adam moments; one copy per growth, not per frame
+        as the reference's torch.cat does, splatam.py:832-833)."""
+        if n <= self.capacity:
+            return
+        cap = max(int(n), int(self.capacity * 1.5) + 1024)
+        for d in (self.p, self.m, self.v):
+            for k in PARAM_ORDER:
+                buf = torch.zeros((cap, self.widths[k]), dtype=torch.float32, device=self.device)
+                buf[:self.count] = d[k][:self.count]
+                d[k] = buf
+        self.capacity = cap
+        total = sum(self.widths[k] for k in self.grad_names) * cap
+        self.grad_flat = torch.zeros((total,), dtype=torch.float32, device=self.device)
+        self._carve()
+
 
 class StepWorkspace:
     """Per-(resolution, N) scratch that is reused across iterations (no per-step allocation)."""
@@ -134,6 +151,23 @@ class StepWorkspace:
                           "The affected step rendered truncated tile lists.")
             return True
         return False
+
+    def ensure_gaussians(self, n):
+        """Grow the per-Gaussian scratch when the map has grown (densification)."""
+        if n <= self.n_cap:
+            return
+        n_cap = int(n * 1.25) + 1024
+        f32, i32, device = torch.float32, torch.int32, self.device
+        self.rec = torch.empty((n_cap, REC), dtype=f32, device=device)
+        self.v_rec = torch.empty((n_cap, REC), dtype=f32, device=device)
+        self.radii = torch.empty((n_cap, 2), dtype=i32, device=device)
+        self.tiles = torch.empty((n_cap,), dtype=i32, device=device)
+        self.cum = torch.empty((n_cap,), dtype=i32, device=device)
+        self.n_cap = n_cap
+        self.scan_b, _ = _lib.temp_bytes(n_cap, 0)
+        self.scan_tmp = torch.empty((self.scan_b,), dtype=torch.uint8, device=device)
+        if self.isect_cap < 3 * n_cap:
+            self._grow_isects(3 * n_cap)
 
     def _grow_isects(self, cap):
         dev = self.device
@@ -231,6 +265,78 @@ def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, all
     adam_gaussians(gmap, lrs)
     _mark(marks, "adam")
     return ws.losses
+
+
+def _pose_of(pose):
+    return pose if isinstance(pose, _lib.Pose) else _lib.make_pose(pose[0], pose[1])
+
+
+def add_new_gaussians(ws, gmap, pose, gt_rgb, gt_depth, sil_thres=0.5, noise_std=0.01, seed=0):
+    """Silhouette-driven densification of one frame (add_new_gaussians, splatam.py:799-841): silhouette +
+    depth render at `pose` (no gradient), non-presence mask `sil < sil_thres or (render_d > gt_d and
+    |err| > 50 median(err))`, back-projection of the masked valid-depth pixels, append to the pool.
+    Appended Gaussians start with zero Adam moments.  Two host reads per mapped frame (the median
+    threshold and the new count).  Returns the number of Gaussians added."""
+    pose = _pose_of(pose)
+    cam = ws.cam
+    P = cam.width * cam.height
+    ws.ensure_gaussians(gmap.count)
+    render_forward(ws, gmap, pose=pose)
+    err = (gt_depth - ws.render[3]).abs() * (gt_depth > 0)                    # splatam.py:811
+    thr = 50.0 * float(err.median())                                           # :812 (one host read)
+    gmap.reserve(gmap.count + P)
+    count = torch.tensor([gmap.count], dtype=torch.int32, device=gmap.device)
+    scan = torch.empty((2 * P,), dtype=torch.int32, device=gmap.device)
+    sb, _ = _lib.temp_bytes(P, 0)
+    tmp = torch.empty((sb,), dtype=torch.uint8, device=gmap.device)
+    quats = gmap.p["unnorm_rotations"]
+    check(lib().isogs_backproject_append(C.byref(cam), C.byref(pose), _ptr(gt_rgb), _ptr(gt_depth), _ptr(ws.render[3]),
+                                         _ptr(ws.alpha), sil_thres, thr, _ptr(gmap.p["means3D"]),
+                                         _ptr(gmap.p["rgb_colors"]), _ptr(quats), _ptr(gmap.p["logit_opacities"]),
+                                         _ptr(gmap.p["log_scales"]), gmap.sd, noise_std, seed, gmap.capacity, _ptr(scan),
+                                         _ptr(tmp), sb, _ptr(count), _stream()))
+    new_count = int(count.item())
+    added = new_count - gmap.count
+    if added > 0:
+        for k in PARAM_ORDER:
+            gmap.m[k][gmap.count:new_count].zero_()
+            gmap.v[k][gmap.count:new_count].zero_()
+        gmap.set_count(new_count)
+        ws.ensure_gaussians(new_count)
+    return added
+
+
+def prune_gaussians(ws, gmap, opac_thres=0.005, max_scale=float("inf")):
+    """prune_gaussians + remove_points (slam_external.py:139-188): drop `sigmoid(o) < opac_thres or
+    max exp(s) > max_scale`; ONE order-preserving compaction of the 5 parameter tensors and their 10 Adam
+    moments.  Returns the number removed (one host read)."""
+    N = gmap.count
+    if N == 0:
+        return 0
+    dev = gmap.device
+    keep = torch.empty((N,), dtype=torch.uint8, device=dev)
+    L, st = lib(), _stream()
+    check(L.isogs_prune_mask(N, _ptr(gmap.p["logit_opacities"]), _ptr(gmap.p["log_scales"]), gmap.sd, opac_thres,
+                             max_scale, _ptr(keep), st))
+    rows_in, rows_out = [], []
+    for d in (gmap.p, gmap.m, gmap.v):
+        for k in PARAM_ORDER:
+            rows_in.append((d, k))
+            rows_out.append(torch.zeros_like(d[k]))
+    arr = (_lib.Rows * len(rows_in))()
+    for i, ((d, k), out) in enumerate(zip(rows_in, rows_out)):
+        arr[i].inp, arr[i].out, arr[i].width = d[k].data_ptr(), out.data_ptr(), gmap.widths[k]
+    scan = torch.empty((N,), dtype=torch.int32, device=dev)
+    sb, _ = _lib.temp_bytes(N, 0)
+    tmp = torch.empty((sb,), dtype=torch.uint8, device=dev)
+    cnt = torch.zeros((1,), dtype=torch.int32, device=dev)
+    check(L.isogs_compact(N, _ptr(keep), arr, len(rows_in), _ptr(scan), _ptr(tmp), sb, _ptr(cnt), st))
+    new_count = int(cnt.item())
+    if new_count != N:
+        for (d, k), out in zip(rows_in, rows_out):
+            d[k] = out
+        gmap.set_count(new_count)
+    return N - new_count
 
 
 class PoseState:

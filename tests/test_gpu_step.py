@@ -443,3 +443,21 @@ def test_ate_50_frames_within_1mm_of_oracle(pkg, orc, syn, ss):
     # ulp-level loss differences (atomic summation order), so 2000 iterations decorrelate at the mm level
     assert between <= 1e-2, "trajectories differ by more than 1 cm"
     assert ate_ours <= 0.05, "tracking lost the camera"
+
+
+# ---------------------------------------------------------------------------------------------
+# the whole loop: tracking + densification + mapping + pruning on a short synthetic sequence
+# ---------------------------------------------------------------------------------------------
+def test_synthetic_slam_loop_runs_and_improves(pkg, syn, ss):
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("run_synthetic_slam", os.path.join(root, "scripts", "run_synthetic_slam.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    out = mod.run(shape="tiny", frames=13, track_iters=20, map_iters=30, map_every=3, kf_every=3)
+    print(out)
+    assert out["added"] > 0, "moving the camera must reveal unseen pixels"
+    assert out["gaussians"] > 18000
+    assert out["ate_rmse_mm"] < 50.0
+    assert out["psnr_last"] > 17.0
