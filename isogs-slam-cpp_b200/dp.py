@@ -23,8 +23,11 @@ def allreduce_mean_(flat, group=None):
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     if world == 1:
         return flat
-    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
-    flat.mul_(1.0 / world)
+    if dist.get_backend(group) == "nccl":
+        dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=group)   # ncclAvg: the 1/world scaling rides in the collective
+    else:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+        flat.mul_(1.0 / world)
     return flat
 
 
