@@ -64,6 +64,8 @@ int isogs_temp_bytes(int64_t N, int64_t cap, size_t* scan_bytes, size_t* sort_by
  * gsplat projection_ewa_3dgs_fused_fwd (Ops.h:42-64; ProjectionEWA3DGSFused.cu:16-212)
  * + intersect_tile pass 1 (IntersectTile.cu:66-84) + cumsum (Intersect.cpp:79).
  * scale_dim 1 = isotropic [N,1]; 3 = [N,3] with quats [N,4].
+ * Alignment: rec, quats (and v_rec, v_quats in the backward) are read / written as float4 rows and must be
+ * 16-byte aligned, radii 8-byte aligned (ISOGS_E_ARG otherwise); every other array is 4-byte aligned.
  * pose (HOST, nullable) or pose_dev (DEVICE float[7] q,t; nullable) is applied first.
  * ch 4: record colours {c0,c1,c2,z}; ch 5: {c0,c1,c2,z,z*z}.
  * Outputs: rec [N,12], radii [N,2] i32, tiles [N] i32, cum [N] i32 (inclusive scan of tiles).

@@ -343,6 +343,10 @@ extern "C" int isogs_preprocess_fwd(const isogs_camera* cam, const isogs_pose* p
         return ISOGS_OK;
     }
     if (N >= (1ll << 31)) { set_error("N too large"); return ISOGS_E_ARG; }
+    if ((((uintptr_t)rec | (uintptr_t)quats) & 15) || ((uintptr_t)radii & 7)) {
+        set_error("isogs_preprocess_fwd: rec / quats must be 16-byte aligned, radii 8-byte aligned");
+        return ISOGS_E_ARG;
+    }
     DevCam dc = make_devcam(*cam);
     DevPose dp = make_devpose(pose, pose_dev);
     const int block = 256;
@@ -383,6 +387,10 @@ extern "C" int isogs_preprocess_bwd(const isogs_camera* cam, const isogs_pose* p
         return ISOGS_E_ARG;
     }
     if (N == 0) return ISOGS_OK;
+    if ((((uintptr_t)v_rec | (uintptr_t)quats | (uintptr_t)v_quats) & 15) || ((uintptr_t)radii & 7)) {
+        set_error("isogs_preprocess_bwd: v_rec / quats / v_quats must be 16-byte aligned, radii 8-byte aligned");
+        return ISOGS_E_ARG;
+    }
     DevCam dc = make_devcam(*cam);
     DevPose dp = make_devpose(pose, pose_dev);
     const bool want_pose = (v_pose != nullptr) && dp.mode != 0;

@@ -48,17 +48,18 @@ class GaussianMap:
             self.v[k] = torch.zeros_like(buf)
         # one contiguous gradient buffer so a single all-reduce covers every parameter group
         self.grad_names = [k for k in PARAM_ORDER if not (self.isotropic and k == "unnorm_rotations")]
-        total = sum(self.widths[k] for k in self.grad_names) * self.capacity
+        total = sum(self.widths[k] for k in self.grad_names) * self.capacity + 4 * len(self.grad_names)
         self.grad_flat = torch.zeros((total,), dtype=torch.float32, device=self.device)
         self._carve()
         self.step_count = 0
 
     def _carve(self):
+        # every group starts on a 16-byte boundary (the kernels store float4 rows); the padding floats stay 0
         self.g, off = {}, 0
         for k in self.grad_names:
             sz = self.widths[k] * self.count
             self.g[k] = self.grad_flat[off:off + sz].view(self.count, self.widths[k])
-            off += sz
+            off = (off + sz + 3) & ~3
         self.grad_used = off
 
     def view(self, k):
@@ -88,7 +89,7 @@ class GaussianMap:
                 buf[:self.count] = d[k][:self.count]
                 d[k] = buf
         self.capacity = cap
-        total = sum(self.widths[k] for k in self.grad_names) * cap
+        total = sum(self.widths[k] for k in self.grad_names) * cap + 4 * len(self.grad_names)
         self.grad_flat = torch.zeros((total,), dtype=torch.float32, device=self.device)
         self._carve()
 
@@ -248,15 +249,17 @@ def _mark(marks, name):
         marks.append((name, ev))
 
 
-def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, allreduce=None, marks=None):
+def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, allreduce=None, marks=None, w_im=0.5,
+             w_depth=1.0):
     """One mapping iteration on one keyframe (splatam.py:1412-1476, L1 terms).  `pose` is the keyframe's
     HOST pose (camera_grad=False).  `allreduce(flat_grad_tensor)` is called between backward and Adam.
-    `marks` (a list) receives (stage, cuda event) pairs for per-stage timing."""
+    `marks` (a list) receives (stage, cuda event) pairs for per-stage timing.  `w_im` weighs the mean colour
+    L1 (the reference's 0.5 * 0.8 * L1 once the 0.2 * (1 - SSIM) term is added, splatam.py:568)."""
     _mark(marks, "begin")
     ws.small.zero_()
     render_forward(ws, gmap, pose=pose, marks=marks)
     _mark(marks, "blend_fwd")
-    loss_l1(ws, 1, gt_rgb, gt_depth, inv_n_depth)
+    loss_l1(ws, 1, gt_rgb, gt_depth, inv_n_depth, w_im=w_im, w_depth=w_depth)
     _mark(marks, "loss")
     render_backward(ws, gmap, pose=pose, want_gaussians=True, marks=marks)
     if allreduce is not None:

@@ -3,7 +3,12 @@
 checker for slam_step.map_step / track_step and for the 50-frame ATE comparison."""
 import numpy as np
 
-MAP_LRS = dict(means3D=1e-4, rgb_colors=2.5e-3, logit_opacities=0.05, log_scales=1e-3)
+MAP_LRS = dict(means3D=1e-4, rgb_colors=2.5e-3, unnorm_rotations=1e-3, logit_opacities=0.05, log_scales=1e-3)
+
+
+def _quats(p):
+    """Rotations matter only for three-axis scales (transform_to_frame, slam_helpers.py:276-279)."""
+    return p["unnorm_rotations"] if p["log_scales"].ndim == 2 and p["log_scales"].shape[1] == 3 else None
 
 
 def new_state(params):
@@ -23,19 +28,22 @@ def _flags(orc):
     return orc.F_LOG_SCALES | orc.F_LOGIT_OPAC
 
 
-def map_iteration(orc, ocam, state, q, t, gt_rgb, gt_depth, grads_out=None, extra_grads=None):
+def map_iteration(orc, ocam, state, q, t, gt_rgb, gt_depth, grads_out=None, extra_grads=None, w_im=0.5, w_depth=1.0):
     """One mapping iteration on one keyframe.  extra_grads: list of gradient dicts from OTHER ranks of the
     data-parallel schedule (averaged with this one before Adam)."""
     p = state["p"]
     pose = orc.make_pose(q, t)
     lo = p["logit_opacities"].reshape(-1)
-    o = orc.render_full(ocam, p["means3D"], p["log_scales"], None, lo, p["rgb_colors"], ch=5, flags=_flags(orc),
+    qs = _quats(p)
+    o = orc.render_full(ocam, p["means3D"], p["log_scales"], qs, lo, p["rgb_colors"], ch=5, flags=_flags(orc),
                         pose=pose)
-    v_render, losses = orc.loss_l1(ocam, 1, o["render"], o["alpha"], gt_rgb, gt_depth)
+    v_render, losses = orc.loss_l1(ocam, 1, o["render"], o["alpha"], gt_rgb, gt_depth, w_im=w_im, w_depth=w_depth)
     v_rec = orc.blend_bwd(ocam, 5, o["rec"], o["vals"], o["ranges"], o["alpha"], o["last"], v_render)
-    g = orc.preprocess_bwd(ocam, p["means3D"], p["log_scales"], None, lo, p["rgb_colors"], o["radii"], o["rec"], v_rec,
+    g = orc.preprocess_bwd(ocam, p["means3D"], p["log_scales"], qs, lo, p["rgb_colors"], o["radii"], o["rec"], v_rec,
                            ch=5, flags=_flags(orc), pose=pose)
     grads = dict(means3D=g["means"], rgb_colors=g["colors"], logit_opacities=g["opacities"], log_scales=g["scales"])
+    if qs is not None:
+        grads["unnorm_rotations"] = g["quats"]
     if grads_out is not None:
         grads_out.update({k: np.array(v, copy=True) for k, v in grads.items()})
     if extra_grads:
@@ -44,6 +52,8 @@ def map_iteration(orc, ocam, state, q, t, gt_rgb, gt_depth, grads_out=None, extr
                  for k, v in grads.items()}
     state["step"] += 1
     for k, lr in MAP_LRS.items():
+        if k not in grads:
+            continue
         orc.adam(p[k].reshape(-1), np.ascontiguousarray(grads[k]).reshape(-1), state["m"][k].reshape(-1),
                  state["v"][k].reshape(-1), lr, eps=1e-15, step=state["step"])
     return float(losses[0])
@@ -71,11 +81,12 @@ def track_iteration(orc, ocam, params, ts, gt_rgb, gt_depth, lr_rot=4e-4, lr_tra
     best candidate kept as in splatam.py:1287-1290."""
     pose = orc.make_pose(ts.pose[:4], ts.pose[4:])
     lo = params["logit_opacities"].reshape(-1)
-    o = orc.render_full(ocam, params["means3D"], params["log_scales"], None, lo, params["rgb_colors"], ch=5,
+    qs = _quats(params)
+    o = orc.render_full(ocam, params["means3D"], params["log_scales"], qs, lo, params["rgb_colors"], ch=5,
                         flags=_flags(orc), pose=pose)
     v_render, losses = orc.loss_l1(ocam, 0, o["render"], o["alpha"], gt_rgb, gt_depth, use_sil=use_sil)
     v_rec = orc.blend_bwd(ocam, 5, o["rec"], o["vals"], o["ranges"], o["alpha"], o["last"], v_render)
-    g = orc.preprocess_bwd(ocam, params["means3D"], params["log_scales"], None, lo, params["rgb_colors"], o["radii"],
+    g = orc.preprocess_bwd(ocam, params["means3D"], params["log_scales"], qs, lo, params["rgb_colors"], o["radii"],
                            o["rec"], v_rec, ch=5, flags=_flags(orc), pose=pose)
     gp = np.ascontiguousarray(g["pose"], dtype=np.float32)
     ts.step += 1

@@ -74,7 +74,8 @@ def _worker(rank, world, port, out_dir):
             if world > 1:
                 assert not torch.equal(before, flat)
             state["step"] += 1
-            for name, lr in osl.MAP_LRS.items():
+            for name in gmap.grad_names:
+                lr = osl.MAP_LRS[name]
                 orc.adam(state["p"][name].reshape(-1), gmap.g[name].numpy().reshape(-1), state["m"][name].reshape(-1),
                          state["v"][name].reshape(-1), lr, eps=1e-15, step=state["step"])
             tens = [torch.from_numpy(state["p"][n]) for n in gmap.grad_names]

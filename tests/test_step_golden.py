@@ -1,0 +1,210 @@
+"""The tracking / mapping step against the reference's OWN Python code.
+
+tests/golden/splatam_step_64x48.npz was written by oracle/pin_against_splatam.py, which imports
+python_ordinary/scripts/splatam.py (get_pointcloud, initialize_params, get_loss, add_new_gaussians,
+initialize_camera_pose, initialize_optimizer) and utils/slam_external.prune_gaussians and runs them
+on the CPU with the oracle standing in for the CUDA rasterizer.  Here:
+  * CPU (`-m "not gpu"`): the oracle's step restatement (tests/oracle_slam.py) against the fixture;
+  * GPU (`-m gpu`): slam_step.track_step / map_step / add_new_gaussians / prune_gaussians /
+    init_camera_pose through the C ABI against the fixture.
+Tolerances: losses 1e-5 relative, gradients 1e-3 of the largest component (north_star), Adam-updated
+values 1e-6 absolute where the gradient is not numerical noise (Adam's first step is lr*sign(g))."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_slam as osl
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+FIX = os.path.join(ROOT, "tests", "golden", "splatam_step_64x48.npz")
+GAUSS = ("means3D", "rgb_colors", "unnorm_rotations", "logit_opacities", "log_scales")
+
+
+@pytest.fixture(scope="module")
+def fx():
+    return dict(np.load(FIX))
+
+
+def _cam_args(fx):
+    W, H, fx_, fy, cx, cy = [float(v) for v in fx["intr"]]
+    return int(W), int(H), fx_, fy, cx, cy
+
+
+def _relmax(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+
+
+def _row_err(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return np.abs(a.reshape(b.shape) - b).reshape(b.shape[0], -1).max(1) / max(np.abs(b).max(), 1e-30)
+
+
+def _check_map_gradients(get_grad, fx):
+    """Gradients within 1e-3 of the largest component (north_star) for all Gaussians but the handful touched
+    by ONE depth-order swap: torch's `rel_w2c @ pts4.T` and the fused transform differ by 1 ulp in camera depth,
+    which swaps the compositing order of two near-coplanar Gaussians (rows 3037 / 3040, the first appended
+    ones) in the top-right corner.  Returns the mask of rows to compare further."""
+    bad = np.zeros(fx["map_in_means3D"].shape[0], bool)
+    for k in GAUSS:
+        bad |= _row_err(get_grad(k), fx[f"map_grad_{k}"]) > 1e-3
+    assert bad.sum() <= 8, np.nonzero(bad)[0]
+    return ~bad
+
+
+def _check_adam_update(p1, ref1, grad, lr, steps, rows, name):
+    """Adam's update is lr * f(g_1/|g_2|...): an element's update error is lr x the RELATIVE error of that
+    gradient element.  Elements above 1% of the largest gradient must agree to 5% of lr; the others (down to
+    numerical noise, where the sign-like first step may flip) are bounded by 2*lr*steps."""
+    g = np.abs(grad.reshape(ref1.shape))
+    solid = (g > 1e-2 * g.max()) & rows.reshape((-1,) + (1,) * (g.ndim - 1))
+    assert solid.mean() > 0.02, (name, solid.mean())
+    d = np.abs(np.asarray(p1).reshape(ref1.shape) - ref1)
+    assert d[solid].max() < 1e-6 + 0.05 * lr, (name, d[solid].max())
+    assert d.max() <= 2.0 * lr * steps + 1e-6, name
+
+
+# ------------------------------------------------------------------ CPU: oracle vs fixture
+def test_fixture_notes(fx):
+    assert "get_loss(tracking=True" in str(fx["notes"])
+
+
+def test_oracle_init_matches_reference(orc, fx):
+    """get_pointcloud + initialize_params (splatam.py:296-399): integer-pixel back-projection, s = z / f."""
+    W, H, f_x, f_y, cx, cy = _cam_args(fx)
+    d = fx["d0"][0]
+    ys, xs = np.nonzero(d > 0)
+    z = d[ys, xs]
+    means = np.stack([(xs - cx) / f_x * z, (ys - cy) / f_y * z, z], -1)
+    assert np.abs(means - fx["init_means3D"]).max() < 1e-5
+    assert np.abs(fx["rgb0"][:, ys, xs].T - fx["init_rgb_colors"]).max() == 0
+    base = np.log(z / ((f_x + f_y) / 2))[:, None]
+    assert np.abs(fx["init_log_scales"] - base).max() < 0.06          # N(0, 0.01) noise, splatam.py:366
+    assert np.abs(fx["init_logit_opacities"]).max() == 0
+
+
+def test_oracle_tracking_matches_reference(orc, fx):
+    ocam = orc.make_camera(*_cam_args(fx))
+    params = {k: fx[f"init_{k}"] for k in GAUSS}
+    ts = osl.TrackState(fx["track_pose0"][:4], fx["track_pose0"][4:])
+    for it in range(3):
+        loss, gp = osl.track_iteration(orc, ocam, params, ts, fx["rgb1"], fx["d1"][0])
+        assert abs(loss - fx["track_losses"][it, 0]) < 2e-5 * fx["track_losses"][it, 0], it
+        assert _relmax(gp, fx["track_grads"][it]) < 1e-3, (it, gp, fx["track_grads"][it])
+        assert np.abs(ts.pose - fx["track_poses"][it]).max() < 2e-6, it
+
+
+def test_oracle_mapping_matches_reference(orc, fx):
+    ocam = orc.make_camera(*_cam_args(fx))
+    st = osl.new_state({k: fx[f"map_in_{k}"] for k in GAUSS})
+    q, t = fx["track_poses"][2][:4], fx["track_poses"][2][4:]
+    g0 = {}
+    for it in range(2):
+        loss = osl.map_iteration(orc, ocam, st, q, t, fx["rgb1"], fx["d1"][0], grads_out=g0 if it == 0 else None,
+                                 w_im=0.5 * 0.8)
+        # 1e-4: torch's `rel_w2c @ pts4.T` and the fused transform differ by 1 ulp in camera depth, which swaps
+        # the compositing order of two near-coplanar Gaussians in the top-right corner (12 pixels, 7e-5 of the
+        # colour term); everything else agrees to 1e-7.
+        assert abs(loss - fx["map_losses"][it, 0]) < 1e-4 * fx["map_losses"][it, 0], it
+    rows = _check_map_gradients(lambda k: g0[k], fx)
+    for k in GAUSS:
+        _check_adam_update(st["p"][k], fx[f"map_out_{k}"], fx[f"map_grad_{k}"], osl.MAP_LRS[k], 2, rows, k)
+
+
+def test_init_camera_pose_matches_reference(fx):
+    """initialize_camera_pose (splatam.py:844-863) on the fixture's poses of frames 0 and 1 (host arithmetic)."""
+    import importlib
+
+    import isogs_b200  # noqa: F401
+    ss = importlib.import_module("isogs_slam_cpp_b200.slam_step")
+    p1 = fx["track_poses"][2]
+    q, t = ss.init_camera_pose((p1[:4], p1[4:]), (np.array([1, 0, 0, 0], np.float32), np.zeros(3, np.float32)))
+    assert np.abs(np.concatenate([q, t]) - fx["init_pose2"]).max() < 1e-6
+
+
+# ------------------------------------------------------------------ GPU: product path vs fixture
+def _gpu(fx):
+    import importlib
+
+    import isogs_b200
+    import torch
+    pkg = isogs_b200.pkg
+    ss = importlib.import_module("isogs_slam_cpp_b200.slam_step")
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).cuda()  # noqa: E731
+    return pkg, ss, torch, dev, pkg.make_camera(*_cam_args(fx))
+
+
+@pytest.mark.gpu
+def test_gpu_track_step_matches_reference(fx):
+    pkg, ss, torch, dev, gcam = _gpu(fx)
+    gmap = ss.GaussianMap({k: fx[f"init_{k}"] for k in GAUSS}, device="cuda")
+    ws = ss.StepWorkspace(gcam, gmap.count, torch.device("cuda"))
+    ps = ss.PoseState(fx["track_pose0"][:4], fx["track_pose0"][4:], "cuda")
+    rgb, depth = dev(fx["rgb1"]), dev(fx["d1"][0])
+    for it in range(3):
+        losses = ss.track_step(ws, gmap, ps, rgb, depth)
+        torch.cuda.synchronize()
+        ref = fx["track_losses"][it]
+        assert abs(float(losses[0]) - ref[0]) < 1e-4 * ref[0], (it, float(losses[0]), ref[0])
+        assert _relmax(ws.v_pose.cpu().numpy(), fx["track_grads"][it]) < 1e-3, it
+        assert np.abs(ps.pose.cpu().numpy() - fx["track_poses"][it]).max() < 5e-6, it
+    assert not ws.check_overflow(wait=True)
+
+
+@pytest.mark.gpu
+def test_gpu_map_step_matches_reference(fx):
+    pkg, ss, torch, dev, gcam = _gpu(fx)
+    gmap = ss.GaussianMap({k: fx[f"map_in_{k}"] for k in GAUSS}, device="cuda")
+    ws = ss.StepWorkspace(gcam, gmap.count, torch.device("cuda"))
+    pose = pkg.make_pose(fx["track_poses"][2][:4], fx["track_poses"][2][4:])
+    rgb, depth = dev(fx["rgb1"]), dev(fx["d1"][0])
+    inv_nd = 1.0 / int((fx["d1"] > 0).sum())
+    rows = None
+    for it in range(2):
+        losses = ss.map_step(ws, gmap, pose, rgb, depth, inv_nd, w_im=0.5 * 0.8)
+        torch.cuda.synchronize()
+        ref = fx["map_losses"][it]
+        assert abs(float(losses[0]) - ref[0]) < 2e-4 * ref[0], (it, float(losses[0]), ref[0])
+        if it == 0:
+            g = {k: gmap.g[k].cpu().numpy() for k in GAUSS}
+            rows = _check_map_gradients(lambda k: g[k], fx)
+            # (means2D.grad of the reference comes from the colour render alone, splatam.py:528-530; the fused
+            # 5-channel step has no separate colour-only screen gradient, so it is not compared here -- the
+            # drop-in rasterizer's means2D.grad is covered by test_dropin_rasterizer_forward_backward.)
+    for k in GAUSS:
+        _check_adam_update(gmap.view(k).cpu().numpy(), fx[f"map_out_{k}"], fx[f"map_grad_{k}"], ss.MAPPING_LRS[k], 2,
+                           rows, k)
+
+
+@pytest.mark.gpu
+def test_gpu_add_new_gaussians_matches_reference(fx):
+    """add_new_gaussians (splatam.py:799-841) at the tracked pose of frame 1: same pixels selected, in the
+    same (row-major) order, same back-projected parameters ("anisotropic": no noise)."""
+    pkg, ss, torch, dev, gcam = _gpu(fx)
+    gmap = ss.GaussianMap({k: fx[f"init_{k}"] for k in GAUSS}, device="cuda")
+    ws = ss.StepWorkspace(gcam, gmap.count, torch.device("cuda"))
+    n0 = gmap.count
+    pose = (fx["track_poses"][2][:4], fx["track_poses"][2][4:])
+    added = ss.add_new_gaussians(ws, gmap, pose, dev(fx["rgb1"]), dev(fx["d1"][0]), sil_thres=0.5, noise_std=0.0)
+    assert added == int(fx["added"][0])
+    assert np.abs(gmap.view("means3D")[n0:].cpu().numpy() - fx["new_means3D"]).max() < 2e-6
+    assert np.array_equal(gmap.view("rgb_colors")[n0:].cpu().numpy(), fx["new_rgb_colors"])
+    assert np.abs(gmap.view("log_scales")[n0:].cpu().numpy() - fx["new_log_scales"]).max() < 1e-6
+    assert np.array_equal(gmap.view("logit_opacities")[n0:].cpu().numpy(), fx["new_logit_opacities"])
+    assert np.array_equal(gmap.view("unnorm_rotations")[n0:].cpu().numpy(), fx["new_unnorm_rotations"])
+    assert np.array_equal(gmap.view("means3D")[:n0].cpu().numpy(), fx["init_means3D"])
+
+
+@pytest.mark.gpu
+def test_gpu_prune_matches_reference(fx):
+    """prune_gaussians + remove_points (slam_external.py:139-188): opacity < 0.005 or max scale >
+    0.1 * scene_radius; survivors keep their order."""
+    pkg, ss, torch, dev, gcam = _gpu(fx)
+    params = {k: fx[f"map_out_{k}"] for k in GAUSS}
+    params["logit_opacities"], params["log_scales"] = fx["prune_in_logit_opacities"], fx["prune_in_log_scales"]
+    gmap = ss.GaussianMap(params, device="cuda")
+    ws = ss.StepWorkspace(gcam, gmap.count, torch.device("cuda"))
+    removed = ss.prune_gaussians(ws, gmap, 0.005, 0.1 * float(fx["scene_radius"][0]))
+    assert gmap.count == fx["prune_out_means3D"].shape[0] and removed == params["means3D"].shape[0] - gmap.count
+    assert np.array_equal(gmap.view("means3D").cpu().numpy(), fx["prune_out_means3D"])
