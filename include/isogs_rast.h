@@ -149,6 +149,16 @@ int isogs_loss_l1_fused(const isogs_camera* cam, int mode, const float* render, 
                         float sil_thres, int use_sil, float inv_n_depth,
                         float* v_render, float* losses, void* stream);
 
+/* fused SSIM term of the mapping colour loss 0.8*L1 + 0.2*(1 - SSIM): replaces calc_ssim / _ssim
+ * (python_ordinary/utils/slam_external.py:54-97; call site splatam.py:568) and its autograd backward
+ * (5 depthwise 11x11 conv2d, zero padding, sigma 1.5, c1 = 1e-4, c2 = 9e-4, mean over [3,H,W]).
+ * render / gt_rgb: DEVICE [>=3,H,W] planes (the first three are used).  dmaps: DEVICE scratch [9,H,W].
+ * ssim_out: DEVICE float[1], += mean SSIM (caller zeroes).  losses (nullable): losses[0] += weight*(1-SSIM).
+ * v_render (nullable): planes 0..2 += d(weight*(1-SSIM))/d(render) -- call AFTER isogs_loss_l1_fused, which
+ * overwrites v_render (pass it w_im = 0.8 * w and this call weight = 0.2 * w for the reference's mix). */
+int isogs_ssim_loss_fused(const isogs_camera* cam, const float* render, const float* gt_rgb, float weight,
+                          float* dmaps, float* v_render, float* losses, float* ssim_out, void* stream);
+
 /* fused multi-tensor Adam with torch.optim.Adam semantics: replaces launch_adam_update
  * (cpp/cuda/kernels/optimizer.cu:15-98), gsplat adam (Ops.h:173-183) and the Python
  * torch.optim.Adam of splatam.py:402-408.  One launch covers n_groups tensors. */

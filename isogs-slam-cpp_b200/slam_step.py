@@ -117,6 +117,8 @@ class StepWorkspace:
         self.last = torch.empty((H, W), dtype=i32, device=device)
         self.small = torch.zeros((32,), dtype=f32, device=device)  # losses[4] | v_pose[7] | pose_acc[16]
         self.losses, self.v_pose, self.pose_acc = self.small[0:4], self.small[4:11], self.small[11:27]
+        self.ssim = self.small[27:28]                               # mean SSIM of the last map_step(ssim=True)
+        self.dmaps = None                                           # [9,H,W] SSIM derivative maps, on first use
         self.isect_cap = 0
         self._grow_isects(max(1024, 3 * n_cap))
         # device-side intersection count {n_isects, overflow} + its lagged pinned mirror
@@ -228,6 +230,15 @@ def loss_l1(ws, mode, gt_rgb, gt_depth, inv_n_depth=1.0, w_im=0.5, w_depth=1.0, 
                                     _ptr(ws.v_render), _ptr(ws.losses), _stream()))
 
 
+def loss_ssim(ws, gt_rgb, weight):
+    """losses[0] += weight * (1 - SSIM(render, gt)); v_render[0:3] += its gradient (calc_ssim,
+    slam_external.py:54-97).  Must follow loss_l1, which overwrites v_render.  ws.ssim receives mean SSIM."""
+    if ws.dmaps is None:
+        ws.dmaps = torch.empty((9, ws.cam.height, ws.cam.width), dtype=torch.float32, device=ws.device)
+    check(lib().isogs_ssim_loss_fused(C.byref(ws.cam), _ptr(ws.render), _ptr(gt_rgb), weight, _ptr(ws.dmaps),
+                                      _ptr(ws.v_render), _ptr(ws.losses), _ptr(ws.ssim), _stream()))
+
+
 def adam_gaussians(gmap, lrs=MAPPING_LRS, eps=1e-15, beta1=0.9, beta2=0.999):
     gmap.step_count += 1
     names = gmap.grad_names
@@ -250,17 +261,20 @@ def _mark(marks, name):
 
 
 def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, allreduce=None, marks=None, w_im=0.5,
-             w_depth=1.0):
+             w_depth=1.0, ssim=False):
     """One mapping iteration on one keyframe (splatam.py:1412-1476, L1 terms).  `pose` is the keyframe's
     HOST pose (camera_grad=False).  `allreduce(flat_grad_tensor)` is called between backward and Adam.
     `marks` (a list) receives (stage, cuda event) pairs for per-stage timing.  `w_im` weighs the mean colour
-    L1 (the reference's 0.5 * 0.8 * L1 once the 0.2 * (1 - SSIM) term is added, splatam.py:568)."""
+    term; `ssim=True` makes that term the reference's 0.8 * L1 + 0.2 * (1 - SSIM) (splatam.py:568), else pure L1."""
     _mark(marks, "begin")
     ws.small.zero_()
     render_forward(ws, gmap, pose=pose, marks=marks)
     _mark(marks, "blend_fwd")
-    loss_l1(ws, 1, gt_rgb, gt_depth, inv_n_depth, w_im=w_im, w_depth=w_depth)
+    loss_l1(ws, 1, gt_rgb, gt_depth, inv_n_depth, w_im=(0.8 * w_im if ssim else w_im), w_depth=w_depth)
     _mark(marks, "loss")
+    if ssim:
+        loss_ssim(ws, gt_rgb, 0.2 * w_im)
+        _mark(marks, "ssim")
     render_backward(ws, gmap, pose=pose, want_gaussians=True, marks=marks)
     if allreduce is not None:
         allreduce(gmap.grad_flat[:gmap.grad_used])

@@ -739,6 +739,90 @@ extern "C" void orc_loss_l1(const orc_camera* cam, int mode, const float* render
     losses[2] = ld;
 }
 
+// calc_ssim / _ssim (python_ordinary/utils/slam_external.py:54-97): separable 11-tap Gaussian (sigma 1.5, float32
+// weights normalised in float32), zero padding, on x, y, x*x, y*y, x*y; SSIM map; mean.  The backward is the
+// analytic adjoint of the same expression (the reference gets it from autograd).
+extern "C" double orc_ssim(int W, int H, const float* x, const float* y, float coef, float* v_x) {
+    const int R = 5;
+    float g[11];
+    {
+        float s = 0.f;
+        for (int i = 0; i < 11; ++i) { g[i] = (float)std::exp(-(double)((i - R) * (i - R)) / (2.0 * 1.5 * 1.5)); s += g[i]; }
+        for (int i = 0; i < 11; ++i) g[i] /= s;
+    }
+    const int64_t P = (int64_t)W * H;
+    const double c1 = 0.01 * 0.01, c2 = 0.03 * 0.03;
+    std::vector<double> tmp(5 * P), mom(5 * P), dm(3 * P);
+    double total = 0.0;
+    for (int c = 0; c < 3; ++c) {
+        const float* X = x + c * P;
+        const float* Y = y + c * P;
+        // horizontal then vertical pass over the five moments
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < P; ++i) {
+            const int yy = (int)(i / W), xx = (int)(i % W);
+            double a[5] = {0, 0, 0, 0, 0};
+            for (int k = -R; k <= R; ++k) {
+                const int q = xx + k;
+                if (q < 0 || q >= W) continue;
+                const double w = g[k + R], vx = X[(int64_t)yy * W + q], vy = Y[(int64_t)yy * W + q];
+                a[0] += w * vx; a[1] += w * vy; a[2] += w * vx * vx; a[3] += w * vy * vy; a[4] += w * vx * vy;
+            }
+            for (int m = 0; m < 5; ++m) tmp[m * P + i] = a[m];
+        }
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < P; ++i) {
+            const int yy = (int)(i / W), xx = (int)(i % W);
+            double a[5] = {0, 0, 0, 0, 0};
+            for (int k = -R; k <= R; ++k) {
+                const int q = yy + k;
+                if (q < 0 || q >= H) continue;
+                for (int m = 0; m < 5; ++m) a[m] += (double)g[k + R] * tmp[m * P + (int64_t)q * W + xx];
+            }
+            for (int m = 0; m < 5; ++m) mom[m * P + i] = a[m];
+        }
+        double sum = 0.0;
+#pragma omp parallel for reduction(+ : sum) schedule(static)
+        for (int64_t i = 0; i < P; ++i) {
+            const double mx = mom[i], my = mom[P + i], exx = mom[2 * P + i], eyy = mom[3 * P + i], exy = mom[4 * P + i];
+            const double A = 2 * mx * my + c1, B = 2 * (exy - mx * my) + c2;
+            const double Cc = mx * mx + my * my + c1, D = (exx - mx * mx) + (eyy - my * my) + c2;
+            const double S = A * B / (Cc * D);
+            sum += S;
+            dm[i] = 2 * my * (B - A) / (Cc * D) + 2 * mx * S * (1 / D - 1 / Cc);
+            dm[P + i] = -S / D;
+            dm[2 * P + i] = 2 * A / (Cc * D);
+        }
+        total += sum;
+        if (!v_x) continue;
+        // adjoint: the window is symmetric, so convolve the three derivative maps with it
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < P; ++i) {
+            const int yy = (int)(i / W), xx = (int)(i % W);
+            double a[3] = {0, 0, 0};
+            for (int k = -R; k <= R; ++k) {
+                const int q = xx + k;
+                if (q < 0 || q >= W) continue;
+                for (int m = 0; m < 3; ++m) a[m] += (double)g[k + R] * dm[m * P + (int64_t)yy * W + q];
+            }
+            for (int m = 0; m < 3; ++m) tmp[m * P + i] = a[m];
+        }
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < P; ++i) {
+            const int yy = (int)(i / W), xx = (int)(i % W);
+            double a[3] = {0, 0, 0};
+            for (int k = -R; k <= R; ++k) {
+                const int q = yy + k;
+                if (q < 0 || q >= H) continue;
+                for (int m = 0; m < 3; ++m) a[m] += (double)g[k + R] * tmp[m * P + (int64_t)q * W + xx];
+            }
+            const double d = a[0] + 2.0 * X[i] * a[1] + (double)Y[i] * a[2];
+            v_x[c * P + i] += (float)((double)coef * d / (3.0 * (double)P));
+        }
+    }
+    return total / (3.0 * (double)P);
+}
+
 extern "C" void orc_adam(int64_t n, float* p, const float* g, float* m, float* v, float lr, float b1, float b2,
                          float eps, int step) {
     // torch.optim.Adam (single tensor, no amsgrad / weight decay): step counted from 1

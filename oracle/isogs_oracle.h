@@ -113,6 +113,11 @@ void orc_loss_l1(const orc_camera* cam, int mode, const float* render /*[5,H,W]*
                  float* v_render, double* losses);
 
 /* torch.optim.Adam semantics (bias-corrected, step counted from 1; splatam.py:402-408). */
+/* SSIM term (python_ordinary/utils/slam_external.py:54-97): returns mean SSIM over [3,H,W]; if v_x is
+ * non-null, v_x[3,H,W] += coef * d(mean SSIM)/dx  (x = first image).  Double accumulation. */
+double orc_ssim(int width, int height, const float* x /*[3,H,W]*/, const float* y /*[3,H,W]*/, float coef,
+                float* v_x /*nullable*/);
+
 void orc_adam(int64_t n, float* p, const float* g, float* m, float* v, float lr, float b1,
               float b2, float eps, int step);
 

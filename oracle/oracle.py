@@ -169,6 +169,15 @@ def loss_l1(cam, mode, render, alpha, gt_rgb, gt_depth, w_im=0.5, w_depth=1.0, s
     return v_render, losses
 
 
+def ssim(x, y, coef=0.0, v_x=None):
+    """Mean SSIM of [3,H,W] images; if v_x is given, v_x += coef * d(mean SSIM)/dx in place."""
+    x, y = _f(x), _f(y)
+    H, W = x.shape[1], x.shape[2]
+    fn = lib().orc_ssim
+    fn.restype = C.c_double
+    return float(fn(C.c_int(W), C.c_int(H), _p(x), _p(y), C.c_float(coef), _p(v_x)))
+
+
 def adam(p, g, m, v, lr, b1=0.9, b2=0.999, eps=1e-8, step=1):
     """In-place on p, m, v (float32 contiguous)."""
     lib().orc_adam(C.c_int64(p.size), _p(p), _p(_f(g)), _p(m), _p(v), C.c_float(lr), C.c_float(b1),

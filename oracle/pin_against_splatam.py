@@ -20,9 +20,10 @@ Outputs tests/golden/splatam_step_*.npz (inputs + the reference's losses, gradie
 parameters).  tests/test_oracle_golden.py repeats the oracle-side comparison anywhere;
 tests/test_gpu_step.py compares track_step / map_step / add_new_gaussians on the GPU.
 
-The mapping colour term in the reference is 0.8*L1 + 0.2*(1-SSIM) (splatam.py:568); SSIM is the
-next row of SURVEY 8(f), so the fixture is generated with calc_ssim pinned to 1 (colour term =
-0.8*L1) and flat/iso weights 0 -- stated again in the fixture's `notes`.
+The mapping iterations use the reference's full colour term 0.8*L1 + 0.2*(1-SSIM) (splatam.py:568,
+calc_ssim of slam_external.py:54-97); the flat / iso weights are 0 (not built) --
+stated again in the fixture's `notes`.  calc_ssim and its autograd gradient are also recorded on
+their own (ssim_value / ssim_grad for x = rgb0, y = rgb1).
 
 Usage:  python oracle/pin_against_splatam.py
 """
@@ -177,7 +178,7 @@ def main():
         K = torch.tensor([[FX, 0, CX], [0, FY, CY], [0, 0, 1]], dtype=torch.float32)
         w2c0 = torch.eye(4)
         rgb0, d0 = frame((0.0, 0.0, 0.0))
-        rgb1, d1 = frame((1.5, -1.0, 0.02))
+        rgb1, d1 = frame((1.5, -1.3, 0.02))    # -1.3: no mirror symmetry in y, hence no exact depth ties
         cam = ref.setup_camera(W, H, K.numpy(), w2c0.numpy())
 
         # --- initialisation (initialize_first_timestep body, splatam.py:427-436) ---
@@ -229,7 +230,10 @@ def main():
             out[f"new_{k}"] = params[k].detach().numpy()[n0:].copy()
 
         # --- mapping: 2 iterations on frame 1, L1 terms only (splatam.py:1406-1476) ---
-        ref.calc_ssim = lambda a, b: torch.tensor(1.0)          # colour term = 0.8 * L1 (see module docstring)
+        x = rgb0.clone().requires_grad_(True)
+        s_val = ref.calc_ssim(x, rgb1)
+        s_val.backward()
+        out.update(ssim_value=np.array([float(s_val)], np.float64), ssim_grad=x.grad.numpy().copy())
         for k in GAUSS:
             out[f"map_in_{k}"] = params[k].detach().numpy().copy()
         opt = ref.initialize_optimizer(params, MAP_LRS, tracking=False)
@@ -262,7 +266,7 @@ def main():
         params, variables = ref.prune_gaussians(params, variables, opt, 0, pd)
         out["prune_out_means3D"] = params["means3D"].detach().numpy().copy()
     out["notes"] = np.array("tracking: get_loss(tracking=True, use_sil_for_loss=True, sil_thres=0.99, im=0.5, depth=1); "
-                            "mapping: get_loss(mapping=True) with calc_ssim:=1 (colour term 0.8*L1), flat=iso=0; "
+                            "mapping: get_loss(mapping=True), colour term 0.8*L1 + 0.2*(1-SSIM), im=0.5, depth=1, flat=iso=0; "
                             "rasterizer = CPU oracle behind the reference's diff_gaussian_rasterization interface")
     path = os.path.join(ROOT, "tests", "golden", "splatam_step_64x48.npz")
     np.savez_compressed(path, **out)

@@ -28,7 +28,8 @@ def _flags(orc):
     return orc.F_LOG_SCALES | orc.F_LOGIT_OPAC
 
 
-def map_iteration(orc, ocam, state, q, t, gt_rgb, gt_depth, grads_out=None, extra_grads=None, w_im=0.5, w_depth=1.0):
+def map_iteration(orc, ocam, state, q, t, gt_rgb, gt_depth, grads_out=None, extra_grads=None, w_im=0.5, w_depth=1.0,
+                  ssim=False):
     """One mapping iteration on one keyframe.  extra_grads: list of gradient dicts from OTHER ranks of the
     data-parallel schedule (averaged with this one before Adam)."""
     p = state["p"]
@@ -37,7 +38,13 @@ def map_iteration(orc, ocam, state, q, t, gt_rgb, gt_depth, grads_out=None, extr
     qs = _quats(p)
     o = orc.render_full(ocam, p["means3D"], p["log_scales"], qs, lo, p["rgb_colors"], ch=5, flags=_flags(orc),
                         pose=pose)
-    v_render, losses = orc.loss_l1(ocam, 1, o["render"], o["alpha"], gt_rgb, gt_depth, w_im=w_im, w_depth=w_depth)
+    v_render, losses = orc.loss_l1(ocam, 1, o["render"], o["alpha"], gt_rgb, gt_depth,
+                                   w_im=(0.8 * w_im if ssim else w_im), w_depth=w_depth)
+    if ssim:  # colour term 0.8 * L1 + 0.2 * (1 - SSIM), splatam.py:568
+        v_c = np.ascontiguousarray(v_render[:3])
+        s_val = orc.ssim(o["render"][:3], gt_rgb, -0.2 * w_im, v_c)
+        v_render[:3] = v_c
+        losses[0] += 0.2 * w_im * (1.0 - s_val)
     v_rec = orc.blend_bwd(ocam, 5, o["rec"], o["vals"], o["ranges"], o["alpha"], o["last"], v_render)
     g = orc.preprocess_bwd(ocam, p["means3D"], p["log_scales"], qs, lo, p["rgb_colors"], o["radii"], o["rec"], v_rec,
                            ch=5, flags=_flags(orc), pose=pose)
