@@ -169,6 +169,38 @@ typedef struct isogs_adam_group {
 int isogs_adam_fused(const isogs_adam_group* groups /*HOST*/, int n_groups, float beta1, float beta2,
                      float eps, int step, void* stream);
 
+/* ---- gradient-driven densification (off in every reference config, part of the operator surface) ---- */
+
+/* accumulate_mean2d_gradient + max_2D_radius (python_ordinary/utils/slam_external.py:100-104,
+ * splatam.py:751-753): for every Gaussian with radius > 0: grad_accum += |(scale_x v_x, scale_y v_y)|,
+ * denom += 1, max_radius = max(max_radius, radius).  v_xy: DEVICE rows of `v_stride` floats whose first two
+ * are dL/d(mean2D) in pixels (v_rec of isogs_blend_bwd: stride ISOGS_REC); scale (1,1) keeps pixel units. */
+int isogs_densify_stats(int64_t N, const int32_t* radii, const float* v_xy, int v_stride, float scale_x,
+                        float scale_y, float* grad_accum, float* denom, float* max_radius, void* stream);
+
+/* densify (slam_external.py:191-243; GaussianModel::densify, cpp/src/core/gaussian_model.cpp:157-289;
+ * clone_gaussian_kernel / split_gaussian_kernel, cpp/cuda/kernels/densify.cu:10-92) in two calls so the host
+ * can size the pool in between:
+ *   select: grads = accum/denom (nan -> 0); clone = grads >= grad_thresh && max exp(s) <= small_scale;
+ *           split = grads >= grad_thresh && max exp(s) > small_scale  (small_scale = 0.01 * scene_radius).
+ *           scratch: DEVICE int32[4N] (flags + inclusive scans, consumed by emit);
+ *           counts: DEVICE int32[3] = {N + n_clone + n_split_into * n_split, n_clone, n_split}.
+ *   emit:   appends the clones in index order, then n_split_into blocks of the split rows (the reference's
+ *           `.repeat(n, 1)` order) with mean + R(q) (exp(s) * z), log_scale = log(exp(s) / (0.8 n)); z ~ N(0,1)
+ *           from `noise` (DEVICE [n_split_into * n_split, 3], the reference's torch.normal draw divided by std)
+ *           or, if null, from a counter-based generator keyed by (seed, parent, copy, axis).
+ *           keep: DEVICE uint8[>= counts[0]]: 0 for split parents, 1 for everything else (feed isogs_compact).
+ *           The caller zeroes the Adam moments of the appended rows. */
+int isogs_densify_select(int64_t N, const float* grad_accum, const float* denom, const float* log_scales,
+                         int scale_dim, float grad_thresh, float small_scale, int n_split_into,
+                         int32_t* scratch, void* scan_temp, size_t scan_temp_bytes, int32_t* counts, void* stream);
+int isogs_densify_emit(int64_t N, int64_t capacity, const int32_t* scratch, float* means, float* rgb,
+                       float* quats /*nullable*/, float* logit_opac, float* log_scales, int scale_dim,
+                       int n_split_into, const float* noise /*nullable*/, uint64_t seed, uint8_t* keep, void* stream);
+
+/* dst[i] = dst[i] && src[i] (combine the split-parent mask with isogs_prune_mask before one compaction). */
+int isogs_mask_and(int64_t N, uint8_t* dst, const uint8_t* src, void* stream);
+
 /* best-candidate selection of the tracking loop (python_ordinary/scripts/splatam.py:1287-1290),
  * on the device so the loop needs no host sync: if losses[0] (evaluated BEFORE this iteration's
  * Adam step) < best[7], then best[0..6] = pose (the values AFTER the step) and best[7] = losses[0].

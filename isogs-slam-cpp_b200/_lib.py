@@ -74,6 +74,10 @@ _SIGS = {
     "isogs_ssim_loss_fused": (C.c_int, [C.POINTER(Camera), _VP, _VP, _F, _VP, _VP, _VP, _VP, _VP]),
     "isogs_adam_fused": (C.c_int, [C.POINTER(AdamGroup), _I32, _F, _F, _F, _I32, _VP]),
     "isogs_pose_keep_best": (C.c_int, [_VP, _VP, _VP, _VP]),
+    "isogs_densify_stats": (C.c_int, [_I64, _VP, _VP, _I32, _F, _F, _VP, _VP, _VP, _VP]),
+    "isogs_densify_select": (C.c_int, [_I64, _VP, _VP, _VP, _I32, _F, _F, _I32, _VP, _VP, _SZ, _VP, _VP]),
+    "isogs_densify_emit": (C.c_int, [_I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _I32, _I32, _VP, C.c_uint64, _VP, _VP]),
+    "isogs_mask_and": (C.c_int, [_I64, _VP, _VP, _VP]),
     "isogs_prune_mask": (C.c_int, [_I64, _VP, _VP, _I32, _F, _F, _VP, _VP]),
     "isogs_compact": (C.c_int, [_I64, _VP, C.POINTER(Rows), _I32, _VP, _VP, _SZ, _VP, _VP]),
     "isogs_backproject_append": (C.c_int, [C.POINTER(Camera), C.POINTER(Pose), _VP, _VP, _VP, _VP, _F, _F, _VP, _VP,

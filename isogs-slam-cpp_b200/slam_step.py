@@ -19,6 +19,7 @@ from ._lib import REC, check, lib
 from .raster import _ptr, _stream
 
 PARAM_ORDER = ("means3D", "rgb_colors", "unnorm_rotations", "logit_opacities", "log_scales")
+VAR_ORDER = ("means2D_gradient_accum", "denom", "max_2D_radius")
 
 # reference learning rates (python_ordinary/configs/replica/splatam.py:88-96,109-117)
 MAPPING_LRS = dict(means3D=1e-4, rgb_colors=2.5e-3, unnorm_rotations=1e-3, logit_opacities=0.05, log_scales=1e-3)
@@ -46,6 +47,8 @@ class GaussianMap:
             self.p[k] = buf
             self.m[k] = torch.zeros_like(buf)
             self.v[k] = torch.zeros_like(buf)
+        # per-Gaussian statistics of the gradient-driven densification (variables[...] of splatam.py:394-397)
+        self.vars = {k: torch.zeros((self.capacity, 1), dtype=torch.float32, device=self.device) for k in VAR_ORDER}
         # one contiguous gradient buffer so a single all-reduce covers every parameter group
         self.grad_names = [k for k in PARAM_ORDER if not (self.isotropic and k == "unnorm_rotations")]
         total = sum(self.widths[k] for k in self.grad_names) * self.capacity + 4 * len(self.grad_names)
@@ -72,6 +75,12 @@ class GaussianMap:
             self.v[k].zero_()
         self.step_count = 0
 
+    def reset_stats(self):
+        """add_new_gaussians and densify re-create the three statistics as zeros (splatam.py:835-837,
+        slam_external.py:219-222)."""
+        for k in VAR_ORDER:
+            self.vars[k].zero_()
+
     def set_count(self, n):
         self.count = int(n)
         self._carve()
@@ -88,6 +97,10 @@ class GaussianMap:
                 buf = torch.zeros((cap, self.widths[k]), dtype=torch.float32, device=self.device)
                 buf[:self.count] = d[k][:self.count]
                 d[k] = buf
+        for k in VAR_ORDER:
+            buf = torch.zeros((cap, 1), dtype=torch.float32, device=self.device)
+            buf[:self.count] = self.vars[k][:self.count]
+            self.vars[k] = buf
         self.capacity = cap
         total = sum(self.widths[k] for k in self.grad_names) * cap + 4 * len(self.grad_names)
         self.grad_flat = torch.zeros((total,), dtype=torch.float32, device=self.device)
@@ -319,41 +332,127 @@ def add_new_gaussians(ws, gmap, pose, gt_rgb, gt_depth, sil_thres=0.5, noise_std
             gmap.m[k][gmap.count:new_count].zero_()
             gmap.v[k][gmap.count:new_count].zero_()
         gmap.set_count(new_count)
+        gmap.reset_stats()
         ws.ensure_gaussians(new_count)
     return added
 
 
-def prune_gaussians(ws, gmap, opac_thres=0.005, max_scale=float("inf")):
-    """prune_gaussians + remove_points (slam_external.py:139-188): drop `sigmoid(o) < opac_thres or
-    max exp(s) > max_scale`; ONE order-preserving compaction of the 5 parameter tensors and their 10 Adam
-    moments.  Returns the number removed (one host read)."""
-    N = gmap.count
-    if N == 0:
-        return 0
+def _compact(gmap, keep, N):
+    """remove_points (slam_external.py:139-160): ONE order-preserving gather of the 5 parameter tensors, their
+    10 Adam moments and the 3 densification statistics.  Returns the new count (one host read)."""
     dev = gmap.device
-    keep = torch.empty((N,), dtype=torch.uint8, device=dev)
-    L, st = lib(), _stream()
-    check(L.isogs_prune_mask(N, _ptr(gmap.p["logit_opacities"]), _ptr(gmap.p["log_scales"]), gmap.sd, opac_thres,
-                             max_scale, _ptr(keep), st))
     rows_in, rows_out = [], []
-    for d in (gmap.p, gmap.m, gmap.v):
-        for k in PARAM_ORDER:
+    for d, names in ((gmap.p, PARAM_ORDER), (gmap.m, PARAM_ORDER), (gmap.v, PARAM_ORDER), (gmap.vars, VAR_ORDER)):
+        for k in names:
             rows_in.append((d, k))
             rows_out.append(torch.zeros_like(d[k]))
     arr = (_lib.Rows * len(rows_in))()
     for i, ((d, k), out) in enumerate(zip(rows_in, rows_out)):
-        arr[i].inp, arr[i].out, arr[i].width = d[k].data_ptr(), out.data_ptr(), gmap.widths[k]
+        arr[i].inp, arr[i].out, arr[i].width = d[k].data_ptr(), out.data_ptr(), d[k].shape[1]
     scan = torch.empty((N,), dtype=torch.int32, device=dev)
     sb, _ = _lib.temp_bytes(N, 0)
     tmp = torch.empty((sb,), dtype=torch.uint8, device=dev)
     cnt = torch.zeros((1,), dtype=torch.int32, device=dev)
-    check(L.isogs_compact(N, _ptr(keep), arr, len(rows_in), _ptr(scan), _ptr(tmp), sb, _ptr(cnt), st))
+    check(lib().isogs_compact(N, _ptr(keep), arr, len(rows_in), _ptr(scan), _ptr(tmp), sb, _ptr(cnt), _stream()))
     new_count = int(cnt.item())
     if new_count != N:
         for (d, k), out in zip(rows_in, rows_out):
             d[k] = out
         gmap.set_count(new_count)
-    return N - new_count
+    return new_count
+
+
+def prune_gaussians(ws, gmap, opac_thres=0.005, max_scale=float("inf")):
+    """prune_gaussians + remove_points (slam_external.py:139-188): drop `sigmoid(o) < opac_thres or
+    max exp(s) > max_scale`; one compaction.  Returns the number removed (one host read)."""
+    N = gmap.count
+    if N == 0:
+        return 0
+    keep = torch.empty((N,), dtype=torch.uint8, device=gmap.device)
+    check(lib().isogs_prune_mask(N, _ptr(gmap.p["logit_opacities"]), _ptr(gmap.p["log_scales"]), gmap.sd, opac_thres,
+                                 max_scale, _ptr(keep), _stream()))
+    return N - _compact(gmap, keep, N)
+
+
+def accumulate_densify_stats(ws, gmap, v_xy=None, scale=(1.0, 1.0)):
+    """accumulate_mean2d_gradient + the max_2D_radius update of get_loss (slam_external.py:100-104,
+    splatam.py:751-753) for the Gaussians seen by the last render.  v_xy defaults to the screen-space gradient
+    of the last backward (ws.v_rec, pixel units).  NOTE: the reference accumulates the gradient of the COLOUR
+    render only (splatam.py:528-530); the fused 5-channel step's v_rec also carries the depth-loss part -- use
+    `colour_only_screen_gradient` for the reference's exact statistic."""
+    v = ws.v_rec if v_xy is None else v_xy
+    check(lib().isogs_densify_stats(gmap.count, _ptr(ws.radii), _ptr(v), v.shape[1], scale[0], scale[1],
+                                    _ptr(gmap.vars["means2D_gradient_accum"]), _ptr(gmap.vars["denom"]),
+                                    _ptr(gmap.vars["max_2D_radius"]), _stream()))
+
+
+def colour_only_screen_gradient(ws, gmap):
+    """Second blend backward with the depth planes of v_render zeroed: dL_colour/d(mean2D) exactly as the
+    reference's separate colour render sees it.  Costs one extra blend_bwd; only for densification statistics."""
+    N = gmap.count
+    if getattr(ws, "v_rec2", None) is None or ws.v_rec2.shape[0] < ws.v_rec.shape[0]:
+        ws.v_rec2 = torch.empty_like(ws.v_rec)
+        ws.v_render2 = torch.zeros_like(ws.v_render)
+    ws.v_render2[:3].copy_(ws.v_render[:3])
+    ws.v_rec2[:N].zero_()
+    check(lib().isogs_blend_bwd(C.byref(ws.cam), 5, N, _ptr(ws.rec), _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.alpha),
+                                _ptr(ws.last), _ptr(ws.v_render2), None, _ptr(ws.v_rec2), _stream()))
+    return ws.v_rec2
+
+
+DENSIFY_DEFAULTS = dict(start_after=500, remove_big_after=3000, stop_after=5000, densify_every=100, grad_thresh=0.0002,
+                        num_to_split_into=2, removal_opacity_threshold=0.005, final_removal_opacity_threshold=0.005,
+                        reset_opacities=False, reset_opacities_every=3000)   # configs/replica/splatam.py:130-141
+
+
+def densify(ws, gmap, it, scene_radius, dd=DENSIFY_DEFAULTS, seed=0, noise=None, accumulate=True, v_xy=None):
+    """densify (slam_external.py:191-243): accumulate the statistics, and every `densify_every` iterations clone
+    the small / split the large high-gradient Gaussians, drop the split parents, prune by opacity / size -- two
+    device passes (select, emit) + ONE compaction instead of the reference's ~40 torch ops and 4 torch.cat
+    re-allocations.  Two host reads (the new count to size the pool, the count after compaction).
+    `noise` ([n*n_split,3] standard normals, reference row order) overrides the built-in generator (tests).
+    Returns (n_clone, n_split, n_removed) or None when nothing was due."""
+    if it > dd["stop_after"]:
+        return None
+    if accumulate:
+        accumulate_densify_stats(ws, gmap, v_xy)
+    out = None
+    if it >= dd["start_after"] and it % dd["densify_every"] == 0:
+        N, n_into, dev = gmap.count, int(dd["num_to_split_into"]), gmap.device
+        L, st = lib(), _stream()
+        scratch = torch.empty((4 * N,), dtype=torch.int32, device=dev)
+        sb, _ = _lib.temp_bytes(N, 0)
+        tmp = torch.empty((sb,), dtype=torch.uint8, device=dev)
+        counts = torch.zeros((3,), dtype=torch.int32, device=dev)
+        check(L.isogs_densify_select(N, _ptr(gmap.vars["means2D_gradient_accum"]), _ptr(gmap.vars["denom"]),
+                                     _ptr(gmap.p["log_scales"]), gmap.sd, dd["grad_thresh"], 0.01 * scene_radius, n_into,
+                                     _ptr(scratch), _ptr(tmp), sb, _ptr(counts), st))
+        total, n_clone, n_split = (int(x) for x in counts.cpu())
+        gmap.reserve(total)
+        keep = torch.empty((total,), dtype=torch.uint8, device=dev)
+        check(L.isogs_densify_emit(N, gmap.capacity, _ptr(scratch), _ptr(gmap.p["means3D"]), _ptr(gmap.p["rgb_colors"]),
+                                   _ptr(gmap.p["unnorm_rotations"]), _ptr(gmap.p["logit_opacities"]),
+                                   _ptr(gmap.p["log_scales"]), gmap.sd, n_into, _ptr(noise), seed, _ptr(keep), st))
+        for k in PARAM_ORDER:                                   # cat_params_to_optimizer: new rows start at zero
+            gmap.m[k][N:total].zero_()
+            gmap.v[k][N:total].zero_()
+        gmap.set_count(total)
+        gmap.reset_stats()                                      # :219-222
+        thr = dd["final_removal_opacity_threshold"] if it == dd["stop_after"] else dd["removal_opacity_threshold"]
+        big = 0.1 * scene_radius if it >= dd["remove_big_after"] else float("inf")
+        keep2 = torch.empty((total,), dtype=torch.uint8, device=dev)
+        check(L.isogs_prune_mask(total, _ptr(gmap.p["logit_opacities"]), _ptr(gmap.p["log_scales"]), gmap.sd, thr, big,
+                                 _ptr(keep2), st))
+        check(L.isogs_mask_and(total, _ptr(keep), _ptr(keep2), st))
+        left = _compact(gmap, keep, total)
+        ws.ensure_gaussians(left)
+        out = (n_clone, n_split, total - left)
+    if it > 0 and it % dd["reset_opacities_every"] == 0 and dd["reset_opacities"]:
+        # inverse_sigmoid(0.01), fresh Adam state for the group (update_params_and_optimizer, :106-119)
+        gmap.p["logit_opacities"][:gmap.count].fill_(-4.59511985013459)
+        gmap.m["logit_opacities"].zero_()
+        gmap.v["logit_opacities"].zero_()
+    return out
 
 
 class PoseState:

@@ -265,6 +265,60 @@ def main():
         out["scene_radius"] = np.array([float(variables["scene_radius"])], np.float32)
         params, variables = ref.prune_gaussians(params, variables, opt, 0, pd)
         out["prune_out_means3D"] = params["means3D"].detach().numpy().copy()
+        # --- gradient-driven densification (slam_external.py:100-104,191-243) on isotropic [N,1] scales, the
+        # only layout the reference's `stds.repeat(n, 3)` supports; torch.normal's draw is captured so that the
+        # device kernel can be fed the same standard normals ---
+        import utils.slam_external as se
+        g = torch.Generator().manual_seed(7)
+        Nd = 300
+        dp = dict(means3D=torch.randn(Nd, 3, generator=g), rgb_colors=torch.rand(Nd, 3, generator=g),
+                  unnorm_rotations=torch.randn(Nd, 4, generator=g),
+                  logit_opacities=3.0 * torch.randn(Nd, 1, generator=g),
+                  log_scales=torch.log(0.005 + 0.075 * torch.rand(Nd, 1, generator=g)),
+                  cam_unnorm_rots=torch.tensor([[[1.0], [0.0], [0.0], [0.0]]]), cam_trans=torch.zeros(1, 3, 1))
+        dp = {k: torch.nn.Parameter(v.float().contiguous().requires_grad_(True)) for k, v in dp.items()}
+        dopt = ref.initialize_optimizer(dp, MAP_LRS, tracking=False)
+        for k in GAUSS:                                        # one Adam step so that the moments are non-trivial
+            dp[k].grad = 1e-3 * torch.randn(dp[k].shape, generator=g)
+        dopt.step()
+        dopt.zero_grad(set_to_none=True)
+        for k in GAUSS:
+            out[f"dens_in_{k}"] = dp[k].detach().numpy().copy()
+            st = dopt.state[dp[k]]
+            out[f"dens_in_m_{k}"] = st["exp_avg"].numpy().copy()
+            out[f"dens_in_v_{k}"] = st["exp_avg_sq"].numpy().copy()
+        m2d = torch.zeros(Nd, 3, requires_grad=True)
+        m2d.grad = torch.cat([8e-4 * torch.randn(Nd, 2, generator=g), torch.zeros(Nd, 1)], dim=1)
+        seen = torch.rand(Nd, generator=g) < 0.8
+        dvars = dict(means2D=m2d, seen=seen, scene_radius=torch.tensor(2.0),
+                     means2D_gradient_accum=3e-4 * torch.rand(Nd, generator=g),
+                     denom=torch.randint(0, 3, (Nd,), generator=g).float(), max_2D_radius=torch.zeros(Nd))
+        # (no 'timestep' entry: the reference's densify does not extend it and remove_points then fails, :156-157)
+        out.update(dens_v_xy=m2d.grad.numpy().copy(), dens_seen=seen.numpy().copy(),
+                   dens_accum0=dvars["means2D_gradient_accum"].numpy().copy(), dens_denom0=dvars["denom"].numpy().copy())
+        dvars = se.accumulate_mean2d_gradient(dvars)            # a first, separate accumulation (a12)
+        out.update(dens_accum1=dvars["means2D_gradient_accum"].numpy().copy(), dens_denom1=dvars["denom"].numpy().copy())
+        captured = {}
+        real_normal = torch.normal
+
+        def capture_normal(mean, std, **kw):
+            r = real_normal(mean=mean, std=std, **kw)
+            captured["z"] = (r / std).detach().numpy().copy()
+            return r
+        torch.normal = capture_normal
+        ddict = dict(start_after=0, remove_big_after=0, stop_after=1000, densify_every=1, grad_thresh=0.0002,
+                     num_to_split_into=2, removal_opacity_threshold=0.005, final_removal_opacity_threshold=0.005,
+                     reset_opacities=False, reset_opacities_every=3000)
+        try:
+            dp, dvars = ref.densify(dp, dvars, dopt, 1, ddict)
+        finally:
+            torch.normal = real_normal
+        out["dens_noise"] = captured["z"].astype(np.float32)
+        for k in GAUSS:
+            out[f"dens_out_{k}"] = dp[k].detach().numpy().copy()
+        st = dopt.state[dp["means3D"]]
+        out["dens_out_m_means3D"] = st["exp_avg"].numpy().copy()
+        out["dens_out_accum"] = dvars["means2D_gradient_accum"].numpy().copy()
     out["notes"] = np.array("tracking: get_loss(tracking=True, use_sil_for_loss=True, sil_thres=0.99, im=0.5, depth=1); "
                             "mapping: get_loss(mapping=True), colour term 0.8*L1 + 0.2*(1-SSIM), im=0.5, depth=1, flat=iso=0; "
                             "rasterizer = CPU oracle behind the reference's diff_gaussian_rasterization interface")

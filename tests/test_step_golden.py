@@ -254,3 +254,46 @@ def test_gpu_ssim_kernel_matches_oracle(orc, fx, W, H):
     if (W, H) == (64, 48):
         assert abs(got[4] - fx["ssim_value"][0]) < 2e-5
         assert _relmax((gv[:3].astype(np.float64) - base) / -weight, fx["ssim_grad"]) < 1e-3
+
+
+@pytest.mark.gpu
+def test_gpu_densify_matches_reference(fx):
+    """accumulate_mean2d_gradient + densify (slam_external.py:100-104,191-243) run by the reference itself on 300
+    isotropic Gaussians: statistics, clone / split selection, appended rows (fed the reference's own normal draw),
+    split-parent removal + opacity / size prune, Adam-moment bookkeeping."""
+    pkg, ss, torch, dev, gcam = _gpu(fx)
+    gmap = ss.GaussianMap({k: fx[f"dens_in_{k}"] for k in GAUSS}, device="cuda")
+    N = gmap.count
+    for k in GAUSS:
+        gmap.m[k][:N] = dev(fx[f"dens_in_m_{k}"]).reshape(N, -1)
+        gmap.v[k][:N] = dev(fx[f"dens_in_v_{k}"]).reshape(N, -1)
+    gmap.vars["means2D_gradient_accum"][:N, 0] = dev(fx["dens_accum0"])
+    gmap.vars["denom"][:N, 0] = dev(fx["dens_denom0"])
+    ws = ss.StepWorkspace(gcam, N, torch.device("cuda"))
+    ws.radii[:N] = torch.from_numpy(np.stack([3 * fx["dens_seen"], 2 * fx["dens_seen"]], 1).astype(np.int32)).cuda()
+    v_xy = dev(fx["dens_v_xy"])
+    ss.accumulate_densify_stats(ws, gmap, v_xy=v_xy)
+    assert np.allclose(gmap.vars["means2D_gradient_accum"][:N, 0].cpu().numpy(), fx["dens_accum1"], rtol=1e-6, atol=1e-10)
+    assert np.array_equal(gmap.vars["denom"][:N, 0].cpu().numpy(), fx["dens_denom1"])
+    assert np.array_equal(gmap.vars["max_2D_radius"][:N, 0].cpu().numpy(), 3.0 * fx["dens_seen"])
+    dd = dict(ss.DENSIFY_DEFAULTS, start_after=0, remove_big_after=0, stop_after=1000, densify_every=1)
+    n_clone, n_split, n_removed = ss.densify(ws, gmap, 1, 2.0, dd, noise=dev(fx["dens_noise"]), v_xy=v_xy)
+    assert 2 * n_split == fx["dens_noise"].shape[0] and n_clone > 0
+    assert gmap.count == fx["dens_out_means3D"].shape[0] == N + n_clone + 2 * n_split - n_removed
+    for k in GAUSS:
+        got, ref = gmap.view(k).cpu().numpy(), fx[f"dens_out_{k}"].reshape(gmap.count, -1)
+        assert np.abs(got - ref).max() < 2e-6, k
+    assert np.abs(gmap.m["means3D"][:gmap.count].cpu().numpy() - fx["dens_out_m_means3D"]).max() < 1e-9
+    assert float(gmap.vars["means2D_gradient_accum"].abs().max()) == 0.0 and fx["dens_out_accum"].max() == 0.0
+    # built-in generator: same counts, children spread around the parents with the parents' scale
+    gmap2 = ss.GaussianMap({k: fx[f"dens_in_{k}"] for k in GAUSS}, device="cuda")
+    gmap2.vars["means2D_gradient_accum"][:N, 0] = dev(fx["dens_accum1"])
+    gmap2.vars["denom"][:N, 0] = dev(fx["dens_denom1"])
+    ws.radii[:N] = torch.from_numpy(np.stack([3 * fx["dens_seen"], 2 * fx["dens_seen"]], 1).astype(np.int32)).cuda()
+    c2 = ss.densify(ws, gmap2, 1, 2.0, dd, seed=3, v_xy=v_xy)
+    assert c2 == (n_clone, n_split, n_removed)
+    a, b = gmap2.view("means3D").cpu().numpy(), fx["dens_out_means3D"]
+    same = np.abs(a - b).max(1) < 1e-6
+    assert same.sum() >= gmap2.count - 2 * n_split and np.isfinite(a).all()
+    spread = np.abs(a - b)[~same]
+    assert 0.0 < spread.mean() < 0.2                               # scales are 0.005 .. 0.08
