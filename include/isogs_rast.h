@@ -143,11 +143,21 @@ int isogs_preprocess_bwd(const isogs_camera* cam, const isogs_pose* pose, const 
  * gt_d>0 & !nan & sil>thres), mode 1 mapping (means).  Writes v_render [5,H,W] and
  * losses (DEVICE float[4], zeroed by the caller) = {total, colour, depth, n_valid_depth}.
  * For mode 1 n_valid (number of gt_depth>0 pixels) must be supplied by the caller as
- * inv_n_depth = 1/n_valid (it is a per-frame constant). */
+ * inv_n_depth = 1/n_valid (it is a per-frame constant).
+ * outlier_thresh (DEVICE float*, nullable; mode 0 only): ignore_outlier_depth_loss of splatam.py:551-554 --
+ * pixels with |gt_d - d| >= *outlier_thresh leave the depth AND colour masks; fill it with
+ * isogs_depth_outlier_threshold. */
 int isogs_loss_l1_fused(const isogs_camera* cam, int mode, const float* render, const float* alpha,
                         const float* gt_rgb, const float* gt_depth, float w_im, float w_depth,
-                        float sil_thres, int use_sil, float inv_n_depth,
+                        float sil_thres, int use_sil, float inv_n_depth, const float* outlier_thresh,
                         float* v_render, float* losses, void* stream);
+
+/* *thresh_out = factor * median(|gt_d - d| * (gt_d > 0)) over all pixels (torch.median = lower median;
+ * splatam.py:552-553 uses factor 10).  render_depth: DEVICE [H,W] plane (render + 3*H*W); scratch: DEVICE
+ * float[2*H*W]; sort_temp: isogs_temp_bytes(0, H*W, ...) sort bytes suffice.  No host sync. */
+int isogs_depth_outlier_threshold(const isogs_camera* cam, const float* render_depth, const float* gt_depth,
+                                  float factor, float* scratch, void* sort_temp, size_t sort_temp_bytes,
+                                  float* thresh_out, void* stream);
 
 /* fused SSIM term of the mapping colour loss 0.8*L1 + 0.2*(1 - SSIM): replaces calc_ssim / _ssim
  * (python_ordinary/utils/slam_external.py:54-97; call site splatam.py:568) and its autograd backward

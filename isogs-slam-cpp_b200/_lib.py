@@ -70,7 +70,9 @@ _SIGS = {
     "isogs_blend_bwd": (C.c_int, [C.POINTER(Camera), _I32, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "isogs_preprocess_bwd": (C.c_int, [C.POINTER(Camera), C.POINTER(Pose), _VP, _I64, _VP, _VP, _I32, _VP, _VP, _I32,
                                        _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
-    "isogs_loss_l1_fused": (C.c_int, [C.POINTER(Camera), _I32, _VP, _VP, _VP, _VP, _F, _F, _F, _I32, _F, _VP, _VP, _VP]),
+    "isogs_loss_l1_fused": (C.c_int, [C.POINTER(Camera), _I32, _VP, _VP, _VP, _VP, _F, _F, _F, _I32, _F, _VP, _VP, _VP,
+                                    _VP]),
+    "isogs_depth_outlier_threshold": (C.c_int, [C.POINTER(Camera), _VP, _VP, _F, _VP, _VP, _SZ, _VP, _VP]),
     "isogs_ssim_loss_fused": (C.c_int, [C.POINTER(Camera), _VP, _VP, _F, _VP, _VP, _VP, _VP, _VP]),
     "isogs_adam_fused": (C.c_int, [C.POINTER(AdamGroup), _I32, _F, _F, _F, _I32, _VP]),
     "isogs_pose_keep_best": (C.c_int, [_VP, _VP, _VP, _VP]),

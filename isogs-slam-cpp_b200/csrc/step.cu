@@ -3,6 +3,7 @@
 // References: python_ordinary/scripts/splatam.py:534-570,747-749 (loss), :402-408 (Adam),
 // :799-841,298-348,763-796 (densify); python_ordinary/utils/slam_external.py:139-188 (prune);
 // cpp/cuda/kernels/optimizer.cu:15-98; cpp/src/core/gaussian_model.cpp:291-331.
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
 #include <cmath>
@@ -19,9 +20,11 @@ __device__ __forceinline__ float sgnf(float d) { return (d > 0.f) ? 1.f : ((d < 
 __global__ void __launch_bounds__(256)
 loss_l1_kernel(int64_t P, int mode, const float* __restrict__ render, const float* __restrict__ alpha,
                const float* __restrict__ gt_rgb, const float* __restrict__ gt_depth, float w_im, float w_depth,
-               float sil_thres, int use_sil, float inv_nd, float inv_nc, float* __restrict__ v_render,
-               float* __restrict__ losses) {
+               float sil_thres, int use_sil, float inv_nd, float inv_nc, const float* __restrict__ outlier_thresh,
+               float* __restrict__ v_render, float* __restrict__ losses) {
     float sum_d = 0.f, sum_c = 0.f, cnt = 0.f;
+    const bool outl = outlier_thresh != nullptr;
+    const float othr = outl ? *outlier_thresh : 0.f;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < P; i += (int64_t)gridDim.x * blockDim.x) {
         const float d = render[3 * P + i], d2 = render[4 * P + i];
         const float gd = gt_depth[i];
@@ -29,12 +32,13 @@ loss_l1_kernel(int64_t P, int mode, const float* __restrict__ render, const floa
         const bool nan_ok = !(isnan(d) || isnan(unc));
         bool m = (gd > 0.f) && nan_ok;
         bool mc = true;
+        const float dd = d - gd;
+        if (outl) m = m && (fabsf(dd) < othr);               // ignore_outlier_depth_loss, splatam.py:551-554
         if (mode == 0) {
             if (use_sil) m = m && (alpha[i] > sil_thres);
-            mc = use_sil ? m : true;
+            mc = (use_sil || outl) ? m : true;               // :563-568
         }
         if (gd > 0.f) cnt += 1.f;
-        const float dd = d - gd;
         if (m) sum_d += fabsf(dd);
         v_render[3 * P + i] = m ? (w_depth * inv_nd) * sgnf(dd) : 0.f;
         v_render[4 * P + i] = 0.f;
@@ -258,17 +262,52 @@ extern "C" int isogs_pose_keep_best(const float* losses, const float* pose, floa
 
 extern "C" int isogs_loss_l1_fused(const isogs_camera* cam, int mode, const float* render, const float* alpha,
                                    const float* gt_rgb, const float* gt_depth, float w_im, float w_depth,
-                                   float sil_thres, int use_sil, float inv_n_depth, float* v_render, float* losses,
-                                   void* stream_) {
+                                   float sil_thres, int use_sil, float inv_n_depth, const float* outlier_thresh,
+                                   float* v_render, float* losses, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (!cam || (mode != 0 && mode != 1)) { set_error("isogs_loss_l1_fused: bad argument"); return ISOGS_E_ARG; }
+    if (mode == 1 && outlier_thresh) {
+        set_error("isogs_loss_l1_fused: the outlier mask is supported for tracking (mode 0) only");
+        return ISOGS_E_ARG;
+    }
     const int64_t P = (int64_t)cam->width * cam->height;
     if (P == 0) return ISOGS_OK;
     const float inv_nd = (mode == 1) ? inv_n_depth : 1.0f;
     const float inv_nc = (mode == 1) ? 1.0f / (float)(3 * P) : 1.0f;
     const int blocks = (int)std::min<int64_t>((P + 255) / 256, 148 * 8);
     loss_l1_kernel<<<blocks, 256, 0, stream>>>(P, mode, render, alpha, gt_rgb, gt_depth, w_im, w_depth, sil_thres,
-                                               use_sil, inv_nd, inv_nc, v_render, losses);
+                                               use_sil, inv_nd, inv_nc, outlier_thresh, v_render, losses);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
+
+// depth_error = |gt - d| * (gt > 0); threshold = factor * lower median (torch.median), splatam.py:552-553
+__global__ void __launch_bounds__(256)
+depth_error_kernel(int64_t P, const float* __restrict__ render_depth, const float* __restrict__ gt_depth,
+                   float* __restrict__ err) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < P) { const float gd = gt_depth[i]; err[i] = fabsf(gd - render_depth[i]) * ((gd > 0.f) ? 1.f : 0.f); }
+}
+__global__ void median_pick_kernel(int64_t P, const float* __restrict__ sorted, float factor, float* out) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) *out = factor * sorted[(P - 1) / 2];
+}
+
+extern "C" int isogs_depth_outlier_threshold(const isogs_camera* cam, const float* render_depth, const float* gt_depth,
+                                             float factor, float* scratch, void* sort_temp, size_t sort_temp_bytes,
+                                             float* thresh_out, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!cam || !render_depth || !gt_depth || !scratch || !thresh_out) {
+        set_error("isogs_depth_outlier_threshold: bad argument");
+        return ISOGS_E_ARG;
+    }
+    const int64_t P = (int64_t)cam->width * cam->height;
+    if (P <= 0 || P >= (1ll << 31)) { set_error("isogs_depth_outlier_threshold: bad image size"); return ISOGS_E_ARG; }
+    depth_error_kernel<<<(unsigned)((P + 255) / 256), 256, 0, stream>>>(P, render_depth, gt_depth, scratch);
+    size_t need = 0;
+    ISOGS_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, need, scratch, scratch + P, (int)P, 0, 32, stream));
+    if (need > sort_temp_bytes) { set_error("sort temp too small (%zu needed)", need); return ISOGS_E_ARG; }
+    ISOGS_CUDA(cub::DeviceRadixSort::SortKeys(sort_temp, sort_temp_bytes, scratch, scratch + P, (int)P, 0, 32, stream));
+    median_pick_kernel<<<1, 32, 0, stream>>>(P, scratch + P, factor, thresh_out);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
 }

@@ -132,6 +132,7 @@ class StepWorkspace:
         self.losses, self.v_pose, self.pose_acc = self.small[0:4], self.small[4:11], self.small[11:27]
         self.ssim = self.small[27:28]                               # mean SSIM of the last map_step(ssim=True)
         self.dmaps = None                                           # [9,H,W] SSIM derivative maps, on first use
+        self.outlier_scratch = None                                 # [2,H,W] depth-error sort buffers, on first use
         self.isect_cap = 0
         self._grow_isects(max(1024, 3 * n_cap))
         # device-side intersection count {n_isects, overflow} + its lagged pinned mirror
@@ -237,9 +238,21 @@ def render_backward(ws, gmap, pose=None, pose_dev=None, ch=5, want_gaussians=Tru
     _mark(marks, "preprocess_bwd")
 
 
-def loss_l1(ws, mode, gt_rgb, gt_depth, inv_n_depth=1.0, w_im=0.5, w_depth=1.0, sil_thres=0.99, use_sil=True):
+def loss_l1(ws, mode, gt_rgb, gt_depth, inv_n_depth=1.0, w_im=0.5, w_depth=1.0, sil_thres=0.99, use_sil=True,
+            ignore_outlier_depth=False):
+    thr = None
+    if ignore_outlier_depth:    # splatam.py:551-554: 10 x median depth error, computed on the device (no sync)
+        P = ws.cam.width * ws.cam.height
+        if ws.outlier_scratch is None:
+            ws.outlier_scratch = torch.empty((2 * P,), dtype=torch.float32, device=ws.device)
+        if ws.sort_b < _lib.temp_bytes(0, P)[1]:
+            ws._grow_isects(max(ws.isect_cap, P))
+        thr = ws.small[28:29]
+        check(lib().isogs_depth_outlier_threshold(C.byref(ws.cam), _ptr(ws.render[3]), _ptr(gt_depth), 10.0,
+                                                  _ptr(ws.outlier_scratch), _ptr(ws.sort_tmp), ws.sort_b, _ptr(thr),
+                                                  _stream()))
     check(lib().isogs_loss_l1_fused(C.byref(ws.cam), mode, _ptr(ws.render), _ptr(ws.alpha), _ptr(gt_rgb),
-                                    _ptr(gt_depth), w_im, w_depth, sil_thres, int(use_sil), inv_n_depth,
+                                    _ptr(gt_depth), w_im, w_depth, sil_thres, int(use_sil), inv_n_depth, _ptr(thr),
                                     _ptr(ws.v_render), _ptr(ws.losses), _stream()))
 
 
@@ -487,11 +500,13 @@ def init_camera_pose(prev1, prev2=None, forward_prop=True):
     return q.astype(np.float32), (t1 + (t1 - t2)).astype(np.float32)
 
 
-def track_step(ws, gmap, ps, gt_rgb, gt_depth, lrs=TRACKING_LRS, eps=1e-8, use_sil=True, sil_thres=0.99):
+def track_step(ws, gmap, ps, gt_rgb, gt_depth, lrs=TRACKING_LRS, eps=1e-8, use_sil=True, sil_thres=0.99,
+               ignore_outlier_depth=False):
     """One tracking iteration (splatam.py:1247-1290): only the pose gets a gradient and a step."""
     ws.small.zero_()
     render_forward(ws, gmap, pose_dev=ps.pose)
-    loss_l1(ws, 0, gt_rgb, gt_depth, 1.0, sil_thres=sil_thres, use_sil=use_sil)
+    loss_l1(ws, 0, gt_rgb, gt_depth, 1.0, sil_thres=sil_thres, use_sil=use_sil,
+            ignore_outlier_depth=ignore_outlier_depth)
     render_backward(ws, gmap, pose_dev=ps.pose, want_gaussians=False, want_pose=True)
     ps.step_count += 1
     arr = (_lib.AdamGroup * 2)()

@@ -699,9 +699,17 @@ extern "C" void orc_preprocess_bwd(const orc_camera* cam, const orc_pose* pose, 
     }
 }
 
+// 10 * torch.median(|gt - d| * (gt > 0)) (splatam.py:552-553; torch.median = lower median)
+extern "C" float orc_depth_outlier_threshold(int64_t P, const float* render_depth, const float* gt_depth, float factor) {
+    std::vector<float> e(P);
+    for (int64_t i = 0; i < P; ++i) e[i] = fabsf(gt_depth[i] - render_depth[i]) * (gt_depth[i] > 0.0f ? 1.0f : 0.0f);
+    std::nth_element(e.begin(), e.begin() + (P - 1) / 2, e.end());
+    return factor * e[(P - 1) / 2];
+}
+
 extern "C" void orc_loss_l1(const orc_camera* cam, int mode, const float* render, const float* alpha,
                             const float* gt_rgb, const float* gt_depth, float w_im, float w_depth, float sil_thres,
-                            int use_sil, float* v_render, double* losses) {
+                            int use_sil, float outlier_thresh, float* v_render, double* losses) {
     const int64_t P = (int64_t)cam->width * cam->height;
     double sum_d = 0.0, sum_c = 0.0;
     int64_t n_d = 0;
@@ -717,11 +725,13 @@ extern "C" void orc_loss_l1(const orc_camera* cam, int mode, const float* render
         bool nan_ok = !(std::isnan(d) || std::isnan(unc)); // splatam.py:541
         bool m = (gt_depth[i] > 0.0f) && nan_ok;
         bool mc = true;
+        float dd = d - gt_depth[i];
+        const bool outl = outlier_thresh >= 0.0f;          // ignore_outlier_depth_loss, :551-554 (tracking)
+        if (outl) m = m && (fabsf(dd) < outlier_thresh);
         if (mode == 0) {
             if (use_sil) m = m && (alpha[i] > sil_thres); // :551-552
-            mc = use_sil ? m : true;                      // :563-568
+            mc = (use_sil || outl) ? m : true;            // :563-568
         }
-        float dd = d - gt_depth[i];
         float sgn_d = (dd > 0.0f) ? 1.0f : ((dd < 0.0f) ? -1.0f : 0.0f);
         if (m) sum_d += (double)fabsf(dd);
         v_render[3 * P + i] = m ? (w_depth * inv_nd) * sgn_d : 0.0f;

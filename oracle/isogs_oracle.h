@@ -107,9 +107,12 @@ void orc_preprocess_bwd(const orc_camera* cam, const orc_pose* pose, int64_t N,
  * mode 0 = tracking (sum over mask = gt_d>0 & !nan & sil>sil_thres), 1 = mapping (mean
  * over gt_d>0 for depth, plain mean for colour).  Writes v_render [5,H,W] and
  * losses[3] = {weighted total, colour term, depth term}. */
+float orc_depth_outlier_threshold(int64_t P, const float* render_depth, const float* gt_depth, float factor);
+
 void orc_loss_l1(const orc_camera* cam, int mode, const float* render /*[5,H,W]*/,
                  const float* alpha, const float* gt_rgb /*[3,H,W]*/, const float* gt_depth /*[H,W]*/,
                  float w_im, float w_depth, float sil_thres, int use_sil,
+                 float outlier_thresh /* < 0: off; splatam.py:551-554 */,
                  float* v_render, double* losses);
 
 /* torch.optim.Adam semantics (bias-corrected, step counted from 1; splatam.py:402-408). */

@@ -159,13 +159,22 @@ def preprocess_bwd(cam, means, scales, quats, opacities, colors, radii, rec, v_r
     return dict(means=v_means, scales=v_scales, quats=v_quats, opacities=v_opac, colors=v_colors, pose=v_pose)
 
 
-def loss_l1(cam, mode, render, alpha, gt_rgb, gt_depth, w_im=0.5, w_depth=1.0, sil_thres=0.99, use_sil=True):
+def depth_outlier_threshold(render_depth, gt_depth, factor=10.0):
+    rd, gd = _f(render_depth), _f(gt_depth)
+    fn = lib().orc_depth_outlier_threshold
+    fn.restype = C.c_float
+    return float(fn(C.c_int64(rd.size), _p(rd), _p(gd), C.c_float(factor)))
+
+
+def loss_l1(cam, mode, render, alpha, gt_rgb, gt_depth, w_im=0.5, w_depth=1.0, sil_thres=0.99, use_sil=True,
+            ignore_outlier_depth=False):
     render, alpha, gt_rgb, gt_depth = _f(render), _f(alpha), _f(gt_rgb), _f(gt_depth)
     v_render = np.empty_like(render)
     losses = np.zeros((3,), np.float64)
+    thr = depth_outlier_threshold(render[3], gt_depth) if ignore_outlier_depth else -1.0
     lib().orc_loss_l1(C.byref(cam), C.c_int(mode), _p(render), _p(alpha), _p(gt_rgb), _p(gt_depth),
                       C.c_float(w_im), C.c_float(w_depth), C.c_float(sil_thres), C.c_int(int(use_sil)),
-                      _p(v_render), _p(losses))
+                      C.c_float(thr), _p(v_render), _p(losses))
     return v_render, losses
 
 

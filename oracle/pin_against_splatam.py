@@ -156,6 +156,8 @@ def frame(shift):
                     0.5 + 0.4 * np.sin(y / 4.0)]).astype(np.float32)
     d = (2.0 + 0.3 * np.sin(x / 11.0) + 0.2 * np.cos(y / 7.0) + shift[2]).astype(np.float32)
     d[10:15, 40:47] = 0.0
+    if shift[2] != 0.0:
+        d[30:36, 10:16] -= 0.8                  # a new foreground object: depth-error outliers for :551-554
     return torch.from_numpy(rgb), torch.from_numpy(d)[None]
 
 
@@ -201,6 +203,15 @@ def main():
         out["track_pose0"] = np.concatenate([params["cam_unnorm_rots"][0, :, 1].detach().numpy(),
                                              params["cam_trans"][0, :, 1].detach().numpy()])
         curr = dict(cam=cam, im=rgb1, depth=d1, id=1, intrinsics=K, w2c=w2c0, iter_gt_w2c_list=[w2c0, w2c0])
+        # one evaluation with ignore_outlier_depth_loss=True (splatam.py:551-554), no optimizer step
+        loss, variables, losses = ref.get_loss(params, curr, variables, 1, dict(im=0.5, depth=1.0), True, 0.99, True,
+                                               True, tracking=True)
+        loss.backward()
+        out["track_outlier_losses"] = np.array([float(loss), float(losses["im"]), float(losses["depth"])], np.float64)
+        out["track_outlier_grad"] = np.concatenate([params["cam_unnorm_rots"].grad[0, :, 1].numpy(),
+                                                    params["cam_trans"].grad[0, :, 1].numpy()])
+        params["cam_unnorm_rots"].grad = None
+        params["cam_trans"].grad = None
         opt = ref.initialize_optimizer(params, TRACK_LRS, tracking=True)
         tl, tg, tp = [], [], []
         for it in range(3):

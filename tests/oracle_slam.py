@@ -83,7 +83,8 @@ class TrackState:
         self.best_loss = 1e20
 
 
-def track_iteration(orc, ocam, params, ts, gt_rgb, gt_depth, lr_rot=4e-4, lr_trans=2e-3, use_sil=True):
+def track_iteration(orc, ocam, params, ts, gt_rgb, gt_depth, lr_rot=4e-4, lr_trans=2e-3, use_sil=True,
+                    ignore_outlier_depth=False):
     """One tracking iteration: sum-L1 with the silhouette mask, pose gradient, Adam on the 7 pose floats,
     best candidate kept as in splatam.py:1287-1290."""
     pose = orc.make_pose(ts.pose[:4], ts.pose[4:])
@@ -91,7 +92,8 @@ def track_iteration(orc, ocam, params, ts, gt_rgb, gt_depth, lr_rot=4e-4, lr_tra
     qs = _quats(params)
     o = orc.render_full(ocam, params["means3D"], params["log_scales"], qs, lo, params["rgb_colors"], ch=5,
                         flags=_flags(orc), pose=pose)
-    v_render, losses = orc.loss_l1(ocam, 0, o["render"], o["alpha"], gt_rgb, gt_depth, use_sil=use_sil)
+    v_render, losses = orc.loss_l1(ocam, 0, o["render"], o["alpha"], gt_rgb, gt_depth, use_sil=use_sil,
+                                   ignore_outlier_depth=ignore_outlier_depth)
     v_rec = orc.blend_bwd(ocam, 5, o["rec"], o["vals"], o["ranges"], o["alpha"], o["last"], v_render)
     g = orc.preprocess_bwd(ocam, params["means3D"], params["log_scales"], qs, lo, params["rgb_colors"], o["radii"],
                            o["rec"], v_rec, ch=5, flags=_flags(orc), pose=pose)

@@ -59,7 +59,7 @@ def test_loss_kernel_matches_oracle(pkg, orc, mode, use_sil):
     losses = torch.zeros((4,), dtype=torch.float32, device="cuda")
     d_render, d_alpha, d_rgb, d_depth = t(render), t(alpha), t(gt_rgb), t(gt_depth)  # keep alive across the call
     pkg._lib.check(pkg.lib().isogs_loss_l1_fused(C.byref(gcam), mode, _ptr(d_render), _ptr(d_alpha), _ptr(d_rgb),
-                                                 _ptr(d_depth), 0.5, 1.0, 0.99, int(use_sil), inv_nd,
+                                                 _ptr(d_depth), 0.5, 1.0, 0.99, int(use_sil), inv_nd, None,
                                                  _ptr(v_render), _ptr(losses), _stream()))
     torch.cuda.synchronize()
     gl = losses.cpu().numpy()

@@ -105,6 +105,17 @@ def test_oracle_tracking_matches_reference(orc, fx):
         assert np.abs(ts.pose - fx["track_poses"][it]).max() < 2e-6, it
 
 
+def test_oracle_outlier_mask_matches_reference(orc, fx):
+    """get_loss(tracking=True, ignore_outlier_depth_loss=True): mask = depth error < 10 x median (splatam.py:551-554)."""
+    ocam = orc.make_camera(*_cam_args(fx))
+    params = {k: fx[f"init_{k}"] for k in GAUSS}
+    ts = osl.TrackState(fx["track_pose0"][:4], fx["track_pose0"][4:])
+    loss, gp = osl.track_iteration(orc, ocam, params, ts, fx["rgb1"], fx["d1"][0], ignore_outlier_depth=True)
+    assert abs(loss - fx["track_outlier_losses"][0]) < 2e-5 * fx["track_outlier_losses"][0]
+    assert fx["track_outlier_losses"][0] < 0.98 * fx["track_losses"][0, 0], "the fixture must contain outliers"
+    assert _relmax(gp, fx["track_outlier_grad"]) < 1e-3
+
+
 def test_oracle_mapping_matches_reference(orc, fx):
     ocam = orc.make_camera(*_cam_args(fx))
     st = osl.new_state({k: fx[f"map_in_{k}"] for k in GAUSS})
@@ -157,6 +168,19 @@ def test_gpu_track_step_matches_reference(fx):
         assert _relmax(ws.v_pose.cpu().numpy(), fx["track_grads"][it]) < 1e-3, it
         assert np.abs(ps.pose.cpu().numpy() - fx["track_poses"][it]).max() < 5e-6, it
     assert not ws.check_overflow(wait=True)
+
+
+@pytest.mark.gpu
+def test_gpu_track_step_outlier_mask_matches_reference(fx):
+    pkg, ss, torch, dev, gcam = _gpu(fx)
+    gmap = ss.GaussianMap({k: fx[f"init_{k}"] for k in GAUSS}, device="cuda")
+    ws = ss.StepWorkspace(gcam, gmap.count, torch.device("cuda"))
+    ps = ss.PoseState(fx["track_pose0"][:4], fx["track_pose0"][4:], "cuda")
+    losses = ss.track_step(ws, gmap, ps, dev(fx["rgb1"]), dev(fx["d1"][0]), ignore_outlier_depth=True)
+    torch.cuda.synchronize()
+    ref = fx["track_outlier_losses"]
+    assert abs(float(losses[0]) - ref[0]) < 1e-4 * ref[0], (float(losses[0]), ref[0])
+    assert _relmax(ws.v_pose.cpu().numpy(), fx["track_outlier_grad"]) < 1e-3
 
 
 @pytest.mark.gpu
