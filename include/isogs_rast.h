@@ -211,6 +211,20 @@ int isogs_densify_emit(int64_t N, int64_t capacity, const int32_t* scratch, floa
 /* dst[i] = dst[i] && src[i] (combine the split-parent mask with isogs_prune_mask before one compaction). */
 int isogs_mask_and(int64_t N, uint8_t* dst, const uint8_t* src, void* stream);
 
+/* keyframe selection by re-projection overlap: replaces keyframe_selection_overlap + get_pointcloud
+ * (python_ordinary/utils/keyframe_selection.py:9-95; cpp/src/utils/keyframe_selection.cpp) up to the final
+ * host-side ranking.  Samples n_samples valid-depth pixels of gt_depth (sample_idx: DEVICE int32[n] flat pixel
+ * indices = the reference's torch.randint draw, or null: drawn on the device from `seed`), back-projects them
+ * with the inverse of cur_w2c (HOST float[12], row-major 3x4 [R|t]), removes points that coincide with another
+ * sample or with the origin after |round(.,4)| (the reference's unique/isin filter), and writes for each
+ * keyframe (kf_w2c: DEVICE [K,12]) the fraction projecting inside the image minus `edge` pixels with z > 0.
+ * scratch_i: DEVICE int32[H*W + n]; scratch_f: DEVICE float[6n]; percent_inside: DEVICE float[K].  No sync.
+ * The caller ranks (descending), keeps > 0 and draws k of them (keyframe_selection.py:86-93). */
+int isogs_keyframe_overlap(const isogs_camera* cam, const float* gt_depth, const float* cur_w2c,
+                           const int32_t* sample_idx, int n_samples, uint64_t seed, const float* kf_w2c,
+                           int n_keyframes, int edge, int32_t* scratch_i, float* scratch_f, void* scan_temp,
+                           size_t scan_temp_bytes, float* percent_inside, void* stream);
+
 /* best-candidate selection of the tracking loop (python_ordinary/scripts/splatam.py:1287-1290),
  * on the device so the loop needs no host sync: if losses[0] (evaluated BEFORE this iteration's
  * Adam step) < best[7], then best[0..6] = pose (the values AFTER the step) and best[7] = losses[0].

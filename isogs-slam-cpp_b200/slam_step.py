@@ -468,6 +468,36 @@ def densify(ws, gmap, it, scene_radius, dd=DENSIFY_DEFAULTS, seed=0, noise=None,
     return out
 
 
+def keyframe_overlap(cam, gt_depth, cur_w2c, kf_w2cs, pixels=1600, seed=0, sample_idx=None, edge=20):
+    """percent_inside of keyframe_selection_overlap (keyframe_selection.py:40-84) for every keyframe, on the
+    device: DEVICE float[K].  cur_w2c: 4x4 (or 3x4) array-like; kf_w2cs: [K,4,4] / [K,3,4] array-like or tensor."""
+    import numpy as np
+    dev = gt_depth.device
+    P = cam.width * cam.height
+    kf = torch.as_tensor(np.asarray(kf_w2cs, dtype=np.float32)[:, :3, :4].copy()).contiguous().to(dev)
+    K = kf.shape[0]
+    w2c = (C.c_float * 12)(*np.asarray(cur_w2c, dtype=np.float32)[:3, :4].reshape(-1).tolist())
+    si = torch.empty((P + pixels,), dtype=torch.int32, device=dev)
+    sf = torch.empty((6 * pixels,), dtype=torch.float32, device=dev)
+    sb, _ = _lib.temp_bytes(P, 0)
+    tmp = torch.empty((sb,), dtype=torch.uint8, device=dev)
+    out = torch.zeros((max(K, 1),), dtype=torch.float32, device=dev)
+    check(lib().isogs_keyframe_overlap(C.byref(cam), _ptr(gt_depth), w2c, _ptr(sample_idx), pixels, seed, _ptr(kf), K,
+                                       edge, _ptr(si), _ptr(sf), _ptr(tmp), sb, _ptr(out), _stream()))
+    return out[:K]
+
+
+def select_keyframes(cam, gt_depth, cur_w2c, kf_w2cs, k, pixels=1600, seed=0, rng=None, sample_idx=None):
+    """keyframe_selection_overlap (keyframe_selection.py:40-95): rank by overlap (stable, descending), keep those
+    with overlap > 0, return a random choice of k of them (one host read of K floats)."""
+    import numpy as np
+    pct = keyframe_overlap(cam, gt_depth, cur_w2c, kf_w2cs, pixels, seed, sample_idx).cpu().numpy()
+    order = sorted(range(len(pct)), key=lambda i: pct[i], reverse=True)
+    sel = [i for i in order if pct[i] > 0.0]
+    rng = rng or np.random
+    return list(rng.permutation(np.array(sel, dtype=np.int64))[:k])
+
+
 class PoseState:
     """cam_unnorm_rots / cam_trans of the frame being tracked, on the device, with Adam moments."""
 

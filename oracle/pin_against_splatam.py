@@ -130,7 +130,7 @@ def load_reference():
     stub.GaussianRasterizer = GaussianRasterizer
     sys.modules["diff_gaussian_rasterization"] = stub
     for name in ("matplotlib", "matplotlib.pyplot", "wandb", "datasets", "datasets.gradslam_datasets",
-                 "utils.eval_helpers", "utils.keyframe_selection", "imageio", "natsort", "kornia", "open3d",
+                 "utils.eval_helpers", "imageio", "natsort", "kornia", "open3d",
                  "pytorch_msssim", "lpips", "torchmetrics", "plyfile"):
         if name not in sys.modules:
             sys.modules[name] = mock.MagicMock(name=name)
@@ -330,6 +330,44 @@ def main():
         st = dopt.state[dp["means3D"]]
         out["dens_out_m_means3D"] = st["exp_avg"].numpy().copy()
         out["dens_out_accum"] = dvars["means2D_gradient_accum"].numpy().copy()
+        # --- keyframe selection by overlap (utils/keyframe_selection.py:40-95); the sampled pixel indices and the
+        # per-keyframe percentages are captured (torch.randint wrapped, module-level `sorted` shadowed) ---
+        import builtins
+        import utils.keyframe_selection as ks
+        cap = {}
+        real_randint = torch.randint
+
+        def capture_randint(*a, **kw):
+            r = real_randint(*a, **kw)
+            cap["indices"] = r.clone()
+            return r
+
+        def capture_sorted(lst, **kw):
+            cap["percent"] = [float(d["percent_inside"]) for d in lst]
+            return builtins.sorted(lst, **kw)
+        cur_w2c = torch.eye(4)
+        cur_w2c[:3, :3] = ref.build_rotation(torch.nn.functional.normalize(torch.tensor([[1.0, 0.02, -0.03, 0.01]])))[0]
+        cur_w2c[:3, 3] = torch.tensor([0.05, -0.02, 0.1])
+        kfs = []
+        for j in range(6):                                      # from nearly identical views to one looking away
+            m = torch.eye(4)
+            q = torch.nn.functional.normalize(torch.tensor([[1.0, 0.03 * j, 0.12 * j, -0.02 * j]]))
+            m[:3, :3] = ref.build_rotation(q)[0]
+            m[:3, 3] = torch.tensor([0.1 * j, -0.05 * j, 0.15 * j])
+            kfs.append({"est_w2c": m})
+        m = torch.eye(4)
+        m[:3, :3] = torch.diag(torch.tensor([-1.0, 1.0, -1.0]))  # looking backwards: no overlap
+        kfs.append({"est_w2c": m})
+        torch.randint, ks.sorted = capture_randint, capture_sorted
+        try:
+            sel = ks.keyframe_selection_overlap(d1, cur_w2c, K, kfs, len(kfs), pixels=400)
+        finally:
+            torch.randint = real_randint
+            del ks.sorted
+        valid = torch.stack(torch.where(d1[0] > 0), dim=1)[cap["indices"]]
+        out.update(kf_cur_w2c=cur_w2c.numpy().copy(), kf_w2cs=np.stack([k_["est_w2c"].numpy() for k_ in kfs]),
+                   kf_sample_idx=(valid[:, 0] * W + valid[:, 1]).numpy().astype(np.int32),
+                   kf_percent=np.array(cap["percent"], np.float32), kf_selected=np.array(sorted(int(i) for i in sel)))
     out["notes"] = np.array("tracking: get_loss(tracking=True, use_sil_for_loss=True, sil_thres=0.99, im=0.5, depth=1); "
                             "mapping: get_loss(mapping=True), colour term 0.8*L1 + 0.2*(1-SSIM), im=0.5, depth=1, flat=iso=0; "
                             "rasterizer = CPU oracle behind the reference's diff_gaussian_rasterization interface")

@@ -34,6 +34,17 @@ def centre(q, t):
     return -R.T @ np.asarray(t, np.float64)
 
 
+def w2c_of(q, t):
+    q = np.asarray(q, np.float64) / np.linalg.norm(q)
+    w, x, y, z = q
+    M = np.eye(4, dtype=np.float32)
+    M[:3, :3] = [[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+                 [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                 [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]]
+    M[:3, 3] = np.asarray(t, np.float32)
+    return M
+
+
 def ate_rmse(est, gt):
     est, gt = np.asarray(est).T, np.asarray(gt).T       # Horn alignment, eval_helpers.py:24-78
     me, mg = est.mean(1, keepdims=True), gt.mean(1, keepdims=True)
@@ -83,7 +94,13 @@ def run(shape="tum", frames=50, track_iters=40, map_iters=40, map_every=5, kf_ev
             added_total += ss.add_new_gaussians(ws, gmap, poses[-1], rgb, depth, seed=seed + f)
             gmap.reset_optimizer()
             cur = dict(rgb=rgb, depth=depth, pose=poses[-1], inv_nd=1.0 / max(1, int((d > 0).sum())))
-            sel = keyframes[-(window - 1):] + [cur]
+            # keyframe_selection_overlap on keyframe_list[:-1] + last keyframe + current frame (splatam.py:1391-1401)
+            sel = []
+            if len(keyframes) > 1:
+                ids = ss.select_keyframes(cam, depth, w2c_of(*poses[-1]), [w2c_of(*k["pose"]) for k in keyframes[:-1]],
+                                          k=window - 2, seed=seed + f, rng=rng)
+                sel = [keyframes[int(i)] for i in ids]
+            sel = sel + [keyframes[-1], cur]
             torch.cuda.synchronize(); t0 = time.perf_counter()
             for it in range(map_iters):
                 if it in (0, 20):                                                  # configs/replica/splatam.py:119-128

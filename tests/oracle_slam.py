@@ -133,3 +133,29 @@ def pose_to_centre(q, t):
                   [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
                   [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
     return -R.T @ np.asarray(t, np.float64)
+
+
+def keyframe_overlap(depth, intr, cur_w2c, kf_w2cs, sample_idx, edge=20):
+    """percent_inside of keyframe_selection_overlap (python_ordinary/utils/keyframe_selection.py:9-84) in numpy
+    float32: back-projection of the sampled pixels, the unique/isin duplicate filter, projection into each
+    keyframe.  depth [H,W]; intr = (W, H, fx, fy, cx, cy); sample_idx flat pixel indices."""
+    W, H, fx, fy, cx, cy = intr
+    f32 = np.float32
+    ys, xs = (sample_idx // int(W)).astype(np.int64), (sample_idx % int(W)).astype(np.int64)
+    z = depth[ys, xs].astype(f32)
+    pc = np.stack([(xs.astype(f32) - f32(cx)) / f32(fx) * z, (ys.astype(f32) - f32(cy)) / f32(fy) * z, z], -1)
+    c2w = np.linalg.inv(np.asarray(cur_w2c, np.float64)).astype(f32)
+    pts = (pc @ c2w[:3, :3].T + c2w[:3, 3]).astype(f32)
+    key = np.abs(np.rint(pts * f32(1e4)) / f32(1e4))
+    _, inv, counts = np.unique(np.concatenate([key, np.zeros((1, 3), f32)]), axis=0, return_inverse=True,
+                               return_counts=True)
+    valid = counts[inv.reshape(-1)[:len(key)]] == 1
+    pts = pts[valid]
+    out = []
+    for M in np.asarray(kf_w2cs, f32):
+        p = pts @ M[:3, :3].T + M[:3, 3]
+        pz = p[:, 2] + f32(1e-5)
+        u, v = (f32(fx) * p[:, 0] + f32(cx) * p[:, 2]) / pz, (f32(fy) * p[:, 1] + f32(cy) * p[:, 2]) / pz
+        m = (u < W - edge) & (u > edge) & (v < H - edge) & (v > edge) & (pz > 0)
+        out.append(m.sum() / max(1, len(pts)))
+    return np.array(out, f32)

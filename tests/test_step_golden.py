@@ -141,6 +141,13 @@ def test_init_camera_pose_matches_reference(fx):
     assert np.abs(np.concatenate([q, t]) - fx["init_pose2"]).max() < 1e-6
 
 
+def test_oracle_keyframe_overlap_matches_reference(fx):
+    """keyframe_selection_overlap (utils/keyframe_selection.py:40-95) with the reference's own pixel draw."""
+    pct = osl.keyframe_overlap(fx["d1"][0], fx["intr"], fx["kf_cur_w2c"], fx["kf_w2cs"], fx["kf_sample_idx"])
+    assert np.abs(pct - fx["kf_percent"]).max() < 1e-6
+    assert sorted(np.nonzero(pct > 0)[0].tolist()) == fx["kf_selected"].tolist()
+
+
 # ------------------------------------------------------------------ GPU: product path vs fixture
 def _gpu(fx):
     import importlib
@@ -321,3 +328,19 @@ def test_gpu_densify_matches_reference(fx):
     assert same.sum() >= gmap2.count - 2 * n_split and np.isfinite(a).all()
     spread = np.abs(a - b)[~same]
     assert 0.0 < spread.mean() < 0.2                               # scales are 0.005 .. 0.08
+
+
+@pytest.mark.gpu
+def test_gpu_keyframe_overlap_matches_reference(fx):
+    pkg, ss, torch, dev, gcam = _gpu(fx)
+    depth = dev(fx["d1"][0])
+    idx = torch.from_numpy(fx["kf_sample_idx"]).cuda()
+    pct = ss.keyframe_overlap(gcam, depth, fx["kf_cur_w2c"], fx["kf_w2cs"], pixels=len(fx["kf_sample_idx"]),
+                              sample_idx=idx).cpu().numpy()
+    assert np.abs(pct - fx["kf_percent"]).max() < 1e-6, (pct, fx["kf_percent"])
+    rng = np.random.RandomState(0)
+    sel = ss.select_keyframes(gcam, depth, fx["kf_cur_w2c"], fx["kf_w2cs"], k=2, pixels=len(idx), rng=rng, sample_idx=idx)
+    assert len(sel) == 2 and set(int(i) for i in sel) <= set(fx["kf_selected"].tolist())
+    # device-side sampling: a different draw of the same statistic (4000 samples -> tighter than the 400 of the fixture)
+    pct2 = ss.keyframe_overlap(gcam, depth, fx["kf_cur_w2c"], fx["kf_w2cs"], pixels=4000, seed=5).cpu().numpy()
+    assert np.all((pct2 > 0) == (fx["kf_percent"] > 0)) and np.abs(pct2 - fx["kf_percent"]).max() < 0.05
