@@ -225,6 +225,34 @@ int isogs_keyframe_overlap(const isogs_camera* cam, const float* gt_depth, const
                            int n_keyframes, int edge, int32_t* scratch_i, float* scratch_f, void* scan_temp,
                            size_t scan_temp_bytes, float* percent_inside, void* stream);
 
+/* ---- IsoGS geometric losses: flat + iso-surface density, three-axis scales only ---- */
+
+/* Exact 16-nearest-neighbour search among the N Gaussian centres for Q query centres: replaces the chunked
+ * torch.cdist + topk of compute_iso_surface_loss_sampled (python_ordinary/scripts/splatam.py:203-208) and the
+ * spatial hash of cpp/cuda/kernels/spatial_hash.cu.  A uniform grid (at most res+1 cells per axis over the
+ * bounding box of the centres) is rebuilt on the device on every call; no host sync.
+ * query_idx: DEVICE int32[Q] (nullable).  If null and sampled_idx (DEVICE int32[Q]) is given, Q centres are
+ * drawn from `seed` (with replacement; the reference uses randperm) and written there; if both are null the
+ * queries are centres 0..Q-1 (Q must be N: the reference's N < 8192 case, :654-656).
+ * grid / sorted: DEVICE scratch of isogs_knn_workspace bytes (sorted 16-byte aligned); scan_temp must hold a
+ * CUB scan of (res+1)^3 + 1 ints (isogs_temp_bytes with that N).  nbr: DEVICE int32[Q,16], nearest first,
+ * -1 padded when N < 16. */
+int isogs_knn_workspace(int64_t N, int res, size_t* grid_bytes, size_t* sorted_bytes);
+int isogs_knn16(int64_t N, const float* means, int res, int Q, const int32_t* query_idx, uint64_t seed,
+                int32_t* sampled_idx, int32_t* grid, float* sorted, void* scan_temp, size_t scan_temp_bytes,
+                int32_t* nbr, void* stream);
+
+/* flat = mean_i min_k clamp(exp(log_scales_ik), 1e-5)  (compute_flat_loss, splatam.py:42-54,580-583) and
+ * iso = mean_q (sum_{j in nbr_q} sigmoid(o_j) exp(-1/2 d^T R_j (S_j^2 + 1e-8)^-1 R_j^T d) - target)^2
+ * (splatam.py:612-668), d = mu_q - mu_j.  losses (nullable): losses[0] += w_flat*flat + w_iso*iso
+ * (reference weights 50 / 2, :733-739).  out: DEVICE float[3], += {flat, iso, mean density} (caller zeroes).
+ * g_*: gradients of the weighted sum, ACCUMULATED into [N,3] / [N,3] / [N,4] / [N] (all four or none);
+ * call after isogs_preprocess_bwd, which overwrites the gradient buffers. */
+int isogs_iso_flat_loss(int64_t N, const float* means, const float* log_scales, const float* quats,
+                        const float* logit_opac, int Q, const int32_t* query_idx, const int32_t* nbr,
+                        float w_iso, float w_flat, float target, float* g_means, float* g_log_scales,
+                        float* g_quats, float* g_logit_opac, float* losses, float* out, void* stream);
+
 /* best-candidate selection of the tracking loop (python_ordinary/scripts/splatam.py:1287-1290),
  * on the device so the loop needs no host sync: if losses[0] (evaluated BEFORE this iteration's
  * Adam step) < best[7], then best[0..6] = pose (the values AFTER the step) and best[7] = losses[0].

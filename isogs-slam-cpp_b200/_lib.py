@@ -82,6 +82,10 @@ _SIGS = {
     "isogs_mask_and": (C.c_int, [_I64, _VP, _VP, _VP]),
     "isogs_keyframe_overlap": (C.c_int, [C.POINTER(Camera), _VP, C.POINTER(C.c_float), _VP, _I32, C.c_uint64, _VP, _I32,
                                          _I32, _VP, _VP, _VP, _SZ, _VP, _VP]),
+    "isogs_knn_workspace": (C.c_int, [_I64, _I32, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    "isogs_knn16": (C.c_int, [_I64, _VP, _I32, _I32, _VP, C.c_uint64, _VP, _VP, _VP, _VP, _SZ, _VP, _VP]),
+    "isogs_iso_flat_loss": (C.c_int, [_I64, _VP, _VP, _VP, _VP, _I32, _VP, _VP, _F, _F, _F, _VP, _VP, _VP, _VP, _VP,
+                                      _VP, _VP]),
     "isogs_prune_mask": (C.c_int, [_I64, _VP, _VP, _I32, _F, _F, _VP, _VP]),
     "isogs_compact": (C.c_int, [_I64, _VP, C.POINTER(Rows), _I32, _VP, _VP, _SZ, _VP, _VP]),
     "isogs_backproject_append": (C.c_int, [C.POINTER(Camera), C.POINTER(Pose), _VP, _VP, _VP, _VP, _F, _F, _VP, _VP,

@@ -140,6 +140,28 @@ __device__ __forceinline__ void quat_to_R(const float* q, float* R, float* qn, f
     R[6] = 2.0f * (xz - wy);        R[7] = 2.0f * (yz + wx);        R[8] = 1.0f - 2.0f * (x2 + y2);
 }
 
+// VJP of quat_to_R w.r.t. the UN-normalised quaternion (accumulates into v_q)
+__device__ __forceinline__ void quat_to_R_vjp(const float* q, const float* vR, float* v_q) {
+    float w = q[0], x = q[1], y = q[2], z = q[3];
+    float n = sqrtf(((w * w + x * x) + y * y) + z * z);
+    float inv = 1.0f / n;
+    w *= inv; x *= inv; y *= inv; z *= inv;
+#define G(r, c) vR[(r) * 3 + (c)]
+    float vw = 2.f * (x * (G(2, 1) - G(1, 2)) + y * (G(0, 2) - G(2, 0)) + z * (G(1, 0) - G(0, 1)));
+    float vx = 2.f * (-2.f * x * (G(1, 1) + G(2, 2)) + y * (G(1, 0) + G(0, 1)) + z * (G(2, 0) + G(0, 2)) +
+                      w * (G(2, 1) - G(1, 2)));
+    float vy = 2.f * (x * (G(1, 0) + G(0, 1)) - 2.f * y * (G(0, 0) + G(2, 2)) + z * (G(2, 1) + G(1, 2)) +
+                      w * (G(0, 2) - G(2, 0)));
+    float vz = 2.f * (x * (G(2, 0) + G(0, 2)) + y * (G(2, 1) + G(1, 2)) - 2.f * z * (G(0, 0) + G(1, 1)) +
+                      w * (G(1, 0) - G(0, 1)));
+#undef G
+    float dot = vw * w + vx * x + vy * y + vz * z;
+    v_q[0] += (vw - dot * w) * inv;
+    v_q[1] += (vx - dot * x) * inv;
+    v_q[2] += (vy - dot * y) * inv;
+    v_q[3] += (vz - dot * z) * inv;
+}
+
 __device__ __forceinline__ void xform(const float* R, const float* t, const float* p, float* o) {
     o[0] = ((R[0] * p[0] + R[1] * p[1]) + R[2] * p[2]) + t[0];
     o[1] = ((R[3] * p[0] + R[4] * p[1]) + R[5] * p[2]) + t[1];

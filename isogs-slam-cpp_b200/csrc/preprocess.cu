@@ -55,27 +55,6 @@ preprocess_fwd_kernel(DevCam cam, DevPose pose, int64_t N, const float* __restri
 // backward
 // ---------------------------------------------------------------------------------------------
 
-__device__ __forceinline__ void quat_to_R_vjp(const float* q, const float* vR, float* v_q) {
-    float w = q[0], x = q[1], y = q[2], z = q[3];
-    float n = sqrtf(((w * w + x * x) + y * y) + z * z);
-    float inv = 1.0f / n;
-    w *= inv; x *= inv; y *= inv; z *= inv;
-#define G(r, c) vR[(r) * 3 + (c)]
-    float vw = 2.f * (x * (G(2, 1) - G(1, 2)) + y * (G(0, 2) - G(2, 0)) + z * (G(1, 0) - G(0, 1)));
-    float vx = 2.f * (-2.f * x * (G(1, 1) + G(2, 2)) + y * (G(1, 0) + G(0, 1)) + z * (G(2, 0) + G(0, 2)) +
-                      w * (G(2, 1) - G(1, 2)));
-    float vy = 2.f * (x * (G(1, 0) + G(0, 1)) - 2.f * y * (G(0, 0) + G(2, 2)) + z * (G(2, 1) + G(1, 2)) +
-                      w * (G(0, 2) - G(2, 0)));
-    float vz = 2.f * (x * (G(2, 0) + G(0, 2)) + y * (G(2, 1) + G(1, 2)) - 2.f * z * (G(0, 0) + G(1, 1)) +
-                      w * (G(1, 0) - G(0, 1)));
-#undef G
-    float dot = vw * w + vx * x + vy * y + vz * z;
-    v_q[0] += (vw - dot * w) * inv;
-    v_q[1] += (vx - dot * x) * inv;
-    v_q[2] += (vy - dot * y) * inv;
-    v_q[3] += (vz - dot * z) * inv;
-}
-
 // pose_acc layout: [0..8] dL/dRp, [9..11] dL/dtp, [12..15] dL/dqn (through quat_mul, aniso only)
 template <bool ISO>
 __global__ void __launch_bounds__(256)

@@ -265,6 +265,50 @@ def loss_ssim(ws, gt_rgb, weight):
                                       _ptr(ws.v_render), _ptr(ws.losses), _ptr(ws.ssim), _stream()))
 
 
+def iso_flat_loss(ws, gmap, w_flat=50.0, w_iso=2.0, seed=0, query_idx=None, sample_size=8192, res=None,
+                  with_grad=True):
+    """The IsoGS geometric terms of get_loss (splatam.py:572-675, weights :733-739): losses[0] += 50 * flat +
+    2 * iso and their gradients accumulated into gmap.g (call after render_backward).  Exact 16-NN through a
+    device-built uniform grid instead of the reference's 8192 x N cdist.  ws.geo receives {flat, iso, mean
+    density}; ws.nbr the neighbour table.  Three-axis scales only (the reference skips both terms otherwise)."""
+    if gmap.isotropic:
+        raise ValueError("iso / flat losses need three-axis scales (splatam.py:586,615)")
+    N, dev = gmap.count, gmap.device
+    if query_idx is not None:
+        Q = int(query_idx.numel())
+    else:
+        Q = N if N < sample_size else sample_size          # :648-656
+    if res is None:
+        res = max(8, min(160, int(round(1.28 * N ** (1.0 / 3.0)))))
+    key = (N, Q, res)
+    if getattr(ws, "_geo_key", None) != key:
+        gb, sb = C.c_size_t(0), C.c_size_t(0)
+        check(lib().isogs_knn_workspace(N, res, C.byref(gb), C.byref(sb)))
+        ws.knn_grid = torch.empty((gb.value // 4,), dtype=torch.int32, device=dev)
+        ws.knn_sorted = torch.empty((sb.value // 4,), dtype=torch.float32, device=dev)
+        ws.knn_scan_b, _ = _lib.temp_bytes((res + 1) ** 3 + 1, 0)
+        ws.knn_scan = torch.empty((ws.knn_scan_b,), dtype=torch.uint8, device=dev)
+        ws.nbr = torch.empty((Q, 16), dtype=torch.int32, device=dev)
+        ws.query_idx = torch.empty((Q,), dtype=torch.int32, device=dev)
+        ws._geo_key = key
+    L, st = lib(), _stream()
+    sampled = None
+    if query_idx is None and Q != N:
+        sampled, qptr = ws.query_idx, None
+    else:
+        qptr = query_idx
+    check(L.isogs_knn16(N, _ptr(gmap.p["means3D"]), res, Q, _ptr(qptr), seed, _ptr(sampled), _ptr(ws.knn_grid),
+                        _ptr(ws.knn_sorted), _ptr(ws.knn_scan), ws.knn_scan_b, _ptr(ws.nbr), st))
+    q_used = qptr if qptr is not None else sampled
+    ws.geo = ws.small[29:32]
+    ws.geo.zero_()
+    g = gmap.g if with_grad else {}
+    check(L.isogs_iso_flat_loss(N, _ptr(gmap.p["means3D"]), _ptr(gmap.p["log_scales"]), _ptr(gmap.p["unnorm_rotations"]),
+                                _ptr(gmap.p["logit_opacities"]), Q, _ptr(q_used), _ptr(ws.nbr), w_iso, w_flat, 1.0,
+                                _ptr(g.get("means3D")), _ptr(g.get("log_scales")), _ptr(g.get("unnorm_rotations")),
+                                _ptr(g.get("logit_opacities")), _ptr(ws.losses), _ptr(ws.geo), st))
+
+
 def adam_gaussians(gmap, lrs=MAPPING_LRS, eps=1e-15, beta1=0.9, beta2=0.999):
     gmap.step_count += 1
     names = gmap.grad_names
@@ -287,11 +331,13 @@ def _mark(marks, name):
 
 
 def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, allreduce=None, marks=None, w_im=0.5,
-             w_depth=1.0, ssim=False):
+             w_depth=1.0, ssim=False, isoflat=False, iso_seed=0):
     """One mapping iteration on one keyframe (splatam.py:1412-1476, L1 terms).  `pose` is the keyframe's
     HOST pose (camera_grad=False).  `allreduce(flat_grad_tensor)` is called between backward and Adam.
     `marks` (a list) receives (stage, cuda event) pairs for per-stage timing.  `w_im` weighs the mean colour
-    term; `ssim=True` makes that term the reference's 0.8 * L1 + 0.2 * (1 - SSIM) (splatam.py:568), else pure L1."""
+    term; `ssim=True` makes that term the reference's 0.8 * L1 + 0.2 * (1 - SSIM) (splatam.py:568), else pure L1;
+    `isoflat=True` adds 50 * flat + 2 * iso (:572-675,733-739; three-axis scales) -- with both flags the loss is the
+    reference's complete mapping loss."""
     _mark(marks, "begin")
     ws.small.zero_()
     render_forward(ws, gmap, pose=pose, marks=marks)
@@ -302,6 +348,9 @@ def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, all
         loss_ssim(ws, gt_rgb, 0.2 * w_im)
         _mark(marks, "ssim")
     render_backward(ws, gmap, pose=pose, want_gaussians=True, marks=marks)
+    if isoflat:
+        iso_flat_loss(ws, gmap, seed=iso_seed)
+        _mark(marks, "isoflat")
     if allreduce is not None:
         allreduce(gmap.grad_flat[:gmap.grad_used])
         _mark(marks, "allreduce")

@@ -833,6 +833,112 @@ extern "C" double orc_ssim(int W, int H, const float* x, const float* y, float c
     return total / (3.0 * (double)P);
 }
 
+// IsoGS geometric terms (python_ordinary/scripts/splatam.py: compute_flat_loss :42-54, get_loss :572-675,
+// compute_iso_surface_loss_sampled :162-262): brute-force exact 16-NN (the reference: cdist + topk), density of the
+// neighbours at the query centre, (D - target)^2, flat = mean min clamp(exp(ls), 1e-5).  Double arithmetic; the
+// gradient is the analytic adjoint (the reference gets it from autograd).  out = {flat, iso, mean density};
+// returns w_flat * flat + w_iso * iso.  g_* (all or none) are ACCUMULATED.
+extern "C" double orc_iso_flat_loss(int64_t N, const float* means, const float* log_scales, const float* quats,
+                                    const float* logit_opac, int Q, const int32_t* query_idx, float w_iso, float w_flat,
+                                    float target, float* g_means, float* g_ls, float* g_quats, float* g_logit,
+                                    double* out, int32_t* nbr_out) {
+    const int K = 16;
+    std::vector<double> gm(g_means ? 3 * N : 0, 0.0), gl(g_means ? 3 * N : 0, 0.0), gq(g_means ? 4 * N : 0, 0.0),
+        go(g_means ? N : 0, 0.0);
+    double iso = 0.0, dens = 0.0;
+    for (int q = 0; q < Q; ++q) {
+        const int64_t qi = query_idx ? query_idx[q] : q;
+        std::vector<std::pair<double, int>> dist(N);
+        for (int64_t j = 0; j < N; ++j) {
+            double d2 = 0;
+            for (int k = 0; k < 3; ++k) { double d = (double)means[3 * qi + k] - (double)means[3 * j + k]; d2 += d * d; }
+            dist[j] = {d2, (int)j};
+        }
+        const int kk = (int)std::min<int64_t>(K, N);
+        std::partial_sort(dist.begin(), dist.begin() + kk, dist.end());
+        struct Nb { int j; double d[3], R[9], y[3], s[3], w[3], alpha, e, qn[4], inv; };
+        std::vector<Nb> nb(kk);
+        double D = 0;
+        for (int t = 0; t < kk; ++t) {
+            Nb& b = nb[t];
+            b.j = dist[t].second;
+            if (nbr_out) nbr_out[(int64_t)q * K + t] = b.j;
+            const float* qq = quats + 4 * (int64_t)b.j;
+            double n = std::sqrt((double)qq[0] * qq[0] + (double)qq[1] * qq[1] + (double)qq[2] * qq[2] + (double)qq[3] * qq[3]);
+            b.inv = 1.0 / n;
+            double w = qq[0] * b.inv, x = qq[1] * b.inv, y = qq[2] * b.inv, z = qq[3] * b.inv;
+            b.qn[0] = w; b.qn[1] = x; b.qn[2] = y; b.qn[3] = z;
+            double Rm[9] = {1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                            2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                            2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)};
+            for (int k = 0; k < 9; ++k) b.R[k] = Rm[k];
+            for (int k = 0; k < 3; ++k) b.d[k] = (double)means[3 * qi + k] - (double)means[3 * (int64_t)b.j + k];
+            double quad = 0;
+            for (int k = 0; k < 3; ++k) {
+                b.y[k] = b.R[k] * b.d[0] + b.R[3 + k] * b.d[1] + b.R[6 + k] * b.d[2];
+                b.s[k] = std::max(std::exp((double)log_scales[3 * (int64_t)b.j + k]), 1e-5);
+                b.w[k] = 1.0 / (b.s[k] * b.s[k] + 1e-8);
+                quad += b.w[k] * b.y[k] * b.y[k];
+            }
+            b.alpha = 1.0 / (1.0 + std::exp(-(double)logit_opac[b.j]));
+            b.e = std::exp(-0.5 * quad);
+            D += b.alpha * b.e;
+        }
+        for (int t = kk; t < K && nbr_out; ++t) nbr_out[(int64_t)q * K + t] = -1;
+        const double diff = D - (double)target;
+        iso += diff * diff;
+        dens += D;
+        if (!g_means) continue;
+        const double c = (double)w_iso * 2.0 * diff / (double)Q;
+        for (const Nb& b : nb) {
+            const double g = c * b.alpha * b.e * -0.5;
+            const double u[3] = {b.w[0] * b.y[0], b.w[1] * b.y[1], b.w[2] * b.y[2]};
+            double vR[9];
+            for (int a = 0; a < 3; ++a) {
+                const double dd = 2.0 * g * (b.R[3 * a] * u[0] + b.R[3 * a + 1] * u[1] + b.R[3 * a + 2] * u[2]);
+                gm[3 * qi + a] += dd;
+                gm[3 * (int64_t)b.j + a] -= dd;
+                for (int k = 0; k < 3; ++k) vR[3 * a + k] = 2.0 * g * b.d[a] * u[k];
+            }
+            // adjoint of quaternion -> rotation through the normalisation
+            const double w = b.qn[0], x = b.qn[1], y = b.qn[2], z = b.qn[3];
+#define G(r, c) vR[(r) * 3 + (c)]
+            double vq[4];
+            vq[0] = 2 * (x * (G(2, 1) - G(1, 2)) + y * (G(0, 2) - G(2, 0)) + z * (G(1, 0) - G(0, 1)));
+            vq[1] = 2 * (-2 * x * (G(1, 1) + G(2, 2)) + y * (G(1, 0) + G(0, 1)) + z * (G(2, 0) + G(0, 2)) + w * (G(2, 1) - G(1, 2)));
+            vq[2] = 2 * (x * (G(1, 0) + G(0, 1)) - 2 * y * (G(0, 0) + G(2, 2)) + z * (G(2, 1) + G(1, 2)) + w * (G(0, 2) - G(2, 0)));
+            vq[3] = 2 * (x * (G(2, 0) + G(0, 2)) + y * (G(2, 1) + G(1, 2)) - 2 * z * (G(0, 0) + G(1, 1)) + w * (G(1, 0) - G(0, 1)));
+#undef G
+            const double dot = vq[0] * w + vq[1] * x + vq[2] * y + vq[3] * z;
+            for (int k = 0; k < 4; ++k) gq[4 * (int64_t)b.j + k] += (vq[k] - dot * b.qn[k]) * b.inv;
+            for (int k = 0; k < 3; ++k)
+                if (std::exp((double)log_scales[3 * (int64_t)b.j + k]) >= 1e-5)
+                    gl[3 * (int64_t)b.j + k] += g * b.y[k] * b.y[k] * (-2.0 * b.s[k] * b.w[k] * b.w[k]) * b.s[k];
+            go[b.j] += c * b.e * b.alpha * (1.0 - b.alpha);
+        }
+    }
+    double flat = 0;
+    for (int64_t i = 0; i < N; ++i) {
+        double best = 1e300, raw = 0;
+        int arg = 0;
+        for (int k = 0; k < 3; ++k) {
+            const double ex = std::exp((double)log_scales[3 * i + k]), sc = std::max(ex, 1e-5);
+            if (sc < best) { best = sc; arg = k; raw = ex; }
+        }
+        flat += best;
+        if (g_means && raw >= 1e-5) gl[3 * i + arg] += (double)w_flat * raw / (double)N;
+    }
+    flat /= (double)N;
+    iso = Q > 0 ? iso / Q : 0.0;
+    if (g_means) {
+        for (int64_t i = 0; i < 3 * N; ++i) { g_means[i] += (float)gm[i]; g_ls[i] += (float)gl[i]; }
+        for (int64_t i = 0; i < 4 * N; ++i) g_quats[i] += (float)gq[i];
+        for (int64_t i = 0; i < N; ++i) g_logit[i] += (float)go[i];
+    }
+    out[0] = flat; out[1] = iso; out[2] = Q > 0 ? dens / Q : 0.0;
+    return (double)w_flat * flat + (double)w_iso * iso;
+}
+
 extern "C" void orc_adam(int64_t n, float* p, const float* g, float* m, float* v, float lr, float b1, float b2,
                          float eps, int step) {
     // torch.optim.Adam (single tensor, no amsgrad / weight decay): step counted from 1

@@ -121,6 +121,12 @@ void orc_loss_l1(const orc_camera* cam, int mode, const float* render /*[5,H,W]*
 double orc_ssim(int width, int height, const float* x /*[3,H,W]*/, const float* y /*[3,H,W]*/, float coef,
                 float* v_x /*nullable*/);
 
+/* IsoGS flat + iso-surface density losses (splatam.py:42-54,162-262,572-675); see the .cpp for the math. */
+double orc_iso_flat_loss(int64_t N, const float* means, const float* log_scales, const float* quats,
+                         const float* logit_opac, int Q, const int32_t* query_idx /*nullable: 0..Q-1*/, float w_iso,
+                         float w_flat, float target, float* g_means, float* g_ls, float* g_quats, float* g_logit,
+                         double* out /*[3]*/, int32_t* nbr_out /*[Q,16] nullable*/);
+
 void orc_adam(int64_t n, float* p, const float* g, float* m, float* v, float lr, float b1,
               float b2, float eps, int step);
 

@@ -187,6 +187,28 @@ def ssim(x, y, coef=0.0, v_x=None):
     return float(fn(C.c_int(W), C.c_int(H), _p(x), _p(y), C.c_float(coef), _p(v_x)))
 
 
+def iso_flat_loss(means, log_scales, quats, logit_opac, query_idx=None, w_iso=2.0, w_flat=50.0, target=1.0,
+                  with_grad=True):
+    """Returns (weighted loss, {flat, iso, mean density}, gradient dict or None, neighbour table [Q,16])."""
+    means, log_scales, quats, lo = _f(means), _f(log_scales), _f(quats), _f(logit_opac).reshape(-1)
+    N = means.shape[0]
+    qi = None if query_idx is None else np.ascontiguousarray(query_idx, dtype=np.int32)
+    Q = N if qi is None else qi.shape[0]
+    g = None
+    if with_grad:
+        g = dict(means3D=np.zeros((N, 3), np.float32), log_scales=np.zeros((N, 3), np.float32),
+                 unnorm_rotations=np.zeros((N, 4), np.float32), logit_opacities=np.zeros((N,), np.float32))
+    out = np.zeros((3,), np.float64)
+    nbr = np.empty((Q, 16), np.int32)
+    fn = lib().orc_iso_flat_loss
+    fn.restype = C.c_double
+    gp = (lambda k: _p(g[k])) if with_grad else (lambda k: None)
+    total = fn(C.c_int64(N), _p(means), _p(log_scales), _p(quats), _p(lo), C.c_int(Q), _p(qi), C.c_float(w_iso),
+               C.c_float(w_flat), C.c_float(target), gp("means3D"), gp("log_scales"), gp("unnorm_rotations"),
+               gp("logit_opacities"), _p(out), _p(nbr))
+    return float(total), out, g, nbr
+
+
 def adam(p, g, m, v, lr, b1=0.9, b2=0.999, eps=1e-8, step=1):
     """In-place on p, m, v (float32 contiguous)."""
     lib().orc_adam(C.c_int64(p.size), _p(p), _p(_f(g)), _p(m), _p(v), C.c_float(lr), C.c_float(b1),

