@@ -45,9 +45,19 @@ __global__ void __launch_bounds__(256) bbox_kernel(int64_t N, const float* __res
             lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], off));
             hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], off));
         }
+    // one set of 6 atomics per CTA (the 6 addresses are shared by the whole grid)
+    __shared__ float s_lo[3][8], s_hi[3][8];
     if ((threadIdx.x & 31) == 0)
 #pragma unroll
-        for (int k = 0; k < 3; ++k) { atomicMin(bb + k, f2o(lo[k])); atomicMax(bb + 3 + k, f2o(hi[k])); }
+        for (int k = 0; k < 3; ++k) { s_lo[k][threadIdx.x >> 5] = lo[k]; s_hi[k][threadIdx.x >> 5] = hi[k]; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        const int k = threadIdx.x;
+        float a = s_lo[k][0], b = s_hi[k][0];
+        for (int w = 1; w < 8; ++w) { a = fminf(a, s_lo[k][w]); b = fmaxf(b, s_hi[k][w]); }
+        atomicMin(bb + k, f2o(a));
+        atomicMax(bb + 3 + k, f2o(b));
+    }
 }
 
 // h = largest extent / res, so every axis has at most res + 1 cells (the tables are sized for (res + 1)^3)
@@ -92,55 +102,93 @@ cell_scatter_kernel(int64_t N, const float* __restrict__ means, const GridParams
     sorted[pos] = make_float4(x, y, z, __int_as_float((int)i));
 }
 
-// ---- exact KNN: one warp per query, per-lane sorted candidate lists in shared memory ----------------------
-struct LaneLists { float d[KNN_K][32]; int id[KNN_K][32]; };
+// ---- exact KNN: one warp per query, ONE shared candidate buffer per warp ---------------------------------
+// buf[0..15] = the best 16 so far (ascending after a compaction), buf[16..] = pending candidates that beat the
+// current 16th distance tau.  A round of 32 candidates costs one compare per lane plus a ballot; only when more
+// than 16 are pending does the warp re-select the best 16 (16 rounds of a warp-wide minimum over two registers per
+// lane).  tau drops fast, so later candidates are rejected by the single compare: ~60 accepted out of ~600.
+struct WarpBuf { float d[64]; int id[64]; };
 
-__device__ __forceinline__ void lane_insert(LaneLists& L, int lane, float d2, int id) {
-    int k = KNN_K - 1;
-    while (k > 0 && L.d[k - 1][lane] > d2) { L.d[k][lane] = L.d[k - 1][lane]; L.id[k][lane] = L.id[k - 1][lane]; --k; }
-    L.d[k][lane] = d2; L.id[k][lane] = id;
-}
-
-__device__ __forceinline__ void scan_range(LaneLists& L, int lane, const float4* __restrict__ sorted, int b, int e,
-                                           float qx, float qy, float qz) {
-    for (int p = b + lane; p < e; p += 32) {
-        const float4 v = sorted[p];
-        const float dx = v.x - qx, dy = v.y - qy, dz = v.z - qz;
-        const float d2 = dx * dx + dy * dy + dz * dz;
-        if (d2 < L.d[KNN_K - 1][lane]) lane_insert(L, lane, d2, __float_as_int(v.w));
-    }
-}
-
-// K-way merge of the 32 sorted lane lists: lane t (< 16) ends up holding the t-th nearest (distance, id);
-// returns the 16th smallest distance (warp-uniform)
-__device__ __forceinline__ float merge_lists(const LaneLists& L, int lane, float& out_d, int& out_id) {
-    int hp = 0;
+__device__ __forceinline__ float compact_top16(WarpBuf& B, int lane, int n_total) {
+    __syncwarp();
+    float a = (lane < n_total) ? B.d[lane] : FLT_MAX;
+    int ia = (lane < n_total) ? B.id[lane] : -1;
+    float b = (lane + 32 < n_total) ? B.d[lane + 32] : FLT_MAX;
+    int ib = (lane + 32 < n_total) ? B.id[lane + 32] : -1;
+    __syncwarp();
     float kth = FLT_MAX;
+#pragma unroll 4
     for (int t = 0; t < KNN_K; ++t) {
-        const float v = (hp < KNN_K) ? L.d[hp][lane] : FLT_MAX;
+        const bool useb = b < a;
+        const float v = useb ? b : a;
         const unsigned m = __reduce_min_sync(0xffffffffu, __float_as_uint(v));
         const unsigned who = __ballot_sync(0xffffffffu, __float_as_uint(v) == m);
-        const int src = __ffs(who) - 1;
-        const int cand = (hp < KNN_K) ? L.id[hp][lane] : -1;
-        const int id = __shfl_sync(0xffffffffu, cand, src);
-        if (lane == t) { out_d = __uint_as_float(m); out_id = (m == __float_as_uint(FLT_MAX)) ? -1 : id; }
-        if (lane == src) ++hp;
+        if (lane == __ffs(who) - 1) {
+            B.d[t] = v;
+            B.id[t] = (m == __float_as_uint(FLT_MAX)) ? -1 : (useb ? ib : ia);
+            if (useb) b = FLT_MAX; else a = FLT_MAX;
+        }
         kth = __uint_as_float(m);
     }
+    __syncwarp();
     return kth;
+}
+
+// Scan a batch of up to 32 cell ranges (lane l holds range l: [rb, rb + rl)) as ONE virtual list: the bounds were
+// loaded by different lanes in parallel (one memory latency for the whole batch), an inclusive warp scan of the
+// lengths maps a virtual index to (range, offset), and every lane strides over the concatenation, so the point
+// loads of a shell are independent of each other.
+__device__ __forceinline__ void scan_batch(WarpBuf& B, int lane, const float4* __restrict__ sorted, int rb, int rl,
+                                           float qx, float qy, float qz, float& tau, int& n_pending) {
+    int incl = rl;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += t;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    for (int v = lane; v < ((total + 31) & ~31); v += 32) {
+        // range of virtual index v = number of lanes whose inclusive prefix is <= v (prefixes are monotone:
+        // 5-step binary search through shuffles)
+        int src = 0;
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1)
+            if (__shfl_sync(0xffffffffu, incl, src + step - 1) <= v) src += step;
+        const int r_incl = __shfl_sync(0xffffffffu, incl, src);
+        const int r_len = __shfl_sync(0xffffffffu, rl, src);
+        const int r_beg = __shfl_sync(0xffffffffu, rb, src);
+        float d2 = FLT_MAX;
+        int id = -1;
+        if (v < total) {
+            const float4 p = sorted[r_beg + (v - (r_incl - r_len))];
+            const float dx = p.x - qx, dy = p.y - qy, dz = p.z - qz;
+            d2 = dx * dx + dy * dy + dz * dz;
+            id = __float_as_int(p.w);
+        }
+        const bool acc = d2 < tau;
+        const unsigned mask = __ballot_sync(0xffffffffu, acc);
+        if (mask) {
+            if (acc) {
+                const int pos = KNN_K + n_pending + __popc(mask & ((1u << lane) - 1u));
+                B.d[pos] = d2; B.id[pos] = id;
+            }
+            n_pending += __popc(mask);
+            if (n_pending > KNN_K) { tau = compact_top16(B, lane, KNN_K + n_pending); n_pending = 0; }
+        }
+    }
 }
 
 __global__ void __launch_bounds__(128)
 knn_kernel(int Q, const int32_t* __restrict__ query_idx, const float* __restrict__ means,
            const GridParams* __restrict__ gp, const int32_t* __restrict__ starts, const float4* __restrict__ sorted,
            int32_t* __restrict__ nbr) {
-    __shared__ LaneLists lists[4];
+    __shared__ WarpBuf bufs[4];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int q = blockIdx.x * 4 + wib;
     if (q >= Q) return;
-    LaneLists& L = lists[wib];
-#pragma unroll
-    for (int k = 0; k < KNN_K; ++k) { L.d[k][lane] = FLT_MAX; L.id[k][lane] = -1; }
+    WarpBuf& B = bufs[wib];
+    if (lane < KNN_K) { B.d[lane] = FLT_MAX; B.id[lane] = -1; }
+    __syncwarp();
     const GridParams g = *gp;
     const int64_t qi = query_idx ? query_idx[q] : q;
     const float qx = means[3 * qi], qy = means[3 * qi + 1], qz = means[3 * qi + 2];
@@ -151,31 +199,39 @@ knn_kernel(int Q, const int32_t* __restrict__ query_idx, const float* __restrict
     const float fx = (qx - g.ox) - cx * g.h, fy = (qy - g.oy) - cy * g.h, fz = (qz - g.oz) - cz * g.h;
     const float face = fmaxf(0.f, fminf(fminf(fminf(fx, g.h - fx), fminf(fy, g.h - fy)), fminf(fz, g.h - fz)));
     const int rmax = max(max(max(cx, g.nx - 1 - cx), max(cy, g.ny - 1 - cy)), max(cz, g.nz - 1 - cz));
-    float out_d = FLT_MAX;
-    int out_id = -1;
+    float tau = FLT_MAX;
+    int n_pending = 0;
     for (int r = 0; r <= rmax; ++r) {
-        for (int dz = -r; dz <= r; ++dz) {
-            const int z = cz + dz;
-            if (z < 0 || z >= g.nz) continue;
-            for (int dy = -r; dy <= r; ++dy) {
-                const int y = cy + dy;
-                if (y < 0 || y >= g.ny) continue;
-                const int64_t row = ((int64_t)z * g.ny + y) * g.nx;
-                if (abs(dz) == r || abs(dy) == r) {                     // a full x-run of the shell: one range
-                    const int xa = max(cx - r, 0), xb = min(cx + r, g.nx - 1);
-                    scan_range(L, lane, sorted, starts[row + xa], starts[row + xb + 1], qx, qy, qz);
-                } else {                                                // only the two end cells belong to the shell
-                    if (cx - r >= 0) scan_range(L, lane, sorted, starts[row + cx - r], starts[row + cx - r + 1], qx, qy, qz);
-                    if (cx + r < g.nx) scan_range(L, lane, sorted, starts[row + cx + r], starts[row + cx + r + 1], qx, qy, qz);
+        // enumerate the shell's ranges: item t -> (dz, dy, which): a row with |dz| == r or |dy| == r is one full
+        // x-run, an inner row contributes its two end cells; lanes take items t = lane, lane + 32, ...
+        const int side = 2 * r + 1;
+        const int n_items = (r == 0) ? 1 : 2 * side * side;          // two slots per row; full rows use slot 0 only
+        for (int base = 0; base < n_items; base += 32) {
+            const int t = base + lane;
+            int rb = 0, rl = 0;
+            if (t < n_items) {
+                const int row_id = t >> 1, which = t & 1;
+                const int dz = row_id / side - r, dy = row_id % side - r;
+                const int z = cz + dz, y = cy + dy;
+                if (z >= 0 && z < g.nz && y >= 0 && y < g.ny) {
+                    const int64_t row = ((int64_t)z * g.ny + y) * g.nx;
+                    const bool full = (abs(dz) == r) || (abs(dy) == r);
+                    int xa = -1, xb = -2;
+                    if (r == 0) { if (which == 0) { xa = cx; xb = cx; } }
+                    else if (full) { if (which == 0) { xa = max(cx - r, 0); xb = min(cx + r, g.nx - 1); } }
+                    else if (which == 0) { if (cx - r >= 0) { xa = cx - r; xb = cx - r; } }
+                    else { if (cx + r < g.nx) { xa = cx + r; xb = cx + r; } }
+                    if (xb >= xa) { rb = starts[row + xa]; rl = starts[row + xb + 1] - rb; }
                 }
             }
+            scan_batch(B, lane, sorted, rb, rl, qx, qy, qz, tau, n_pending);
         }
-        __syncwarp();
-        const float kth = merge_lists(L, lane, out_d, out_id);
+        if (n_pending > 0) { tau = compact_top16(B, lane, KNN_K + n_pending); n_pending = 0; }
         const float bound = (float)r * g.h + face;
-        if (kth <= bound * bound) break;
+        if (tau <= bound * bound) break;
     }
-    if (lane < KNN_K) nbr[(int64_t)q * KNN_K + lane] = out_id;
+    __syncwarp();
+    if (lane < KNN_K) nbr[(int64_t)q * KNN_K + lane] = B.id[lane];
 }
 
 // ---- iso-surface density loss: 16 lanes per query, one neighbour per lane -------------------------------
@@ -328,7 +384,7 @@ extern "C" int isogs_knn16(int64_t N, const float* means, int res, int Q, const 
     ISOGS_CUDA(cudaMemsetAsync(starts, 0, sizeof(int32_t) * (size_t)(2 * cells + 1), stream));
     bbox_init_kernel<<<1, 32, 0, stream>>>(bb);
     const unsigned gN = (unsigned)((N + 255) / 256);
-    bbox_kernel<<<min(gN, 148u * 8u), 256, 0, stream>>>(N, means, bb);
+    bbox_kernel<<<min(gN, 148u * 4u), 256, 0, stream>>>(N, means, bb);
     grid_params_kernel<<<1, 32, 0, stream>>>(bb, res, gp);
     cell_count_kernel<<<gN, 256, 0, stream>>>(N, means, gp, starts);
     size_t need = 0;
