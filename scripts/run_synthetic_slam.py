@@ -58,7 +58,7 @@ def ate_rmse(est, gt):
 
 
 def run(shape="tum", frames=50, track_iters=40, map_iters=40, map_every=5, kf_every=5, window=8, seed=0,
-        isotropic=True, quiet=True, ssim=False):
+        isotropic=True, quiet=True, ssim=False, isoflat=False):
     dev = torch.device("cuda", 0)
     W, H, fx, fy, cx, cy = syn.SHAPES[shape][:6]
     cam = pkg.make_camera(W, H, fx, fy, cx, cy)
@@ -106,7 +106,8 @@ def run(shape="tum", frames=50, track_iters=40, map_iters=40, map_every=5, kf_ev
                 if it in (0, 20):                                                  # configs/replica/splatam.py:119-128
                     pruned_total += ss.prune_gaussians(ws, gmap, 0.005, 0.1 * scene_radius if it >= 0 else float("inf"))
                 k = sel[rng.randint(len(sel))]
-                ss.map_step(ws, gmap, pkg.make_pose(*k["pose"]), k["rgb"], k["depth"], k["inv_nd"], ssim=ssim)
+                ss.map_step(ws, gmap, pkg.make_pose(*k["pose"]), k["rgb"], k["depth"], k["inv_nd"], ssim=ssim, isoflat=isoflat,
+                            iso_seed=seed + 1000 * f + it)
             torch.cuda.synchronize(); t_map += time.perf_counter() - t0; n_map += map_iters
             if f % kf_every == 0:
                 keyframes.append(cur)
@@ -121,7 +122,8 @@ def run(shape="tum", frames=50, track_iters=40, map_iters=40, map_every=5, kf_ev
                 tracking_iters_per_s=n_track / max(t_track, 1e-9), mapping_iters_per_s=n_map / max(t_map, 1e-9),
                 note="wall clock with synchronize() around each tracking / mapping block; includes the densify / "
                      "prune host reads; mapping colour loss = " +
-                     ("0.8*L1 + 0.2*(1-SSIM)" if ssim else "L1") + ", masked depth L1; flat/iso not built (SURVEY 8(f)-2)")
+                     ("0.8*L1 + 0.2*(1-SSIM)" if ssim else "L1") + ", masked depth L1" +
+                     (" + 50*flat + 2*iso (three-axis scales)" if isoflat else ""))
 
 
 if __name__ == "__main__":
@@ -132,5 +134,8 @@ if __name__ == "__main__":
     ap.add_argument("--map-iters", type=int, default=40)
     ap.add_argument("--map-every", type=int, default=5)
     ap.add_argument("--ssim", action="store_true", help="mapping colour loss 0.8*L1 + 0.2*(1-SSIM) (splatam.py:568)")
+    ap.add_argument("--isoflat", action="store_true",
+                    help="three-axis scales + the IsoGS flat / iso-surface terms (splatam.py:572-675): the complete loss")
     a = ap.parse_args()
-    print(json.dumps(run(a.shape, a.frames, a.track_iters, a.map_iters, a.map_every, ssim=a.ssim)))
+    print(json.dumps(run(a.shape, a.frames, a.track_iters, a.map_iters, a.map_every, ssim=a.ssim,
+                         isotropic=not a.isoflat, isoflat=a.isoflat)))
