@@ -121,6 +121,16 @@ int isogs_blend_bwd(const isogs_camera* cam, int ch, int64_t N, const float* rec
                     const float* v_render, const float* v_alpha /*nullable*/,
                     float* v_rec, void* stream);
 
+/* Tracking variant of isogs_blend_bwd (same arguments): only the pose gets a gradient in the tracking loop
+ * (python_ordinary/scripts/splatam.py:1247-1290, transform_to_frame(gaussians_grad=False)), and the pose sees
+ * the record through {x, y, conic, z, z*z} alone, so only v_rec[0..4] and v_rec[9..10] are accumulated; the
+ * colour / opacity slots keep the caller's zeros.  Feed the result to isogs_preprocess_bwd with v_pose. */
+int isogs_blend_bwd_geom(const isogs_camera* cam, int ch, int64_t N, const float* rec,
+                         const int32_t* vals_sorted, const int32_t* tile_ranges,
+                         const float* alpha, const int32_t* last,
+                         const float* v_render, const float* v_alpha /*nullable*/,
+                         float* v_rec, void* stream);
+
 /* preprocess backward: replaces projection_ewa_3dgs_fused_bwd (Ops.h:65-88;
  * ProjectionEWA3DGSFused.cu:294-531) and, when a pose is given, the autograd backward of
  * transform_to_frame (slam_helpers.py:252-304) including the N->7 pose reduction.

@@ -281,7 +281,33 @@ __device__ __forceinline__ void quad_reduce12(float (&v)[12], int lane) {
     }
 }
 
-template <int CH, int NW>
+// Same scheme for 8 values (6 shuffles): lane l ends with the totals of components
+// 4*(l&1) + 2*((l>>1)&1) + {0,1}.
+__device__ __forceinline__ void quad_reduce8(float (&v)[8], int lane) {
+    {
+        const bool up = lane & 1;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float send = up ? v[k] : v[k + 4];
+            const float keep = up ? v[k + 4] : v[k];
+            v[k] = keep + __shfl_xor_sync(FULL, send, 1);
+        }
+    }
+    {
+        const bool up = lane & 2;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const float send = up ? v[k] : v[k + 2];
+            const float keep = up ? v[k + 2] : v[k];
+            v[k] = keep + __shfl_xor_sync(FULL, send, 2);
+        }
+    }
+}
+
+// GEOM = true: tracking.  Only the pose gets a gradient there (splatam.py:1247-1290), and it depends on the
+// record through {x, y, conic, z, z^2} alone -- colour and opacity gradients are neither reduced nor written
+// (7 values, 6 shuffles, 2 REDs per lane instead of 11 / 9 / 3).
+template <int CH, int NW, bool GEOM>
 __global__ void __launch_bounds__(BLOCK)
 blend_bwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
                  const int32_t* __restrict__ ranges, const float* __restrict__ alpha,
@@ -327,9 +353,11 @@ blend_bwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
     // gradient only through its dot product with the pixel's v_render, so one scalar carries it
     float bdot = 0.f;
 
-    // component triple this lane owns after quad_reduce12
-    const int comp0 = 6 * (lane & 1) + 3 * ((lane >> 1) & 1);
+    // component triple this lane owns after quad_reduce12 (pair after quad_reduce8: vector {x,y,a,b,c,z,z^2,-}
+    // lives at record offsets {0,1,2,3,4,9,10})
+    const int comp0 = GEOM ? 4 * (lane & 1) + 2 * ((lane >> 1) & 1) : 6 * (lane & 1) + 3 * ((lane >> 1) & 1);
     const bool third = comp0 + 2 < 6 + CH;
+    const int goff0 = comp0 < 5 ? comp0 : comp0 + 4, goff1 = comp0 + 1 < 5 ? comp0 + 1 : comp0 + 5;
 
     int staged = 0, base = 0; // warp-uniform: words [base, staged) are live in the ring
     Prefetch pf;
@@ -395,23 +423,41 @@ blend_bwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
             const float v_sigma = -opac * u;
             const float ca = 2.0f * g0s.z, cb = g0s.w, cc = 2.0f * g1s.x;
             const float wx = v_sigma * dx, wy = v_sigma * dy;
-            float v[12];
-            v[0] = fmaf(ca, wx, cb * wy);
-            v[1] = fmaf(cb, wx, cc * wy);
-            v[2] = 0.5f * wx * dx;
-            v[3] = wx * dy;
-            v[4] = 0.5f * wy * dy;
-            v[5] = u;
+            if constexpr (GEOM) {
+                float v[8];
+                v[0] = fmaf(ca, wx, cb * wy);
+                v[1] = fmaf(cb, wx, cc * wy);
+                v[2] = 0.5f * wx * dx;
+                v[3] = wx * dy;
+                v[4] = 0.5f * wy * dy;
+                v[5] = fac * vr[3];
+                v[6] = (CH == 5) ? fac * vr[CH - 1] : 0.f;
+                v[7] = 0.f;
+                quad_reduce8(v, lane);
+                if ((vb >> qshift) & 15u) {
+                    float* dst = v_rec + (int64_t)st.id[slot] * REC;
+                    atomicAdd(dst + goff0, v[0]);
+                    if (comp0 != 6) atomicAdd(dst + goff1, v[1]);
+                }
+            } else {
+                float v[12];
+                v[0] = fmaf(ca, wx, cb * wy);
+                v[1] = fmaf(cb, wx, cc * wy);
+                v[2] = 0.5f * wx * dx;
+                v[3] = wx * dy;
+                v[4] = 0.5f * wy * dy;
+                v[5] = u;
 #pragma unroll
-            for (int k = 0; k < CH; ++k) v[6 + k] = fac * vr[k];
+                for (int k = 0; k < CH; ++k) v[6 + k] = fac * vr[k];
 #pragma unroll
-            for (int k = 6 + CH; k < 12; ++k) v[k] = 0.f;
-            quad_reduce12(v, lane);
-            if ((vb >> qshift) & 15u) {
-                float* dst = v_rec + (int64_t)st.id[slot] * REC + comp0;
-                atomicAdd(dst, v[0]);
-                atomicAdd(dst + 1, v[1]);
-                if (third) atomicAdd(dst + 2, v[2]);
+                for (int k = 6 + CH; k < 12; ++k) v[k] = 0.f;
+                quad_reduce12(v, lane);
+                if ((vb >> qshift) & 15u) {
+                    float* dst = v_rec + (int64_t)st.id[slot] * REC + comp0;
+                    atomicAdd(dst, v[0]);
+                    atomicAdd(dst + 1, v[1]);
+                    if (third) atomicAdd(dst + 2, v[2]);
+                }
             }
         }
         if (wmin > base) {
@@ -465,7 +511,7 @@ static int launch_fwd(const DevCam& dc, const float* rec, const int32_t* vals, c
     return ISOGS_OK;
 }
 
-template <int CH, int NW>
+template <int CH, int NW, bool GEOM = false>
 static int launch_bwd(const DevCam& dc, const float* rec, const int32_t* vals, const int32_t* ranges,
                       const float* alpha, const int32_t* last, const float* v_render, const float* v_alpha,
                       float* v_rec, cudaStream_t stream) {
@@ -474,13 +520,13 @@ static int launch_bwd(const DevCam& dc, const float* rec, const int32_t* vals, c
     int dev = 0;
     ISOGS_CUDA(cudaGetDevice(&dev));
     if (attr_dev != dev) {
-        int rc = set_smem(blend_bwd_kernel<CH, NW>, smem);
+        int rc = set_smem(blend_bwd_kernel<CH, NW, GEOM>, smem);
         if (rc != 0) return rc;
         attr_dev = dev;
     }
     dim3 grid(dc.tw, dc.th);
-    blend_bwd_kernel<CH, NW><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last, v_render,
-                                                             v_alpha, v_rec);
+    blend_bwd_kernel<CH, NW, GEOM><<<grid, BLOCK, smem, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last, v_render,
+                                                                   v_alpha, v_rec);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
 }
@@ -520,4 +566,18 @@ extern "C" int isogs_blend_bwd(const isogs_camera* cam, int ch, int64_t N, const
     if (ch == 4) return nw == 2 ? ISOGS_BWD(4, 2) : nw == 8 ? ISOGS_BWD(4, 8) : ISOGS_BWD(4, 4);
     return nw == 2 ? ISOGS_BWD(5, 2) : nw == 8 ? ISOGS_BWD(5, 8) : ISOGS_BWD(5, 4);
 #undef ISOGS_BWD
+}
+
+// Tracking variant: identical traversal, but only the gradient components the POSE depends on are reduced and
+// written: v_rec[0..4] (x, y, conic) and v_rec[9..10] (z, z^2); the colour / opacity slots are left untouched.
+extern "C" int isogs_blend_bwd_geom(const isogs_camera* cam, int ch, int64_t N, const float* rec,
+                                    const int32_t* vals_sorted, const int32_t* tile_ranges, const float* alpha,
+                                    const int32_t* last, const float* v_render, const float* v_alpha, float* v_rec,
+                                    void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    (void)N;
+    if (!cam || (ch != 4 && ch != 5)) { set_error("isogs_blend_bwd_geom: ch must be 4 or 5"); return ISOGS_E_ARG; }
+    DevCam dc = make_devcam(*cam);
+    if (ch == 4) return launch_bwd<4, 4, true>(dc, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
+    return launch_bwd<5, 4, true>(dc, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
 }

@@ -224,7 +224,9 @@ def render_backward(ws, gmap, pose=None, pose_dev=None, ch=5, want_gaussians=Tru
     ws.v_rec[:N].zero_()
     _mark(marks, "zero_v_rec")
     if N > 0:
-        check(L.isogs_blend_bwd(C.byref(cam), ch, N, _ptr(ws.rec), _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.alpha),
+        # tracking needs only the geometric + depth-channel gradients (the pose's inputs)
+        bwd = L.isogs_blend_bwd if want_gaussians else L.isogs_blend_bwd_geom
+        check(bwd(C.byref(cam), ch, N, _ptr(ws.rec), _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.alpha),
                                 _ptr(ws.last), _ptr(ws.v_render), None, _ptr(ws.v_rec), st))
     _mark(marks, "blend_bwd")
     quats = None if gmap.isotropic else gmap.p["unnorm_rotations"]

@@ -461,3 +461,30 @@ def test_synthetic_slam_loop_runs_and_improves(pkg, syn, ss):
     assert out["gaussians"] > 18000
     assert out["ate_rmse_mm"] < 50.0
     assert out["psnr_last"] > 17.0
+
+
+def test_blend_bwd_geom_is_the_pose_subset_of_blend_bwd(pkg, syn, ss):
+    """isogs_blend_bwd_geom (tracking) writes exactly the {x, y, conic, z, z^2} slots of isogs_blend_bwd."""
+    params, frames, (W, H, fx, fy, cx, cy) = _scene(syn)
+    gcam = pkg.make_camera(W, H, fx, fy, cx, cy)
+    gmap = ss.GaussianMap(params, device="cuda")
+    ws = ss.StepWorkspace(gcam, gmap.count, torch.device("cuda"))
+    traj = syn.trajectory(8, step=3.0)
+    q, tr = syn.w2c_to_pose(traj[2])
+    ss.render_forward(ws, gmap, pose=pkg.make_pose(q, tr))
+    ws.v_render.copy_(torch.from_numpy(np.random.RandomState(3).randn(*ws.v_render.shape).astype(np.float32)).cuda())
+    N, L, st = gmap.count, pkg.lib(), _stream()
+    out = []
+    for fn in (L.isogs_blend_bwd, L.isogs_blend_bwd_geom):
+        v = torch.zeros((N, 12), dtype=torch.float32, device="cuda")
+        pkg._lib.check(fn(C.byref(gcam), 5, N, _ptr(ws.rec), _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.alpha), _ptr(ws.last),
+                          _ptr(ws.v_render), None, _ptr(v), st))
+        torch.cuda.synchronize()
+        out.append(v.cpu().numpy())
+    full, geom = out
+    keep = [0, 1, 2, 3, 4, 9, 10]
+    drop = [5, 6, 7, 8, 11]
+    assert np.abs(full[:, keep]).max() > 0
+    scale = np.abs(full[:, keep]).max(0) + 1e-30
+    assert (np.abs(geom[:, keep] - full[:, keep]).max(0) / scale).max() < 1e-4   # same sums, different atomic order
+    assert np.all(geom[:, drop] == 0.0)
