@@ -108,29 +108,46 @@ __device__ __forceinline__ uint32_t quad_hits(bool have, const float4& g0, const
 }
 
 // One list entry held in registers between its global load and its commit to the ring, so the
-// vals -> rec dependent load chain of word w+1 overlaps the blending of the words before it.
+// vals -> rec dependent load chain of word w+1 overlaps the blending of the words before it.  The chain is
+// split over TWO calls: the call for word w issues the record loads with the Gaussian id that the call for
+// word w-1 requested, and requests the id of word w+1 -- otherwise the warp would sit on the long scoreboard
+// inside the prefetch, waiting for `vals` before it can even issue the `rec` loads (8 % of the forward's stall
+// samples in profiles/r1h_blend_fwd).
 struct Prefetch {
     float4 g0, g1, g2;
     int id;
     bool have;
+    int id_next;      // id of entry (32 * next_word + lane), requested one call ahead
+    int next_word;    // warp-uniform; -1 before the first call
 };
 
-// Load list entry (32*word + lane), i.e. sorted index first + dir*(32*word + lane).
+__device__ __forceinline__ int list_id(int word, int first, int dir, int n_entries, const int32_t* __restrict__ vals,
+                                       int lane) {
+    const int e = 32 * word + lane;
+    return (e < n_entries) ? __ldg(vals + first + dir * e) : -1;
+}
+
+// Load list entry (32*word + lane), i.e. sorted index first + dir*(32*word + lane).  TWO_STAGE requests the id
+// of word+1 as well (used by the forward; in the backward the extra registers cost more than the stall).
+template <bool TWO_STAGE>
 __device__ __forceinline__ void prefetch_word(Prefetch& pf, int word, int first, int dir, int n_entries,
                                               const float4* __restrict__ rec, const int32_t* __restrict__ vals,
                                               int lane) {
-    const int e = 32 * word + lane;
-    pf.have = e < n_entries;
+    const int id = (TWO_STAGE && pf.next_word == word) ? pf.id_next : list_id(word, first, dir, n_entries, vals, lane);
+    pf.have = id >= 0;
+    pf.id = pf.have ? id : 0;
     pf.g0 = make_float4(0.f, 0.f, 0.f, 0.f);
     pf.g1 = pf.g0;
     pf.g2 = pf.g0;
-    pf.id = 0;
     if (pf.have) {
-        pf.id = __ldg(vals + first + dir * e);
-        const float4* r = rec + 3 * (int64_t)pf.id;
+        const float4* r = rec + 3 * (int64_t)id;
         pf.g0 = __ldg(r);
         pf.g1 = __ldg(r + 1);
         pf.g2 = __ldg(r + 2);
+    }
+    if (TWO_STAGE) {
+        pf.id_next = list_id(word + 1, first, dir, n_entries, vals, lane);
+        pf.next_word = word + 1;
     }
 }
 
@@ -184,10 +201,11 @@ blend_fwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
     if (n_words > 0 && !__all_sync(FULL, done)) {
         int staged = 0, base = 0; // warp-uniform: words [base, staged) are live in the ring
         Prefetch pf;
-        prefetch_word(pf, 0, start, 1, n_entries, rec, vals, lane);
+        pf.next_word = -1;
+        prefetch_word<true>(pf, 0, start, 1, n_entries, rec, vals, lane);
         for (; staged < min(NW, n_words); ++staged) {
             commit_word<NW, false>(st, pf, staged, bx0, by0, lane);
-            prefetch_word(pf, staged + 1, start, 1, n_entries, rec, vals, lane);
+            prefetch_word<true>(pf, staged + 1, start, 1, n_entries, rec, vals, lane);
         }
         static_assert((NW & (NW - 1)) == 0, "NW must be a power of two");
         const uint32_t* hq = &st.hits[0][q]; // this quad's hit word of ring word w is hq[8 * w]
@@ -242,7 +260,7 @@ blend_fwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
                 if (staged < n_words) {
                     commit_word<NW, false>(st, pf, staged, bx0, by0, lane);
                     ++staged;
-                    prefetch_word(pf, staged, start, 1, n_entries, rec, vals, lane);
+                    prefetch_word<true>(pf, staged, start, 1, n_entries, rec, vals, lane);
                 }
             }
         }
@@ -361,10 +379,11 @@ blend_bwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
 
     int staged = 0, base = 0; // warp-uniform: words [base, staged) are live in the ring
     Prefetch pf;
-    prefetch_word(pf, 0, warp_last, -1, n_entries, rec, vals, lane);
+    pf.next_word = -1;
+    prefetch_word<false>(pf, 0, warp_last, -1, n_entries, rec, vals, lane);
     for (; staged < min(NW, n_words); ++staged) {
         commit_word<NW, true>(st, pf, staged, bx0, by0, lane);
-        prefetch_word(pf, staged + 1, warp_last, -1, n_entries, rec, vals, lane);
+        prefetch_word<false>(pf, staged + 1, warp_last, -1, n_entries, rec, vals, lane);
     }
     static_assert((NW & (NW - 1)) == 0, "NW must be a power of two");
     const uint32_t* hq = &st.hits[0][q]; // this quad's hit word of ring word w is hq[8 * w]
@@ -465,7 +484,7 @@ blend_bwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
             if (staged < n_words) {
                 commit_word<NW, true>(st, pf, staged, bx0, by0, lane);
                 ++staged;
-                prefetch_word(pf, staged, warp_last, -1, n_entries, rec, vals, lane);
+                prefetch_word<false>(pf, staged, warp_last, -1, n_entries, rec, vals, lane);
             }
         }
     }
