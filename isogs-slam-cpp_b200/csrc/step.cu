@@ -17,6 +17,20 @@ namespace isogs {
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ float sgnf(float d) { return (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f); }
 
+// V pixels per thread per trip: V = 4 moves every plane as float4 (P % 4 == 0 and 16-byte aligned planes)
+template <int V> struct Px { float v[V]; };
+template <int V> __device__ __forceinline__ Px<V> ldv(const float* p) {
+    Px<V> r;
+    if constexpr (V == 4) { const float4 t = *reinterpret_cast<const float4*>(p); r.v[0] = t.x; r.v[1] = t.y; r.v[2] = t.z; r.v[3] = t.w; }
+    else r.v[0] = *p;
+    return r;
+}
+template <int V> __device__ __forceinline__ void stv(float* p, const Px<V>& r) {
+    if constexpr (V == 4) *reinterpret_cast<float4*>(p) = make_float4(r.v[0], r.v[1], r.v[2], r.v[3]);
+    else *p = r.v[0];
+}
+
+template <int V>
 __global__ void __launch_bounds__(256)
 loss_l1_kernel(int64_t P, int mode, const float* __restrict__ render, const float* __restrict__ alpha,
                const float* __restrict__ gt_rgb, const float* __restrict__ gt_depth, float w_im, float w_depth,
@@ -25,29 +39,42 @@ loss_l1_kernel(int64_t P, int mode, const float* __restrict__ render, const floa
     float sum_d = 0.f, sum_c = 0.f, cnt = 0.f;
     const bool outl = outlier_thresh != nullptr;
     const float othr = outl ? *outlier_thresh : 0.f;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < P; i += (int64_t)gridDim.x * blockDim.x) {
-        const float d = render[3 * P + i], d2 = render[4 * P + i];
-        const float gd = gt_depth[i];
-        const float unc = d2 - d * d;
-        const bool nan_ok = !(isnan(d) || isnan(unc));
-        bool m = (gd > 0.f) && nan_ok;
-        bool mc = true;
-        const float dd = d - gd;
-        if (outl) m = m && (fabsf(dd) < othr);               // ignore_outlier_depth_loss, splatam.py:551-554
-        if (mode == 0) {
-            if (use_sil) m = m && (alpha[i] > sil_thres);
-            mc = (use_sil || outl) ? m : true;               // :563-568
-        }
-        if (gd > 0.f) cnt += 1.f;
-        if (m) sum_d += fabsf(dd);
-        v_render[3 * P + i] = m ? (w_depth * inv_nd) * sgnf(dd) : 0.f;
-        v_render[4 * P + i] = 0.f;
+    const bool need_alpha = (mode == 0) && use_sil;
+    for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * V; i < P; i += (int64_t)gridDim.x * blockDim.x * V) {
+        const Px<V> d = ldv<V>(render + 3 * P + i), d2 = ldv<V>(render + 4 * P + i), gd = ldv<V>(gt_depth + i);
+        Px<V> al;
+        if (need_alpha) al = ldv<V>(alpha + i);
+        Px<V> c[3], g[3];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const float dc = render[k * P + i] - gt_rgb[k * P + i];
-            if (mc) sum_c += fabsf(dc);
-            v_render[k * P + i] = mc ? (w_im * inv_nc) * sgnf(dc) : 0.f;
+        for (int k = 0; k < 3; ++k) { c[k] = ldv<V>(render + k * P + i); g[k] = ldv<V>(gt_rgb + k * P + i); }
+        Px<V> od, oc[3], zero;
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+            const float unc = d2.v[j] - d.v[j] * d.v[j];
+            const bool nan_ok = !(isnan(d.v[j]) || isnan(unc));
+            bool m = (gd.v[j] > 0.f) && nan_ok;
+            bool mc = true;
+            const float dd = d.v[j] - gd.v[j];
+            if (outl) m = m && (fabsf(dd) < othr);               // ignore_outlier_depth_loss, splatam.py:551-554
+            if (mode == 0) {
+                if (use_sil) m = m && (al.v[j] > sil_thres);
+                mc = (use_sil || outl) ? m : true;               // :563-568
+            }
+            if (gd.v[j] > 0.f) cnt += 1.f;
+            if (m) sum_d += fabsf(dd);
+            od.v[j] = m ? (w_depth * inv_nd) * sgnf(dd) : 0.f;
+            zero.v[j] = 0.f;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const float dc = c[k].v[j] - g[k].v[j];
+                if (mc) sum_c += fabsf(dc);
+                oc[k].v[j] = mc ? (w_im * inv_nc) * sgnf(dc) : 0.f;
+            }
         }
+        stv<V>(v_render + 3 * P + i, od);
+        stv<V>(v_render + 4 * P + i, zero);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) stv<V>(v_render + k * P + i, oc[k]);
     }
     __shared__ float sm[3][8];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -274,9 +301,17 @@ extern "C" int isogs_loss_l1_fused(const isogs_camera* cam, int mode, const floa
     if (P == 0) return ISOGS_OK;
     const float inv_nd = (mode == 1) ? inv_n_depth : 1.0f;
     const float inv_nc = (mode == 1) ? 1.0f / (float)(3 * P) : 1.0f;
-    const int blocks = (int)std::min<int64_t>((P + 255) / 256, 148 * 8);
-    loss_l1_kernel<<<blocks, 256, 0, stream>>>(P, mode, render, alpha, gt_rgb, gt_depth, w_im, w_depth, sil_thres,
-                                               use_sil, inv_nd, inv_nc, outlier_thresh, v_render, losses);
+    const bool vec = (P % 4 == 0) && ((((uintptr_t)render | (uintptr_t)alpha | (uintptr_t)gt_rgb | (uintptr_t)gt_depth |
+                                        (uintptr_t)v_render) & 15) == 0);
+    if (vec) {
+        const int blocks = (int)std::min<int64_t>((P / 4 + 255) / 256, 148 * 8);
+        loss_l1_kernel<4><<<blocks, 256, 0, stream>>>(P, mode, render, alpha, gt_rgb, gt_depth, w_im, w_depth, sil_thres,
+                                                      use_sil, inv_nd, inv_nc, outlier_thresh, v_render, losses);
+    } else {
+        const int blocks = (int)std::min<int64_t>((P + 255) / 256, 148 * 8);
+        loss_l1_kernel<1><<<blocks, 256, 0, stream>>>(P, mode, render, alpha, gt_rgb, gt_depth, w_im, w_depth, sil_thres,
+                                                      use_sil, inv_nd, inv_nc, outlier_thresh, v_render, losses);
+    }
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
 }
