@@ -376,8 +376,15 @@ def add_new_gaussians(ws, gmap, pose, gt_rgb, gt_depth, sil_thres=0.5, noise_std
     P = cam.width * cam.height
     ws.ensure_gaussians(gmap.count)
     render_forward(ws, gmap, pose=pose)
-    err = (gt_depth - ws.render[3]).abs() * (gt_depth > 0)                    # splatam.py:811
-    thr = 50.0 * float(err.median())                                           # :812 (one host read)
+    # 50 x median(|gt_d - d| * (gt_d > 0)) (splatam.py:811-812) by the device-side median kernel; one host read
+    if ws.outlier_scratch is None:
+        ws.outlier_scratch = torch.empty((2 * P,), dtype=torch.float32, device=ws.device)
+    if ws.sort_b < _lib.temp_bytes(0, P)[1]:
+        ws._grow_isects(max(ws.isect_cap, P))
+    check(lib().isogs_depth_outlier_threshold(C.byref(cam), _ptr(ws.render[3]), _ptr(gt_depth), 50.0,
+                                              _ptr(ws.outlier_scratch), _ptr(ws.sort_tmp), ws.sort_b,
+                                              _ptr(ws.small[28:29]), _stream()))
+    thr = float(ws.small[28])
     gmap.reserve(gmap.count + P)
     count = torch.tensor([gmap.count], dtype=torch.int32, device=gmap.device)
     scan = torch.empty((2 * P,), dtype=torch.int32, device=gmap.device)
