@@ -285,10 +285,12 @@ def run_ours(args):
     ab = algorithmic_bytes(gmap.count, V, M, P, cam.n_tiles)
     dom = max((s for s in stage_ms if s in ab), key=lambda s: stage_ms[s])
     achieved = ab[dom] / (stage_ms[dom] * 1e-3) / 1e9
-    traffic = None   # DRAM bytes of the dominant kernel per launch, from the committed ncu capture
+    traffic, issue_pct = None, None   # DRAM bytes / issue-slot use of the dominant kernel, from the committed ncu capture
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
-        traffic = json.load(open(tp)).get("dram_bytes_per_launch", {}).get(dom)
+        tj = json.load(open(tp))
+        traffic = tj.get("dram_bytes_per_launch", {}).get(dom)
+        issue_pct = tj.get("issue_active_pct", {}).get(dom)
     raster_ms = sum(stage_ms.get(s, 0.0) for s in ("preprocess_fwd", "tile_bin", "blend_fwd", "zero_v_rec",
                                                    "blend_bwd", "preprocess_bwd"))
     step_bytes = sum(ab.values())
@@ -317,8 +319,8 @@ def run_ours(args):
 
         "roofline": {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                     "algorithmic_bytes": ab[dom],
-                     "note": "the blend kernels are instruction-issue bound (ncu: issue-active ~77 %, DRAM < 5 % of "
+                     "algorithmic_bytes": ab[dom], "issue_active_pct_ncu": issue_pct,
+                     "note": "the blend kernels are instruction-issue bound (ncu: issue slots 77-82 % busy, DRAM < 5 % of "
                              "peak), not HBM bound (SURVEY 8(d)); achieved = algorithmic bytes / CUDA-event time of the "
                              "stage inside the timed region; traffic = ncu dram read+write of one launch "
                              "(profiles/traffic.json)"},
