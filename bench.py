@@ -123,7 +123,22 @@ def run_ours(args):
     syn, params, kfs = build_workload(SHAPE, N_GAUSS, WINDOW)
     W, H, fx, fy, cx, cy = syn.SHAPES[SHAPE][:6]
     cam = pkg.make_camera(W, H, fx, fy, cx, cy)
-    gmap = ss.GaussianMap(params, device=dev)
+    # the one exchange step of the sharded path: the gradient average.  Default: our own two-shot kernel over
+    # NVLink peer memory (csrc/peer.cu); NCCL when asked for, or when CUDA IPC is unavailable on the box.
+    dp = importlib.import_module("isogs_slam_cpp_b200.dp")
+    ar, ar_kind, grad_alloc = None, "none", None
+    if world > 1:
+        ar, ar_kind = dp.allreduce_mean_, "nccl all-reduce (ncclAvg)"
+        if args.allreduce == "p2p":
+            peer = dp.PeerAllReduce(dev)
+            try:
+                peer.alloc(1024)                       # probe: cudaMalloc + IPC export + peer mapping on every rank
+                ar, ar_kind, grad_alloc = peer, "own two-shot kernel over NVLink peer memory (isogs_allreduce_avg_p2p)", peer.alloc
+            except RuntimeError as e:
+                ar_kind += f"; p2p unavailable: {e}"
+                if rank == 0:
+                    print(f"[bench] peer all-reduce unavailable, using NCCL: {e}", file=sys.stderr)
+    gmap = ss.GaussianMap(params, device=dev, grad_alloc=grad_alloc)
     ws = ss.StepWorkspace(cam, gmap.count, dev)
     P = W * H
     # keyframes resident in HBM (for `value`) and in pinned host memory (for `e2e`)
@@ -144,8 +159,6 @@ def run_ours(args):
              for _ in range(2)]
     e2e_state = dict(prefetched=-1, last_loss=0.0)
 
-    dp = importlib.import_module("isogs_slam_cpp_b200.dp")
-    ar = dp.allreduce_mean_ if world > 1 else None   # ONE all-reduce of the flat gradient buffer per iteration
 
     def step_resident(i, marks=None):
         k = kfs[dp.keyframe_for(i, rank, world, WINDOW)]
@@ -277,6 +290,14 @@ def run_ours(args):
                     tot += ev0.elapsed_time(ev1)
         isoflat_ms = tot / max(1, len(full_marks))
         del gmap3
+    replicas_ok = None
+    if world > 1:
+        if hasattr(ar, "check_status"):
+            ar.check_status()                      # a peer spin that timed out would have left garbage
+        replicas_ok = dp.replicas_identical([gmap.p[k][:gmap.count] for k in ("means3D", "rgb_colors", "logit_opacities")])
+        if hasattr(ar, "release"):
+            gmap.grad_flat, gmap.g = None, {}
+            ar.release()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -304,7 +325,8 @@ def run_ours(args):
                            "mapping_with_ssim_iters_per_s, and the reference's complete loss (+ 50*flat + 2*iso, exact 16-NN of "
                            "8192 centres, three-axis scales) as mapping_full_loss_3axis_iters_per_s",
                    "l2": "working set per step ~%.0f MB > 126 MB L2; keyframes rotate every step" % (step_bytes / 1e6 + 300),
-                   "parallelism": f"keyframe-dp{world}" if world > 1 else "single"},
+                   "parallelism": f"keyframe-dp{world}" if world > 1 else "single",
+                   "allreduce": ar_kind, "replicas_identical_after_run": replicas_ok},
         "raster_fwd_bwd_ms": raster_ms, "tracking_iters_per_s": track_ips,
         "mapping_with_ssim_iters_per_s": ssim_ips, "ssim_fwd_bwd_ms": ssim_ms,
         "mapping_full_loss_3axis_iters_per_s": full_ips, "iso_flat_knn_ms": isoflat_ms,
@@ -417,6 +439,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--allreduce", default="p2p", choices=["p2p", "nccl"],
+                    help="gradient average at N > 1: own NVLink peer kernel (default) or NCCL")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

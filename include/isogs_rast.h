@@ -300,6 +300,26 @@ int isogs_backproject_append(const isogs_camera* cam, const isogs_pose* pose,
                              int32_t* scan /*[2*H*W] scratch*/, void* scan_temp, size_t scan_temp_bytes,
                              int32_t* count, void* stream);
 
+/* keyframe-sharded mapping, SURVEY 8(e): the average of the flat gradient buffer over the ranks as ONE kernel over
+ * NVLink peer memory (two-shot: every rank reduces the 1/world slice it owns from all ranks in rank order and stores the
+ * result into every rank's buffer), instead of an NCCL all-reduce.  The reference has no distributed code; the
+ * sequential analogue is one keyframe per iteration (python_ordinary/scripts/splatam.py:1415-1426).
+ * isogs_peer_alloc: cudaMalloc'd, zeroed, IPC-exportable memory (handle: 64 bytes, HOST); isogs_peer_open maps a
+ * peer's allocation into this process (peer access is enabled lazily).  Layout chosen by the caller: the float
+ * gradient buffer plus a block of 64 uint32 flags (zero at start), both inside such allocations.
+ * isogs_allreduce_avg_p2p: bufs / flags are HOST arrays of `world` DEVICE pointers (index = rank; own entry = own
+ * memory); numel a multiple of 4, buffers 16-byte aligned; epoch must increase by one per call, identically on
+ * every rank; n_ctas <= 0 picks the grid.  In-place: afterwards every buffer holds the same bits.
+ * isogs_peer_wait (same stream, before the first consumer of the reduced gradients) waits until every rank's slice
+ * has landed locally.  status: DEVICE int32, set non-zero if a spin timed out after 2 s (results then undefined). */
+int isogs_peer_alloc(size_t bytes, void** ptr, unsigned char* handle);
+int isogs_peer_open(const unsigned char* handle, void** ptr);
+int isogs_peer_close(void* ptr);
+int isogs_peer_free(void* ptr);
+int isogs_allreduce_avg_p2p(int world, int rank, float* const* bufs /*HOST*/, uint32_t* const* flags /*HOST*/,
+                            int64_t numel, uint32_t epoch, int n_ctas, int32_t* status, void* stream);
+int isogs_peer_wait(int world, const uint32_t* flags_local, uint32_t epoch, int32_t* status, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

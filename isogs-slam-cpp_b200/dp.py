@@ -7,6 +7,8 @@ rank applies the identical Adam step -- replicas stay bit-identical without any 
 reference has no distributed code; its sequential analogue is one uniformly drawn keyframe
 per iteration (python_ordinary/scripts/splatam.py:1415-1426).
 """
+import ctypes as C
+
 import torch
 import torch.distributed as dist
 
@@ -46,3 +48,132 @@ def replicas_identical(tensors, group=None):
     dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
     dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
     return bool(torch.equal(hi, lo))
+
+
+def slice_bounds(numel, world, rank):
+    """[begin, end) in floats of the slice `rank` reduces in the two-shot peer all-reduce (csrc/peer.cu):
+    float4 granularity, ceil(n4 / world) float4 per rank, the tail ranks may own less or nothing."""
+    n4 = numel // 4
+    per = (n4 + world - 1) // world
+    b = min(n4, per * rank)
+    return 4 * b, 4 * min(n4, b + per)
+
+
+class _RawCudaBuffer:
+    """Lets torch view cudaMalloc'd memory that this package owns (CUDA array interface, no copy)."""
+
+    def __init__(self, ptr, numel):
+        self.__cuda_array_interface__ = dict(shape=(int(numel),), typestr="<f4", data=(int(ptr), False), version=2)
+
+
+class PeerAllReduce:
+    """The gradient average of keyframe-sharded mapping as ONE kernel over NVLink peer memory
+    (isogs_allreduce_avg_p2p + isogs_peer_wait, csrc/peer.cu) instead of an NCCL all-reduce.
+
+        ar = PeerAllReduce(device)                       # after dist.init_process_group
+        gmap = GaussianMap(params, device, grad_alloc=ar.alloc)
+        map_step(..., allreduce=ar)
+
+    `alloc(numel)` is COLLECTIVE: every rank cudaMallocs its flat gradient buffer (+ 256 B of flags), the IPC
+    handles travel through torch.distributed, and every rank maps all peers.  Calling the object averages the
+    given prefix of the buffer in place on the current stream; every replica receives identical bits (the owner
+    of a slice sums in rank order and stores the same values everywhere)."""
+    FLAG_BYTES = 256
+
+    def __init__(self, device, group=None, n_ctas=0):
+        from . import _lib
+        self._lib = _lib
+        self.group = group
+        self.device = torch.device(device)
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.n_ctas = int(n_ctas)
+        self.epoch = 0
+        self.status = torch.zeros((1,), dtype=torch.int32, device=self.device)
+        self.own = None
+        self.ptrs = []
+        self.tensor = None
+
+    def _last_error(self):
+        msg = self._lib.lib().isogs_last_error()
+        return msg.decode() if msg else ""
+
+    def _agree(self, ok):
+        """True iff `ok` on every rank (so that a failure on one rank makes all of them fall back together)."""
+        if self.world == 1:
+            return bool(ok)
+        t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=self.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN, group=self.group)
+        return bool(t.item())
+
+    def alloc(self, numel):
+        L = self._lib.lib()
+        self.release()
+        numel = (int(numel) + 3) & ~3
+        flag_off = (4 * numel + 255) & ~255
+        ptr, handle = C.c_void_p(), (C.c_ubyte * 64)()
+        with torch.cuda.device(self.device):
+            rc = L.isogs_peer_alloc(flag_off + self.FLAG_BYTES, C.byref(ptr), handle)
+            err = None if rc == 0 else self._last_error()
+            if not self._agree(rc == 0):
+                if rc == 0:
+                    L.isogs_peer_free(ptr)
+                raise RuntimeError(f"isogs_peer_alloc failed on some rank ({err})")
+            self.own = int(ptr.value)
+            handles = [None] * self.world
+            if self.world > 1:
+                dist.all_gather_object(handles, bytes(handle), group=self.group)
+            self.ptrs, ok, err = [], True, None
+            for r in range(self.world):
+                if r == self.rank:
+                    self.ptrs.append(self.own)
+                    continue
+                q = C.c_void_p()
+                hb = (C.c_ubyte * 64).from_buffer_copy(handles[r])
+                if L.isogs_peer_open(hb, C.byref(q)) != 0:
+                    ok, err = False, self._last_error()
+                    self.ptrs.append(0)
+                else:
+                    self.ptrs.append(int(q.value))
+            if not self._agree(ok):
+                self.release()
+                raise RuntimeError(f"isogs_peer_open failed on some rank ({err})")
+        self.bufs = (C.c_void_p * self.world)(*self.ptrs)
+        self.flags = (C.c_void_p * self.world)(*[p + flag_off for p in self.ptrs])
+        self.numel = numel
+        self.epoch = 0
+        self.tensor = torch.as_tensor(_RawCudaBuffer(self.own, numel), device=self.device)
+        return self.tensor
+
+    def __call__(self, flat):
+        L = self._lib.lib()
+        n = flat.numel()
+        if flat.data_ptr() != self.own or n > self.numel or n % 4:
+            raise ValueError("PeerAllReduce: pass a prefix (a multiple of 4 floats) of the buffer alloc() returned")
+        self.epoch += 1
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        self._lib.check(L.isogs_allreduce_avg_p2p(self.world, self.rank, self.bufs, self.flags, n, self.epoch, self.n_ctas,
+                                                  self.status.data_ptr(), st))
+        self._lib.check(L.isogs_peer_wait(self.world, self.flags[self.rank], self.epoch, self.status.data_ptr(), st))
+        return flat
+
+    def check_status(self):
+        """One host read: raises if a peer spin timed out since the last check."""
+        s = int(self.status.item())
+        if s:
+            self.status.zero_()
+            raise RuntimeError(f"peer all-reduce timed out waiting for a rank (stage {s})")
+
+    def release(self):
+        if self.own is None:
+            return
+        L = self._lib.lib()
+        torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            dist.barrier(group=self.group)           # nobody may still be reading this rank's buffer
+        for r, p in enumerate(self.ptrs):
+            if r != self.rank and p:
+                L.isogs_peer_close(C.c_void_p(p))
+        self.tensor = None
+        L.isogs_peer_free(C.c_void_p(self.own))
+        self.own, self.ptrs = None, []

@@ -29,7 +29,10 @@ TRACKING_LRS = dict(cam_unnorm_rots=4e-4, cam_trans=2e-3)
 class GaussianMap:
     """Replicated Gaussian map: parameters, Adam moments and one flat gradient buffer."""
 
-    def __init__(self, params, capacity=None, device="cuda"):
+    def __init__(self, params, capacity=None, device="cuda", grad_alloc=None):
+        """`grad_alloc(numel) -> zeroed fp32 CUDA tensor` supplies the flat gradient buffer (dp.PeerAllReduce.alloc
+        makes it NVLink-peer-mapped memory); default: a plain torch allocation."""
+        self.grad_alloc = grad_alloc
         n = params["means3D"].shape[0]
         self.isotropic = params["log_scales"].shape[1] == 1
         self.sd = 1 if self.isotropic else 3
@@ -52,9 +55,18 @@ class GaussianMap:
         # one contiguous gradient buffer so a single all-reduce covers every parameter group
         self.grad_names = [k for k in PARAM_ORDER if not (self.isotropic and k == "unnorm_rotations")]
         total = sum(self.widths[k] for k in self.grad_names) * self.capacity + 4 * len(self.grad_names)
-        self.grad_flat = torch.zeros((total,), dtype=torch.float32, device=self.device)
+        self.grad_flat = self._new_grad_flat(total)
         self._carve()
         self.step_count = 0
+
+    def _new_grad_flat(self, total):
+        if self.grad_alloc is None:
+            return torch.zeros((total,), dtype=torch.float32, device=self.device)
+        self.grad_flat, self.g = None, {}                       # drop the views before the old buffer is freed
+        buf = self.grad_alloc(total)
+        if buf.numel() < total or buf.dtype != torch.float32 or buf.data_ptr() % 16:
+            raise ValueError("grad_alloc returned an unusable buffer")
+        return buf
 
     def _carve(self):
         # every group starts on a 16-byte boundary (the kernels store float4 rows); the padding floats stay 0
@@ -103,7 +115,7 @@ class GaussianMap:
             self.vars[k] = buf
         self.capacity = cap
         total = sum(self.widths[k] for k in self.grad_names) * cap + 4 * len(self.grad_names)
-        self.grad_flat = torch.zeros((total,), dtype=torch.float32, device=self.device)
+        self.grad_flat = self._new_grad_flat(total)
         self._carve()
 
 

@@ -102,6 +102,22 @@ def test_keyframe_schedule():
 
 
 @pytest.mark.timeout(300)
+def test_peer_allreduce_slices_partition_the_buffer():
+    """Slice ownership of the two-shot peer all-reduce (csrc/peer.cu): float4 granularity, disjoint, complete."""
+    import importlib
+
+    import isogs_b200  # noqa: F401
+    dp = importlib.import_module("isogs_slam_cpp_b200.dp")
+    for world in (1, 2, 3, 4, 5, 8, 16):
+        for numel in (0, 4, 8, 40, 1000, 4096 + 8, 8 * 1000 * 1000):
+            prev = 0
+            for r in range(world):
+                b, e = dp.slice_bounds(numel, world, r)
+                assert b == prev and e >= b and b % 4 == 0 and e % 4 == 0
+                prev = e
+            assert prev == numel
+
+
 def test_dp_mapping_world2_gloo(tmp_path):
     world, port = 2, _free_port()
     mp.spawn(_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
