@@ -104,6 +104,14 @@ def algorithmic_bytes(N, V, M, P, n_tiles):
     }
 
 
+_JSON_FD = 1
+
+
+def emit(line):
+    sys.stdout.flush()
+    os.write(_JSON_FD, (line + "\n").encode())
+
+
 def run_ours(args):
     import importlib
 
@@ -369,7 +377,7 @@ def run_ours(args):
     }
     if world == 1 and not args.no_cpu:
         out["cpu_baseline"] = cpu_baseline(syn, params, kfs, sample_steps=1)
-    print(json.dumps(out))
+    emit(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
 
@@ -438,7 +446,7 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     val = steps / dt
     cores = orc.lib().orc_num_threads()
-    print(json.dumps({
+    emit(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "iters/s", "n_gpus": world, "steps": steps,
         "warmup": warm, "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -461,6 +469,13 @@ def main():
     ap.add_argument("--allreduce", default="p2p", choices=["p2p", "nccl"],
                     help="gradient average at N > 1: own NVLink peer kernel (default) or NCCL")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: anything a library prints there (NCCL's version banner under
+    # NCCL_DEBUG=VERSION, torchrun notices) goes to stderr instead -- file descriptor 1 is pointed at stderr for
+    # the run and the line is written to the saved descriptor
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
