@@ -550,6 +550,17 @@ static int launch_bwd(const DevCam& dc, const float* rec, const int32_t* vals, c
     return ISOGS_OK;
 }
 
+namespace isogs {
+int launch_blend_bwd_lq(const DevCam& dc, int ch, int nw, bool geom, bool vec, const float* rec, const int32_t* vals,
+                        const int32_t* ranges, const float* alpha, const int32_t* last, const float* v_render,
+                        const float* v_alpha, float* v_rec, cudaStream_t stream); // blend_lq.cu
+}
+
+static int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+
 static int env_nw(const char* name, int dflt) {
     const char* e = getenv(name);
     const int v = e ? atoi(e) : dflt;
@@ -580,6 +591,8 @@ extern "C" int isogs_blend_bwd(const isogs_camera* cam, int ch, int64_t N, const
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
     static const int nw = env_nw("ISOGS_NW_BWD", NW_BWD);
+    static const int lq = env_int("ISOGS_BWD_LQ", 0); // 1: lane-per-quad kernel (blend_lq.cu), 2: same with scalar REDs
+    if (lq) return launch_blend_bwd_lq(dc, ch, nw, false, lq != 2, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
 #define ISOGS_BWD(CHN, NWN) \
     launch_bwd<CHN, NWN>(dc, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream)
     if (ch == 4) return nw == 2 ? ISOGS_BWD(4, 2) : nw == 8 ? ISOGS_BWD(4, 8) : ISOGS_BWD(4, 4);
@@ -597,6 +610,8 @@ extern "C" int isogs_blend_bwd_geom(const isogs_camera* cam, int ch, int64_t N, 
     (void)N;
     if (!cam || (ch != 4 && ch != 5)) { set_error("isogs_blend_bwd_geom: ch must be 4 or 5"); return ISOGS_E_ARG; }
     DevCam dc = make_devcam(*cam);
+    static const int lq = env_int("ISOGS_BWD_LQ", 0);
+    if (lq) return launch_blend_bwd_lq(dc, ch, env_nw("ISOGS_NW_BWD", NW_BWD), true, true, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
     if (ch == 4) return launch_bwd<4, 4, true>(dc, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
     return launch_bwd<5, 4, true>(dc, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
 }

@@ -1,0 +1,321 @@
+// blend_lq.cu -- north_star (4) backward alpha-blend, "lane-per-quad" variant.
+// Reference: gsplat RasterizeToPixels3DGSBwd.cu:15-278.
+//
+// Same warp-autonomous ring walk as blend.cu, but a LANE owns a whole 2x2 pixel quad (its four pixels
+// live in registers and are processed one after the other) and a warp owns a 16x8 half tile = 32 quads.
+// In one warp iteration every lane blends a different Gaussian (its quad's next hit) into its four
+// pixels, so the per-quad partial gradients are summed INSIDE the lane: no shuffle reduction, no
+// select network, and one quad's 11 gradient components leave as three 16-byte vector REDs into the
+// 48-byte gradient record instead of 12 scalar REDs from four lanes.  The cursor / ring bookkeeping
+// (about 35 instructions per warp iteration) is shared by 32 (quad, Gaussian) pairs instead of 8.
+//
+// The sigma expression is the one of blend.cu / the oracle (explicit round-to-nearest intrinsics), so the
+// contribute / skip decision of every pixel is the forward's.
+#include <cstdlib>
+
+#include "common.cuh"
+
+namespace isogs {
+namespace lq {
+
+constexpr unsigned FULL = 0xffffffffu;
+constexpr int WARPS = 2;   // per tile: warp w owns rows [8w, 8w+8) of the 16x16 tile
+constexpr int THREADS = 32 * WARPS;
+constexpr int FAR = 0x01000000;
+
+template <int NW>
+struct __align__(16) Ring {
+    float4 g0[32 * NW]; // x, y, 0.5*conic_a, conic_b
+    float4 g1[32 * NW]; // 0.5*conic_c, L (= sigma_max), opacity, c0
+    float4 g2[32 * NW]; // c1, c2, c3 (depth), c4 (depth^2)
+    uint32_t hits[32 * NW]; // [ring word][quad]: which of the word's 32 Gaussians can touch the quad
+    int id[32 * NW];
+};
+
+struct Pf {
+    float4 g0, g1, g2;
+    int id;
+    bool have;
+};
+
+// list entry e of the backward walk is sorted index first - e
+__device__ __forceinline__ void prefetch(Pf& pf, int word, int first, int n_entries, const float4* __restrict__ rec,
+                                         const int32_t* __restrict__ vals, int lane) {
+    const int e = 32 * word + lane;
+    const int id = (e < n_entries) ? __ldg(vals + first - e) : -1;
+    pf.have = id >= 0;
+    pf.id = pf.have ? id : 0;
+    pf.g0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    pf.g1 = pf.g0;
+    pf.g2 = pf.g0;
+    if (pf.have) {
+        const float4* r = rec + 3 * (int64_t)id;
+        pf.g0 = __ldg(r);
+        pf.g1 = __ldg(r + 1);
+        pf.g2 = __ldg(r + 2);
+    }
+}
+
+// Commit the prefetched word into ring slot word % NW; lane q receives (and stores) the hit mask of quad q.
+// Footprint test as in blend.cu::quad_hits (squared half extents + Gershgorin circle, padded, conservative).
+template <int NW>
+__device__ __forceinline__ void commit(Ring<NW>& st, const Pf& pf, int word, float bx0, float by0, int lane) {
+    const unsigned wsl = ((unsigned)word & (NW - 1)) * 32u;
+    const unsigned slot = wsl + lane;
+    __syncwarp();
+    if (pf.have) {
+        st.g0[slot] = pf.g0;
+        st.g1[slot] = pf.g1;
+        st.g2[slot] = pf.g2;
+        st.id[slot] = pf.id;
+    }
+    float hx2 = -1.f, hy2 = -1.f, R2 = -1.f;
+    if (pf.have) {
+        const float a = 2.0f * pf.g0.z, b = pf.g0.w, c = 2.0f * pf.g1.x;
+        const float inv_det = __fdividef(1.0f, fmaf(a, c, -(b * b)));
+        const float twoL = 2.0f * pf.g1.y * inv_det;
+        const float cxx = c * twoL, cyy = a * twoL, cxy = fabsf(b * twoL);
+        hx2 = fmaf(cxx, 1.01f, 0.05f);
+        hy2 = fmaf(cyy, 1.01f, 0.05f);
+        R2 = fmaf(fmaxf(cxx, cyy) + cxy, 1.01f, 0.05f);
+    }
+    const float X = pf.g0.x - bx0, Y = pf.g0.y - by0; // relative to the region's first pixel centre
+    float ex2[8], ey2[4];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const float e = fmaxf(fmaxf((float)(2 * c) - X, X - (float)(2 * c + 1)), 0.f);
+        ex2[c] = e * e;
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const float e = fmaxf(fmaxf((float)(2 * r) - Y, Y - (float)(2 * r + 1)), 0.f);
+        ey2[r] = (e * e <= hy2) ? e * e : 3.0e38f; // fold the y-extent test into the circle test
+    }
+    uint32_t bits = 0;
+#pragma unroll
+    for (int q = 0; q < 32; ++q) {
+        const float ex = ex2[q & 7];
+        const bool hit = ex <= hx2 && ex + ey2[q >> 3] <= R2;
+        const uint32_t m = __ballot_sync(FULL, hit);
+        if (lane == q) bits = m;
+    }
+    st.hits[slot] = bits;
+    __syncwarp();
+}
+
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// GEOM = true: tracking (only x, y, conic, z, z^2 gradients are produced; see blend.cu).
+template <int CH, int NW, bool GEOM, bool VEC>
+__global__ void __launch_bounds__(THREADS, 8)
+blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
+                    const int32_t* __restrict__ ranges, const float* __restrict__ alpha,
+                    const int32_t* __restrict__ last, const float* __restrict__ v_render,
+                    const float* __restrict__ v_alpha, float* __restrict__ v_rec) {
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    Ring<NW>& st = reinterpret_cast<Ring<NW>*>(s_raw)[wid];
+    const int tile = blockIdx.y * cam.tw + blockIdx.x;
+    const int qx = lane & 7, qy = lane >> 3;
+    const int x0 = blockIdx.x * TILE + 2 * qx, y0 = blockIdx.y * TILE + 8 * wid + 2 * qy;
+    const float bx0 = (float)(blockIdx.x * TILE) + 0.5f, by0 = (float)(blockIdx.y * TILE + 8 * wid) + 0.5f;
+    const float pxa = (float)x0 + 0.5f, pxb = (float)x0 + 1.5f, pya = (float)y0 + 0.5f, pyb = (float)y0 + 1.5f;
+    const int start = ranges[tile];
+    const int64_t P = (int64_t)cam.width * cam.height;
+
+    int first[4]; // first list entry (back to front) that contributed to pixel p
+    float T[4], bdot[4], va_eff[4], vr[4][CH];
+    int quad_last = start - 1;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        const int xi = x0 + (p & 1), yi = y0 + (p >> 1);
+        const bool inside = xi < cam.width && yi < cam.height;
+        const int64_t pix = inside ? (int64_t)yi * cam.width + xi : 0;
+        const int my_last = inside ? last[pix] : start - 1;
+        first[p] = my_last; // turned into an entry index below
+        quad_last = max(quad_last, my_last);
+        const float T_final = inside ? 1.0f - alpha[pix] : 1.0f;
+        T[p] = T_final;
+#pragma unroll
+        for (int k = 0; k < CH; ++k) vr[p][k] = inside ? v_render[k * P + pix] : 0.f;
+        const float va = (inside && v_alpha) ? v_alpha[pix] : 0.f;
+        float bg_dot = 0.f;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) bg_dot += cam.bg[k] * vr[p][k];
+        va_eff[p] = T_final * (va - bg_dot);
+        bdot[p] = 0.f;
+    }
+    const int warp_last = __reduce_max_sync(FULL, quad_last);
+    if (warp_last < start) return; // nothing was blended into this warp's half tile
+    const int n_entries = warp_last - start + 1;
+    const int n_words = (n_entries + 31) >> 5;
+    const int e_first = warp_last - quad_last;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) first[p] = warp_last - first[p];
+
+    int staged = 0, base = 0; // warp-uniform: words [base, staged) are live in the ring
+    Pf pf;
+    prefetch(pf, 0, warp_last, n_entries, rec, vals, lane);
+    for (; staged < min(NW, n_words); ++staged) {
+        commit<NW>(st, pf, staged, bx0, by0, lane);
+        prefetch(pf, staged + 1, warp_last, n_entries, rec, vals, lane);
+    }
+    static_assert((NW & (NW - 1)) == 0, "NW must be a power of two");
+    const uint32_t* hq = st.hits + lane; // this quad's hit word of ring slot base wsl is hq[wsl]
+    auto fetch = [&](int w, unsigned wsl_) -> uint32_t {
+        const uint32_t m = hq[wsl_];
+        const int cut = e_first - 32 * w; // entries in front of e_first lie behind this quad's last contributor
+        return cut <= 0 ? m : (cut >= 32 ? 0u : (m & ~((1u << cut) - 1u)));
+    };
+    int jq = min(e_first >> 5, staged - 1);
+    unsigned wsl = ((unsigned)jq & (NW - 1)) * 32u;
+    uint32_t bits = fetch(jq, wsl);
+    if (quad_last < start) { jq = FAR; bits = 0u; wsl = 0u; }
+    while (true) {
+        if (bits == 0u && jq + 1 < staged) {
+            ++jq;
+            wsl = (wsl + 32u) & (32u * NW - 1u);
+            bits = fetch(jq, wsl);
+        }
+        const bool act = bits != 0u;
+        const int wmin = __reduce_min_sync(FULL, act ? jq : jq + 1);
+        if (wmin >= n_words) break;
+        const int s = act ? __ffs(bits) - 1 : 0;
+        bits &= bits - 1u;
+        const unsigned slot = wsl + s;
+        const float4 g0s = st.g0[slot];
+        const float4 g1s = st.g1[slot];
+        const int e = act ? 32 * jq + s : -1;
+        const float dxa = __fsub_rn(g0s.x, pxa), dxb = __fsub_rn(g0s.x, pxb);
+        const float dya = __fsub_rn(g0s.y, pya), dyb = __fsub_rn(g0s.y, pyb);
+        const float zxa = __fmul_rn(g0s.z, dxa), zxb = __fmul_rn(g0s.z, dxb);
+        const float cya = __fmul_rn(__fmul_rn(g1s.x, dya), dya), cyb = __fmul_rn(__fmul_rn(g1s.x, dyb), dyb);
+        float sigma[4];
+        sigma[0] = __fmaf_rn(__fmaf_rn(g0s.w, dya, zxa), dxa, cya);
+        sigma[1] = __fmaf_rn(__fmaf_rn(g0s.w, dya, zxb), dxb, cya);
+        sigma[2] = __fmaf_rn(__fmaf_rn(g0s.w, dyb, zxa), dxa, cyb);
+        sigma[3] = __fmaf_rn(__fmaf_rn(g0s.w, dyb, zxb), dxb, cyb);
+        bool valid[4];
+        bool anyv = false;
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            valid[p] = e >= first[p] && sigma[p] >= 0.f && sigma[p] <= g1s.y;
+            anyv |= valid[p];
+        }
+        if (__any_sync(FULL, anyv)) {
+            const float4 g2 = st.g2[slot];
+            const float opac = g1s.z;
+            float Swx = 0.f, Swy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f, Su = 0.f;
+            float col[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+                const float dx = (p & 1) ? dxb : dxa, dy = (p >> 1) ? dyb : dya;
+                // branch-free: an invalid pixel runs with sigma = 0 and contributes exact zeros
+                const float vis = __expf(valid[p] ? -sigma[p] : 0.f);
+                const float ov = opac * vis;
+                const float a = fminf(MAX_ALPHA, ov);
+                const float ra = __fdividef(1.0f, 1.0f - a);
+                const float Tn = T[p] * ra; // transmittance in front of this Gaussian
+                T[p] = valid[p] ? Tn : T[p];
+                const float fac = valid[p] ? a * Tn : 0.f;
+                float cdot = g1s.w * vr[p][0];
+                cdot = fmaf(g2.x, vr[p][1], cdot);
+                cdot = fmaf(g2.y, vr[p][2], cdot);
+                cdot = fmaf(g2.z, vr[p][3], cdot);
+                if (CH == 5) cdot = fmaf(g2.w, vr[p][CH - 1], cdot);
+                const float v_a = fmaf(Tn, cdot, ra * (va_eff[p] - bdot[p]));
+                bdot[p] = fmaf(fac, cdot, bdot[p]);
+                const float u = (valid[p] && ov <= MAX_ALPHA) ? vis * v_a : 0.f;
+                const float v_sigma = -opac * u;
+                const float wx = v_sigma * dx, wy = v_sigma * dy;
+                Swx += wx;
+                Swy += wy;
+                Sxx = fmaf(wx, dx, Sxx);
+                Sxy = fmaf(wx, dy, Sxy);
+                Syy = fmaf(wy, dy, Syy);
+                if (!GEOM) {
+                    Su += u;
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) col[k] = fmaf(fac, vr[p][k], col[k]);
+                }
+#pragma unroll
+                for (int k = 3; k < CH; ++k) col[k] = fmaf(fac, vr[p][k], col[k]);
+            }
+            if (anyv) {
+                const float ca = 2.0f * g0s.z, cb = g0s.w, cc = 2.0f * g1s.x;
+                const float v0 = fmaf(ca, Swx, cb * Swy), v1 = fmaf(cb, Swx, cc * Swy);
+                float* dst = v_rec + (int64_t)st.id[slot] * REC;
+                if (VEC) {
+                    red_add_v4(dst, v0, v1, 0.5f * Sxx, Sxy);
+                    if (GEOM) {
+                        atomicAdd(dst + 4, 0.5f * Syy);
+                        red_add_v4(dst + 8, 0.f, col[3], col[4], 0.f);
+                    } else {
+                        red_add_v4(dst + 4, 0.5f * Syy, Su, col[0], col[1]);
+                        red_add_v4(dst + 8, col[2], col[3], col[4], 0.f);
+                    }
+                } else {
+                    atomicAdd(dst + 0, v0);
+                    atomicAdd(dst + 1, v1);
+                    atomicAdd(dst + 2, 0.5f * Sxx);
+                    atomicAdd(dst + 3, Sxy);
+                    atomicAdd(dst + 4, 0.5f * Syy);
+                    if (!GEOM) {
+                        atomicAdd(dst + 5, Su);
+                        atomicAdd(dst + 6, col[0]);
+                        atomicAdd(dst + 7, col[1]);
+                        atomicAdd(dst + 8, col[2]);
+                    }
+                    atomicAdd(dst + 9, col[3]);
+                    if (CH == 5) atomicAdd(dst + 10, col[4]);
+                }
+            }
+        }
+        if (wmin > base) {
+            ++base;
+            if (staged < n_words) {
+                commit<NW>(st, pf, staged, bx0, by0, lane);
+                ++staged;
+                prefetch(pf, staged, warp_last, n_entries, rec, vals, lane);
+            }
+        }
+    }
+}
+
+template <int CH, int NW, bool GEOM, bool VEC>
+int launch(const DevCam& dc, const float* rec, const int32_t* vals, const int32_t* ranges, const float* alpha,
+           const int32_t* last, const float* v_render, const float* v_alpha, float* v_rec, cudaStream_t stream) {
+    constexpr size_t smem = sizeof(Ring<NW>) * WARPS;
+    static thread_local int attr_dev = -1;
+    int dev = 0;
+    ISOGS_CUDA(cudaGetDevice(&dev));
+    if (attr_dev != dev) {
+        ISOGS_CUDA(cudaFuncSetAttribute(blend_bwd_lq_kernel<CH, NW, GEOM, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)smem));
+        attr_dev = dev;
+    }
+    dim3 grid(dc.tw, dc.th);
+    blend_bwd_lq_kernel<CH, NW, GEOM, VEC><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last,
+                                                                            v_render, v_alpha, v_rec);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
+
+} // namespace lq
+
+// called by isogs_blend_bwd / isogs_blend_bwd_geom (blend.cu); nw in {4, 8}
+int launch_blend_bwd_lq(const DevCam& dc, int ch, int nw, bool geom, bool vec, const float* rec, const int32_t* vals,
+                        const int32_t* ranges, const float* alpha, const int32_t* last, const float* v_render,
+                        const float* v_alpha, float* v_rec, cudaStream_t stream) {
+#define LQ(CHN, NWN, G, V) lq::launch<CHN, NWN, G, V>(dc, rec, vals, ranges, alpha, last, v_render, v_alpha, v_rec, stream)
+#define LQ_NW(CHN, G, V) (nw == 8 ? LQ(CHN, 8, G, V) : LQ(CHN, 4, G, V))
+    if (geom) return ch == 4 ? LQ_NW(4, true, true) : LQ_NW(5, true, true);
+    if (!vec) return ch == 4 ? LQ_NW(4, false, false) : LQ_NW(5, false, false);
+    return ch == 4 ? LQ_NW(4, false, true) : LQ_NW(5, false, true);
+#undef LQ_NW
+#undef LQ
+}
+
+} // namespace isogs
