@@ -554,6 +554,8 @@ namespace isogs {
 int launch_blend_bwd_lq(const DevCam& dc, int ch, int nw, bool geom, bool vec, const float* rec, const int32_t* vals,
                         const int32_t* ranges, const float* alpha, const int32_t* last, const float* v_render,
                         const float* v_alpha, float* v_rec, cudaStream_t stream); // blend_lq.cu
+int launch_blend_fwd_lq(const DevCam& dc, int ch, int nw, const float* rec, const int32_t* vals, const int32_t* ranges,
+                        float* render, float* alpha, int32_t* last, cudaStream_t stream);
 }
 
 static int env_int(const char* name, int dflt) {
@@ -575,6 +577,8 @@ extern "C" int isogs_blend_fwd(const isogs_camera* cam, int ch, const float* rec
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
     static const int nw = env_nw("ISOGS_NW_FWD", NW_FWD); // ring words per warp (tuning knob)
+    static const int lq = env_int("ISOGS_FWD_LQ", 0); // 1: lane-per-quad kernel (blend_lq.cu)
+    if (lq) return launch_blend_fwd_lq(dc, ch, nw, rec, vals_sorted, tile_ranges, render, alpha, last, stream);
 #define ISOGS_FWD(CHN, NWN) launch_fwd<CHN, NWN>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, stream)
     if (ch == 4) return nw == 2 ? ISOGS_FWD(4, 2) : nw == 8 ? ISOGS_FWD(4, 8) : ISOGS_FWD(4, 4);
     return nw == 2 ? ISOGS_FWD(5, 2) : nw == 8 ? ISOGS_FWD(5, 8) : ISOGS_FWD(5, 4);

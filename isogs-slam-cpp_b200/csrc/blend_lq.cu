@@ -23,13 +23,13 @@ constexpr int WARPS = 2;   // per tile: warp w owns rows [8w, 8w+8) of the 16x16
 constexpr int THREADS = 32 * WARPS;
 constexpr int FAR = 0x01000000;
 
-template <int NW>
+template <int NW, bool WITH_ID = true>
 struct __align__(16) Ring {
     float4 g0[32 * NW]; // x, y, 0.5*conic_a, conic_b
     float4 g1[32 * NW]; // 0.5*conic_c, L (= sigma_max), opacity, c0
     float4 g2[32 * NW]; // c1, c2, c3 (depth), c4 (depth^2)
     uint32_t hits[32 * NW]; // [ring word][quad]: which of the word's 32 Gaussians can touch the quad
-    int id[32 * NW];
+    int id[WITH_ID ? 32 * NW : 4];
 };
 
 struct Pf {
@@ -38,11 +38,12 @@ struct Pf {
     bool have;
 };
 
-// list entry e of the backward walk is sorted index first - e
+// list entry e is sorted index first + DIR * e (backward walk: DIR = -1)
+template <int DIR = -1>
 __device__ __forceinline__ void prefetch(Pf& pf, int word, int first, int n_entries, const float4* __restrict__ rec,
                                          const int32_t* __restrict__ vals, int lane) {
     const int e = 32 * word + lane;
-    const int id = (e < n_entries) ? __ldg(vals + first - e) : -1;
+    const int id = (e < n_entries) ? __ldg(vals + first + DIR * e) : -1;
     pf.have = id >= 0;
     pf.id = pf.have ? id : 0;
     pf.g0 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -58,8 +59,8 @@ __device__ __forceinline__ void prefetch(Pf& pf, int word, int first, int n_entr
 
 // Commit the prefetched word into ring slot word % NW; lane q receives (and stores) the hit mask of quad q.
 // Footprint test as in blend.cu::quad_hits (squared half extents + Gershgorin circle, padded, conservative).
-template <int NW>
-__device__ __forceinline__ void commit(Ring<NW>& st, const Pf& pf, int word, float bx0, float by0, int lane) {
+template <int NW, bool WITH_ID>
+__device__ __forceinline__ void commit(Ring<NW, WITH_ID>& st, const Pf& pf, int word, float bx0, float by0, int lane) {
     const unsigned wsl = ((unsigned)word & (NW - 1)) * 32u;
     const unsigned slot = wsl + lane;
     __syncwarp();
@@ -67,7 +68,7 @@ __device__ __forceinline__ void commit(Ring<NW>& st, const Pf& pf, int word, flo
         st.g0[slot] = pf.g0;
         st.g1[slot] = pf.g1;
         st.g2[slot] = pf.g2;
-        st.id[slot] = pf.id;
+        if (WITH_ID) st.id[slot] = pf.id;
     }
     float hx2 = -1.f, hy2 = -1.f, R2 = -1.f;
     if (pf.have) {
@@ -159,7 +160,7 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
     Pf pf;
     prefetch(pf, 0, warp_last, n_entries, rec, vals, lane);
     for (; staged < min(NW, n_words); ++staged) {
-        commit<NW>(st, pf, staged, bx0, by0, lane);
+        commit<NW, true>(st, pf, staged, bx0, by0, lane);
         prefetch(pf, staged + 1, warp_last, n_entries, rec, vals, lane);
     }
     static_assert((NW & (NW - 1)) == 0, "NW must be a power of two");
@@ -276,12 +277,151 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
         if (wmin > base) {
             ++base;
             if (staged < n_words) {
-                commit<NW>(st, pf, staged, bx0, by0, lane);
+                commit<NW, true>(st, pf, staged, bx0, by0, lane);
                 ++staged;
                 prefetch(pf, staged, warp_last, n_entries, rec, vals, lane);
             }
         }
     }
+}
+
+// Forward, same organisation: a lane owns a 2x2 quad (T, 5 accumulators, last index per pixel in registers), a warp a
+// 16x8 half tile.  Reference: gsplat RasterizeToPixels3DGSFwd.cu:17-188.  The per-pixel body is predicated, not
+// branched; the contribute / saturate decisions are those of blend.cu::blend_fwd_kernel.
+template <int CH, int NW>
+__global__ void __launch_bounds__(THREADS, 8)
+blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
+                    const int32_t* __restrict__ ranges, float* __restrict__ render, float* __restrict__ alpha,
+                    int32_t* __restrict__ last) {
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    using R = Ring<NW, false>;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    R& st = reinterpret_cast<R*>(s_raw)[wid];
+    const int tile = blockIdx.y * cam.tw + blockIdx.x;
+    const int qx = lane & 7, qy = lane >> 3;
+    const int x0 = blockIdx.x * TILE + 2 * qx, y0 = blockIdx.y * TILE + 8 * wid + 2 * qy;
+    const float bx0 = (float)(blockIdx.x * TILE) + 0.5f, by0 = (float)(blockIdx.y * TILE + 8 * wid) + 0.5f;
+    const float pxa = (float)x0 + 0.5f, pxb = (float)x0 + 1.5f, pya = (float)y0 + 0.5f, pyb = (float)y0 + 1.5f;
+    const int start = ranges[tile], end = ranges[tile + 1];
+    const int n_entries = end - start;
+    const int n_words = (n_entries + 31) >> 5;
+
+    float T[4], acc[4][CH];
+    int last_idx[4];
+    bool done[4];
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        T[p] = 1.0f;
+        last_idx[p] = start - 1;
+        done[p] = !(x0 + (p & 1) < cam.width && y0 + (p >> 1) < cam.height);
+#pragma unroll
+        for (int k = 0; k < CH; ++k) acc[p][k] = 0.f;
+    }
+    bool quad_done = done[0] && done[1] && done[2] && done[3];
+
+    if (n_words > 0 && !__all_sync(FULL, quad_done)) {
+        int staged = 0, base = 0;
+        Pf pf;
+        prefetch<1>(pf, 0, start, n_entries, rec, vals, lane);
+        for (; staged < min(NW, n_words); ++staged) {
+            commit<NW, false>(st, pf, staged, bx0, by0, lane);
+            prefetch<1>(pf, staged + 1, start, n_entries, rec, vals, lane);
+        }
+        const uint32_t* hq = st.hits + lane;
+        int jq = 0;
+        unsigned wsl = 0;
+        uint32_t bits = hq[0];
+        if (quad_done) { jq = FAR; bits = 0u; }
+        while (true) {
+            if (bits == 0u && jq + 1 < staged) {
+                ++jq;
+                wsl = (wsl + 32u) & (32u * NW - 1u);
+                bits = hq[wsl];
+            }
+            const bool act = bits != 0u;
+            const int wmin = __reduce_min_sync(FULL, act ? jq : jq + 1);
+            if (wmin >= n_words) break;
+            const int s = act ? __ffs(bits) - 1 : 0;
+            bits &= bits - 1u;
+            const unsigned slot = wsl + s;
+            const float4 g0s = st.g0[slot];
+            const float4 g1s = st.g1[slot];
+            const float dxa = __fsub_rn(g0s.x, pxa), dxb = __fsub_rn(g0s.x, pxb);
+            const float dya = __fsub_rn(g0s.y, pya), dyb = __fsub_rn(g0s.y, pyb);
+            const float zxa = __fmul_rn(g0s.z, dxa), zxb = __fmul_rn(g0s.z, dxb);
+            const float cya = __fmul_rn(__fmul_rn(g1s.x, dya), dya), cyb = __fmul_rn(__fmul_rn(g1s.x, dyb), dyb);
+            float sigma[4];
+            sigma[0] = __fmaf_rn(__fmaf_rn(g0s.w, dya, zxa), dxa, cya);
+            sigma[1] = __fmaf_rn(__fmaf_rn(g0s.w, dya, zxb), dxb, cya);
+            sigma[2] = __fmaf_rn(__fmaf_rn(g0s.w, dyb, zxa), dxa, cyb);
+            sigma[3] = __fmaf_rn(__fmaf_rn(g0s.w, dyb, zxb), dxb, cyb);
+            bool hit[4];
+            bool anyh = false;
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+                hit[p] = act && !done[p] && sigma[p] >= 0.f && sigma[p] <= g1s.y;
+                anyh |= hit[p];
+            }
+            if (__any_sync(FULL, anyh)) {
+                const float4 g2 = st.g2[slot];
+                const int idx = start + 32 * jq + s;
+#pragma unroll
+                for (int p = 0; p < 4; ++p) {
+                    const float a = fminf(MAX_ALPHA, g1s.z * __expf(hit[p] ? -sigma[p] : 0.f));
+                    const float nT = T[p] * (1.0f - a);
+                    const bool sat = hit[p] && nT <= T_CUTOFF;
+                    const bool contrib = hit[p] && !sat;
+                    done[p] = done[p] || sat;
+                    const float vis = contrib ? a * T[p] : 0.f;
+                    acc[p][0] = fmaf(g1s.w, vis, acc[p][0]);
+                    acc[p][1] = fmaf(g2.x, vis, acc[p][1]);
+                    acc[p][2] = fmaf(g2.y, vis, acc[p][2]);
+                    acc[p][3] = fmaf(g2.z, vis, acc[p][3]);
+                    if (CH == 5) acc[p][CH - 1] = fmaf(g2.w, vis, acc[p][CH - 1]);
+                    last_idx[p] = contrib ? idx : last_idx[p];
+                    T[p] = contrib ? nT : T[p];
+                }
+                if (done[0] && done[1] && done[2] && done[3]) { jq = FAR; bits = 0u; } // quad saturated
+            }
+            if (wmin > base) {
+                ++base;
+                if (staged < n_words) {
+                    commit<NW, false>(st, pf, staged, bx0, by0, lane);
+                    ++staged;
+                    prefetch<1>(pf, staged, start, n_entries, rec, vals, lane);
+                }
+            }
+        }
+    }
+    const int64_t P = (int64_t)cam.width * cam.height;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        const int xi = x0 + (p & 1), yi = y0 + (p >> 1);
+        if (xi < cam.width && yi < cam.height) {
+            const int64_t pix = (int64_t)yi * cam.width + xi;
+#pragma unroll
+            for (int k = 0; k < CH; ++k) render[k * P + pix] = (k < 3) ? fmaf(T[p], cam.bg[k], acc[p][k]) : acc[p][k];
+            alpha[pix] = 1.0f - T[p];
+            last[pix] = last_idx[p];
+        }
+    }
+}
+
+template <int CH, int NW>
+int launch_fwd(const DevCam& dc, const float* rec, const int32_t* vals, const int32_t* ranges, float* render, float* alpha,
+               int32_t* last, cudaStream_t stream) {
+    constexpr size_t smem = sizeof(Ring<NW, false>) * WARPS;
+    static thread_local int attr_dev = -1;
+    int dev = 0;
+    ISOGS_CUDA(cudaGetDevice(&dev));
+    if (attr_dev != dev) {
+        ISOGS_CUDA(cudaFuncSetAttribute(blend_fwd_lq_kernel<CH, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_dev = dev;
+    }
+    dim3 grid(dc.tw, dc.th);
+    blend_fwd_lq_kernel<CH, NW><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, render, alpha, last);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
 }
 
 template <int CH, int NW, bool GEOM, bool VEC>
@@ -316,6 +456,14 @@ int launch_blend_bwd_lq(const DevCam& dc, int ch, int nw, bool geom, bool vec, c
     return ch == 4 ? LQ_NW(4, false, true) : LQ_NW(5, false, true);
 #undef LQ_NW
 #undef LQ
+}
+
+int launch_blend_fwd_lq(const DevCam& dc, int ch, int nw, const float* rec, const int32_t* vals, const int32_t* ranges,
+                        float* render, float* alpha, int32_t* last, cudaStream_t stream) {
+#define LQF(CHN, NWN) lq::launch_fwd<CHN, NWN>(dc, rec, vals, ranges, render, alpha, last, stream)
+    if (ch == 4) return nw == 8 ? LQF(4, 8) : LQF(4, 4);
+    return nw == 8 ? LQF(5, 8) : LQF(5, 4);
+#undef LQF
 }
 
 } // namespace isogs
