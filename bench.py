@@ -369,7 +369,7 @@ def run_ours(args):
         "roofline": {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes": ab[dom], "issue_active_pct_ncu": issue_pct,
-                     "note": "the blend kernels are instruction-issue bound (ncu: issue slots 77-82 % busy, DRAM < 5 % of "
+                     "note": "the blend kernels are instruction-issue bound (ncu: issue slots 62-64 % busy at 14-16 resident warps per SM, DRAM < 5 % of "
                              "peak), not HBM bound (SURVEY 8(d)); achieved = algorithmic bytes / CUDA-event time of the "
                              "stage inside the timed region; traffic = ncu dram read+write of one launch "
                              "(profiles/traffic.json)"},

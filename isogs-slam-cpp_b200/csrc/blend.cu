@@ -495,7 +495,7 @@ blend_bwd_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __re
 using namespace isogs;
 
 namespace {
-constexpr int NW_FWD = 4, NW_BWD = 4;
+constexpr int NW_FWD = 4, NW_BWD = 4, NW_LQ = 8;
 
 template <typename K>
 int set_smem(K kernel, size_t bytes) {
@@ -551,7 +551,7 @@ static int launch_bwd(const DevCam& dc, const float* rec, const int32_t* vals, c
 }
 
 namespace isogs {
-int launch_blend_bwd_lq(const DevCam& dc, int ch, int nw, bool geom, bool vec, const float* rec, const int32_t* vals,
+int launch_blend_bwd_lq(const DevCam& dc, int ch, int nw, bool geom, bool vec, bool idg, const float* rec, const int32_t* vals,
                         const int32_t* ranges, const float* alpha, const int32_t* last, const float* v_render,
                         const float* v_alpha, float* v_rec, cudaStream_t stream); // blend_lq.cu
 int launch_blend_fwd_lq(const DevCam& dc, int ch, int nw, const float* rec, const int32_t* vals, const int32_t* ranges,
@@ -576,8 +576,10 @@ extern "C" int isogs_blend_fwd(const isogs_camera* cam, int ch, const float* rec
     if (!cam || (ch != 4 && ch != 5)) { set_error("isogs_blend_fwd: ch must be 4 or 5"); return ISOGS_E_ARG; }
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
-    static const int nw = env_nw("ISOGS_NW_FWD", NW_FWD); // ring words per warp (tuning knob)
-    static const int lq = env_int("ISOGS_FWD_LQ", 0); // 1: lane-per-quad kernel (blend_lq.cu)
+    // default: the lane-per-quad kernel of blend_lq.cu with a ring of 8 words; ISOGS_FWD_LQ=0 selects the
+    // quad-of-lanes kernel above (ring of 4 words), kept as the A/B baseline
+    static const int lq = env_int("ISOGS_FWD_LQ", 1);
+    static const int nw = env_nw("ISOGS_NW_FWD", lq ? NW_LQ : NW_FWD); // ring words per warp (tuning knob)
     if (lq) return launch_blend_fwd_lq(dc, ch, nw, rec, vals_sorted, tile_ranges, render, alpha, last, stream);
 #define ISOGS_FWD(CHN, NWN) launch_fwd<CHN, NWN>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, stream)
     if (ch == 4) return nw == 2 ? ISOGS_FWD(4, 2) : nw == 8 ? ISOGS_FWD(4, 8) : ISOGS_FWD(4, 4);
@@ -594,9 +596,9 @@ extern "C" int isogs_blend_bwd(const isogs_camera* cam, int ch, int64_t N, const
     if (!cam || (ch != 4 && ch != 5)) { set_error("isogs_blend_bwd: ch must be 4 or 5"); return ISOGS_E_ARG; }
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
-    static const int nw = env_nw("ISOGS_NW_BWD", NW_BWD);
-    static const int lq = env_int("ISOGS_BWD_LQ", 0); // 1: lane-per-quad kernel (blend_lq.cu), 2: same with scalar REDs
-    if (lq) return launch_blend_bwd_lq(dc, ch, nw, false, lq != 2, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
+    static const int lq = env_int("ISOGS_BWD_LQ", 1); // 1 (default): lane-per-quad kernel (blend_lq.cu), 2: same with scalar REDs, 0: quad-of-lanes kernel
+    static const int nw = env_nw("ISOGS_NW_BWD", lq ? NW_LQ : NW_BWD);
+    if (lq) return launch_blend_bwd_lq(dc, ch, nw, false, lq != 2, lq == 3, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
 #define ISOGS_BWD(CHN, NWN) \
     launch_bwd<CHN, NWN>(dc, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream)
     if (ch == 4) return nw == 2 ? ISOGS_BWD(4, 2) : nw == 8 ? ISOGS_BWD(4, 8) : ISOGS_BWD(4, 4);
@@ -614,8 +616,8 @@ extern "C" int isogs_blend_bwd_geom(const isogs_camera* cam, int ch, int64_t N, 
     (void)N;
     if (!cam || (ch != 4 && ch != 5)) { set_error("isogs_blend_bwd_geom: ch must be 4 or 5"); return ISOGS_E_ARG; }
     DevCam dc = make_devcam(*cam);
-    static const int lq = env_int("ISOGS_BWD_LQ", 0);
-    if (lq) return launch_blend_bwd_lq(dc, ch, env_nw("ISOGS_NW_BWD", NW_BWD), true, true, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
+    static const int lq = env_int("ISOGS_BWD_LQ", 1);
+    if (lq) return launch_blend_bwd_lq(dc, ch, env_nw("ISOGS_NW_BWD", NW_LQ), true, true, lq == 3, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
     if (ch == 4) return launch_bwd<4, 4, true>(dc, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
     return launch_bwd<5, 4, true>(dc, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
 }

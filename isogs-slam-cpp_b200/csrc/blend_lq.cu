@@ -81,7 +81,9 @@ __device__ __forceinline__ void commit(Ring<NW, WITH_ID>& st, const Pf& pf, int 
         R2 = fmaf(fmaxf(cxx, cyy) + cxy, 1.01f, 0.05f);
     }
     const float X = pf.g0.x - bx0, Y = pf.g0.y - by0; // relative to the region's first pixel centre
-    float ex2[8], ey2[4];
+    // per quad row r the three tests (x extent, y extent, circle) collapse into one threshold on ex2:
+    // ex2 <= min(hx2, R2 - ey2[r]) if ey2[r] <= hy2, never otherwise
+    float ex2[8], thr[4];
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
         const float e = fmaxf(fmaxf((float)(2 * c) - X, X - (float)(2 * c + 1)), 0.f);
@@ -90,17 +92,14 @@ __device__ __forceinline__ void commit(Ring<NW, WITH_ID>& st, const Pf& pf, int 
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
         const float e = fmaxf(fmaxf((float)(2 * r) - Y, Y - (float)(2 * r + 1)), 0.f);
-        ey2[r] = (e * e <= hy2) ? e * e : 3.0e38f; // fold the y-extent test into the circle test
+        const float e2 = e * e;
+        thr[r] = (e2 <= hy2) ? fminf(hx2, R2 - e2) : -1.f;
     }
-    uint32_t bits = 0;
 #pragma unroll
     for (int q = 0; q < 32; ++q) {
-        const float ex = ex2[q & 7];
-        const bool hit = ex <= hx2 && ex + ey2[q >> 3] <= R2;
-        const uint32_t m = __ballot_sync(FULL, hit);
-        if (lane == q) bits = m;
+        const uint32_t m = __ballot_sync(FULL, ex2[q & 7] <= thr[q >> 3]);
+        if (lane == 0) st.hits[wsl + q] = m;
     }
-    st.hits[slot] = bits;
     __syncwarp();
 }
 
@@ -109,7 +108,9 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
 }
 
 // GEOM = true: tracking (only x, y, conic, z, z^2 gradients are produced; see blend.cu).
-template <int CH, int NW, bool GEOM, bool VEC>
+// IDG = true: the ring keeps no Gaussian ids (13 KB per warp at NW = 8, so EIGHT CTAs fit an SM instead of seven);
+// the id of the entry a lane is about to blend is re-read from `vals` at the top of the iteration.
+template <int CH, int NW, bool GEOM, bool VEC, bool IDG>
 __global__ void __launch_bounds__(THREADS, 8)
 blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
                     const int32_t* __restrict__ ranges, const float* __restrict__ alpha,
@@ -117,7 +118,8 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                     const float* __restrict__ v_alpha, float* __restrict__ v_rec) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    Ring<NW>& st = reinterpret_cast<Ring<NW>*>(s_raw)[wid];
+    using R = Ring<NW, !IDG>;
+    R& st = reinterpret_cast<R*>(s_raw)[wid];
     const int tile = blockIdx.y * cam.tw + blockIdx.x;
     const int qx = lane & 7, qy = lane >> 3;
     const int x0 = blockIdx.x * TILE + 2 * qx, y0 = blockIdx.y * TILE + 8 * wid + 2 * qy;
@@ -160,7 +162,7 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
     Pf pf;
     prefetch(pf, 0, warp_last, n_entries, rec, vals, lane);
     for (; staged < min(NW, n_words); ++staged) {
-        commit<NW, true>(st, pf, staged, bx0, by0, lane);
+        commit<NW, !IDG>(st, pf, staged, bx0, by0, lane);
         prefetch(pf, staged + 1, warp_last, n_entries, rec, vals, lane);
     }
     static_assert((NW & (NW - 1)) == 0, "NW must be a power of two");
@@ -189,6 +191,8 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
         const float4 g0s = st.g0[slot];
         const float4 g1s = st.g1[slot];
         const int e = act ? 32 * jq + s : -1;
+        int gid = 0;
+        if (IDG) gid = __ldg(vals + warp_last - max(e, 0));
         const float dxa = __fsub_rn(g0s.x, pxa), dxb = __fsub_rn(g0s.x, pxb);
         const float dya = __fsub_rn(g0s.y, pya), dyb = __fsub_rn(g0s.y, pyb);
         const float zxa = __fmul_rn(g0s.z, dxa), zxb = __fmul_rn(g0s.z, dxb);
@@ -247,7 +251,7 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
             if (anyv) {
                 const float ca = 2.0f * g0s.z, cb = g0s.w, cc = 2.0f * g1s.x;
                 const float v0 = fmaf(ca, Swx, cb * Swy), v1 = fmaf(cb, Swx, cc * Swy);
-                float* dst = v_rec + (int64_t)st.id[slot] * REC;
+                float* dst = v_rec + (int64_t)(IDG ? gid : st.id[slot]) * REC;
                 if (VEC) {
                     red_add_v4(dst, v0, v1, 0.5f * Sxx, Sxy);
                     if (GEOM) {
@@ -277,7 +281,7 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
         if (wmin > base) {
             ++base;
             if (staged < n_words) {
-                commit<NW, true>(st, pf, staged, bx0, by0, lane);
+                commit<NW, !IDG>(st, pf, staged, bx0, by0, lane);
                 ++staged;
                 prefetch(pf, staged, warp_last, n_entries, rec, vals, lane);
             }
@@ -424,20 +428,20 @@ int launch_fwd(const DevCam& dc, const float* rec, const int32_t* vals, const in
     return ISOGS_OK;
 }
 
-template <int CH, int NW, bool GEOM, bool VEC>
+template <int CH, int NW, bool GEOM, bool VEC, bool IDG>
 int launch(const DevCam& dc, const float* rec, const int32_t* vals, const int32_t* ranges, const float* alpha,
            const int32_t* last, const float* v_render, const float* v_alpha, float* v_rec, cudaStream_t stream) {
-    constexpr size_t smem = sizeof(Ring<NW>) * WARPS;
+    constexpr size_t smem = sizeof(Ring<NW, !IDG>) * WARPS;
     static thread_local int attr_dev = -1;
     int dev = 0;
     ISOGS_CUDA(cudaGetDevice(&dev));
     if (attr_dev != dev) {
-        ISOGS_CUDA(cudaFuncSetAttribute(blend_bwd_lq_kernel<CH, NW, GEOM, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        ISOGS_CUDA(cudaFuncSetAttribute(blend_bwd_lq_kernel<CH, NW, GEOM, VEC, IDG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)smem));
         attr_dev = dev;
     }
     dim3 grid(dc.tw, dc.th);
-    blend_bwd_lq_kernel<CH, NW, GEOM, VEC><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last,
+    blend_bwd_lq_kernel<CH, NW, GEOM, VEC, IDG><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last,
                                                                             v_render, v_alpha, v_rec);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
@@ -446,14 +450,18 @@ int launch(const DevCam& dc, const float* rec, const int32_t* vals, const int32_
 } // namespace lq
 
 // called by isogs_blend_bwd / isogs_blend_bwd_geom (blend.cu); nw in {4, 8}
-int launch_blend_bwd_lq(const DevCam& dc, int ch, int nw, bool geom, bool vec, const float* rec, const int32_t* vals,
+int launch_blend_bwd_lq(const DevCam& dc, int ch, int nw, bool geom, bool vec, bool idg, const float* rec, const int32_t* vals,
                         const int32_t* ranges, const float* alpha, const int32_t* last, const float* v_render,
                         const float* v_alpha, float* v_rec, cudaStream_t stream) {
-#define LQ(CHN, NWN, G, V) lq::launch<CHN, NWN, G, V>(dc, rec, vals, ranges, alpha, last, v_render, v_alpha, v_rec, stream)
-#define LQ_NW(CHN, G, V) (nw == 8 ? LQ(CHN, 8, G, V) : LQ(CHN, 4, G, V))
-    if (geom) return ch == 4 ? LQ_NW(4, true, true) : LQ_NW(5, true, true);
-    if (!vec) return ch == 4 ? LQ_NW(4, false, false) : LQ_NW(5, false, false);
-    return ch == 4 ? LQ_NW(4, false, true) : LQ_NW(5, false, true);
+#define LQ(CHN, NWN, G, V, I) lq::launch<CHN, NWN, G, V, I>(dc, rec, vals, ranges, alpha, last, v_render, v_alpha, v_rec, stream)
+#define LQ_NW(CHN, G, V, I) (nw == 8 ? LQ(CHN, 8, G, V, I) : LQ(CHN, 4, G, V, I))
+    if (!vec) return ch == 4 ? LQ_NW(4, false, false, false) : LQ_NW(5, false, false, false);
+    if (idg) {
+        if (geom) return ch == 4 ? LQ_NW(4, true, true, true) : LQ_NW(5, true, true, true);
+        return ch == 4 ? LQ_NW(4, false, true, true) : LQ_NW(5, false, true, true);
+    }
+    if (geom) return ch == 4 ? LQ_NW(4, true, true, false) : LQ_NW(5, true, true, false);
+    return ch == 4 ? LQ_NW(4, false, true, false) : LQ_NW(5, false, true, false);
 #undef LQ_NW
 #undef LQ
 }
