@@ -19,8 +19,13 @@ namespace isogs {
 namespace lq {
 
 constexpr unsigned FULL = 0xffffffffu;
-constexpr int WARPS = 2;   // per tile: warp w owns rows [8w, 8w+8) of the 16x16 tile
+constexpr int WARPS = 2;   // half tiles (16x8 pixels, one warp each) per tile
 constexpr int THREADS = 32 * WARPS;
+// warps per CTA: 2 = one tile per CTA, 1 = one half tile per CTA (finer-grained CTA scheduling); ISOGS_LQ_WARPS
+inline int cta_warps() {
+    static const int w = [] { const char* e = getenv("ISOGS_LQ_WARPS"); const int v = e ? atoi(e) : 2; return v == 1 ? 1 : 2; }();
+    return w;
+}
 constexpr int FAR = 0x01000000;
 
 template <int NW, bool WITH_ID = true>
@@ -57,30 +62,23 @@ __device__ __forceinline__ void prefetch(Pf& pf, int word, int first, int n_entr
     }
 }
 
-// Commit the prefetched word into ring slot word % NW; lane q receives (and stores) the hit mask of quad q.
-// Footprint test as in blend.cu::quad_hits (squared half extents + Gershgorin circle, padded, conservative).
+// Hit masks of the 32 Gaussians of one ring word (lane L holds Gaussian L's g0 / g1) against the warp's 32 quads,
+// written to st.hits[wsl + q].  Footprint test as in blend.cu::quad_hits (squared half extents + Gershgorin circle,
+// padded, conservative).
 template <int NW, bool WITH_ID>
-__device__ __forceinline__ void commit(Ring<NW, WITH_ID>& st, const Pf& pf, int word, float bx0, float by0, int lane) {
-    const unsigned wsl = ((unsigned)word & (NW - 1)) * 32u;
-    const unsigned slot = wsl + lane;
-    __syncwarp();
-    if (pf.have) {
-        st.g0[slot] = pf.g0;
-        st.g1[slot] = pf.g1;
-        st.g2[slot] = pf.g2;
-        if (WITH_ID) st.id[slot] = pf.id;
-    }
+__device__ __forceinline__ void publish_hits(Ring<NW, WITH_ID>& st, bool have, const float4& g0, const float4& g1,
+                                             unsigned wsl, float bx0, float by0, int lane) {
     float hx2 = -1.f, hy2 = -1.f, R2 = -1.f;
-    if (pf.have) {
-        const float a = 2.0f * pf.g0.z, b = pf.g0.w, c = 2.0f * pf.g1.x;
+    if (have) {
+        const float a = 2.0f * g0.z, b = g0.w, c = 2.0f * g1.x;
         const float inv_det = __fdividef(1.0f, fmaf(a, c, -(b * b)));
-        const float twoL = 2.0f * pf.g1.y * inv_det;
+        const float twoL = 2.0f * g1.y * inv_det;
         const float cxx = c * twoL, cyy = a * twoL, cxy = fabsf(b * twoL);
         hx2 = fmaf(cxx, 1.01f, 0.05f);
         hy2 = fmaf(cyy, 1.01f, 0.05f);
         R2 = fmaf(fmaxf(cxx, cyy) + cxy, 1.01f, 0.05f);
     }
-    const float X = pf.g0.x - bx0, Y = pf.g0.y - by0; // relative to the region's first pixel centre
+    const float X = g0.x - bx0, Y = g0.y - by0; // relative to the region's first pixel centre
     // per quad row r the three tests (x extent, y extent, circle) collapse into one threshold on ex2:
     // ex2 <= min(hx2, R2 - ey2[r]) if ey2[r] <= hy2, never otherwise
     float ex2[8], thr[4];
@@ -100,7 +98,69 @@ __device__ __forceinline__ void commit(Ring<NW, WITH_ID>& st, const Pf& pf, int 
         const uint32_t m = __ballot_sync(FULL, ex2[q & 7] <= thr[q >> 3]);
         if (lane == 0) st.hits[wsl + q] = m;
     }
+}
+
+// Commit the prefetched word into ring slot word % NW and publish its hit masks.
+template <int NW, bool WITH_ID>
+__device__ __forceinline__ void commit(Ring<NW, WITH_ID>& st, const Pf& pf, int word, float bx0, float by0, int lane) {
+    const unsigned wsl = ((unsigned)word & (NW - 1)) * 32u;
+    const unsigned slot = wsl + lane;
     __syncwarp();
+    if (pf.have) {
+        st.g0[slot] = pf.g0;
+        st.g1[slot] = pf.g1;
+        st.g2[slot] = pf.g2;
+        if (WITH_ID) st.id[slot] = pf.id;
+    }
+    publish_hits<NW, WITH_ID>(st, pf.have, pf.g0, pf.g1, wsl, bx0, by0, lane);
+    __syncwarp();
+}
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+
+// Initial fill of the ring (words 0 .. min(NW, n_words) - 1) with every load in flight at once: the NW ids of a lane
+// first, then 3 x 16 B asynchronous copies per entry straight into the ring -- two global round trips instead of the
+// 2 * NW a word-by-word fill serialises at the start of every warp.  Returns the number of words staged.
+template <int NW, bool WITH_ID, int DIR>
+__device__ __forceinline__ int initial_fill(Ring<NW, WITH_ID>& st, int first, int n_entries, int n_words,
+                                            const float4* __restrict__ rec, const int32_t* __restrict__ vals, float bx0,
+                                            float by0, int lane) {
+    const int nfill = min(NW, n_words);
+    int ids[NW];
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+        const int e = 32 * w + lane;
+        ids[w] = (e < n_entries) ? __ldg(vals + first + DIR * e) : -1;
+    }
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+        if (ids[w] >= 0) {
+            const float4* r = rec + 3 * (int64_t)ids[w];
+            const unsigned slot = 32u * w + lane;
+            cp_async16(&st.g0[slot], r);
+            cp_async16(&st.g1[slot], r + 1);
+            cp_async16(&st.g2[slot], r + 2);
+            if (WITH_ID) st.id[slot] = ids[w];
+        }
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncwarp();
+#pragma unroll 1
+    for (int w = 0; w < nfill; ++w) {
+        const unsigned slot = 32u * w + lane;
+        const bool have = 32 * w + lane < n_entries;
+        float4 g0 = make_float4(0.f, 0.f, 0.f, 0.f), g1 = g0;
+        if (have) {
+            g0 = st.g0[slot];
+            g1 = st.g1[slot];
+        }
+        publish_hits<NW, WITH_ID>(st, have, g0, g1, 32u * w, bx0, by0, lane);
+    }
+    __syncwarp();
+    return nfill;
 }
 
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
@@ -120,10 +180,12 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     using R = Ring<NW, !IDG>;
     R& st = reinterpret_cast<R*>(s_raw)[wid];
-    const int tile = blockIdx.y * cam.tw + blockIdx.x;
+    // half tile h = 2 * tile_y + half; a CTA holds blockDim.x / 32 consecutive halves of one tile column
+    const int hidx = blockIdx.y * (blockDim.x >> 5) + wid, ty = hidx >> 1, half = hidx & 1;
+    const int tile = ty * cam.tw + blockIdx.x;
     const int qx = lane & 7, qy = lane >> 3;
-    const int x0 = blockIdx.x * TILE + 2 * qx, y0 = blockIdx.y * TILE + 8 * wid + 2 * qy;
-    const float bx0 = (float)(blockIdx.x * TILE) + 0.5f, by0 = (float)(blockIdx.y * TILE + 8 * wid) + 0.5f;
+    const int x0 = blockIdx.x * TILE + 2 * qx, y0 = ty * TILE + 8 * half + 2 * qy;
+    const float bx0 = (float)(blockIdx.x * TILE) + 0.5f, by0 = (float)(ty * TILE + 8 * half) + 0.5f;
     const float pxa = (float)x0 + 0.5f, pxb = (float)x0 + 1.5f, pya = (float)y0 + 0.5f, pyb = (float)y0 + 1.5f;
     const int start = ranges[tile];
     const int64_t P = (int64_t)cam.width * cam.height;
@@ -159,12 +221,9 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
     for (int p = 0; p < 4; ++p) first[p] = warp_last - first[p];
 
     int staged = 0, base = 0; // warp-uniform: words [base, staged) are live in the ring
+    staged = initial_fill<NW, !IDG, -1>(st, warp_last, n_entries, n_words, rec, vals, bx0, by0, lane);
     Pf pf;
-    prefetch(pf, 0, warp_last, n_entries, rec, vals, lane);
-    for (; staged < min(NW, n_words); ++staged) {
-        commit<NW, !IDG>(st, pf, staged, bx0, by0, lane);
-        prefetch(pf, staged + 1, warp_last, n_entries, rec, vals, lane);
-    }
+    prefetch(pf, staged, warp_last, n_entries, rec, vals, lane);
     static_assert((NW & (NW - 1)) == 0, "NW must be a power of two");
     const uint32_t* hq = st.hits + lane; // this quad's hit word of ring slot base wsl is hq[wsl]
     auto fetch = [&](int w, unsigned wsl_) -> uint32_t {
@@ -301,10 +360,12 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
     using R = Ring<NW, false>;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     R& st = reinterpret_cast<R*>(s_raw)[wid];
-    const int tile = blockIdx.y * cam.tw + blockIdx.x;
+    // half tile h = 2 * tile_y + half; a CTA holds blockDim.x / 32 consecutive halves of one tile column
+    const int hidx = blockIdx.y * (blockDim.x >> 5) + wid, ty = hidx >> 1, half = hidx & 1;
+    const int tile = ty * cam.tw + blockIdx.x;
     const int qx = lane & 7, qy = lane >> 3;
-    const int x0 = blockIdx.x * TILE + 2 * qx, y0 = blockIdx.y * TILE + 8 * wid + 2 * qy;
-    const float bx0 = (float)(blockIdx.x * TILE) + 0.5f, by0 = (float)(blockIdx.y * TILE + 8 * wid) + 0.5f;
+    const int x0 = blockIdx.x * TILE + 2 * qx, y0 = ty * TILE + 8 * half + 2 * qy;
+    const float bx0 = (float)(blockIdx.x * TILE) + 0.5f, by0 = (float)(ty * TILE + 8 * half) + 0.5f;
     const float pxa = (float)x0 + 0.5f, pxb = (float)x0 + 1.5f, pya = (float)y0 + 0.5f, pyb = (float)y0 + 1.5f;
     const int start = ranges[tile], end = ranges[tile + 1];
     const int n_entries = end - start;
@@ -325,12 +386,9 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
 
     if (n_words > 0 && !__all_sync(FULL, quad_done)) {
         int staged = 0, base = 0;
+        staged = initial_fill<NW, false, 1>(st, start, n_entries, n_words, rec, vals, bx0, by0, lane);
         Pf pf;
-        prefetch<1>(pf, 0, start, n_entries, rec, vals, lane);
-        for (; staged < min(NW, n_words); ++staged) {
-            commit<NW, false>(st, pf, staged, bx0, by0, lane);
-            prefetch<1>(pf, staged + 1, start, n_entries, rec, vals, lane);
-        }
+        prefetch<1>(pf, staged, start, n_entries, rec, vals, lane);
         const uint32_t* hq = st.hits + lane;
         int jq = 0;
         unsigned wsl = 0;
@@ -422,8 +480,9 @@ int launch_fwd(const DevCam& dc, const float* rec, const int32_t* vals, const in
         ISOGS_CUDA(cudaFuncSetAttribute(blend_fwd_lq_kernel<CH, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_dev = dev;
     }
-    dim3 grid(dc.tw, dc.th);
-    blend_fwd_lq_kernel<CH, NW><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, render, alpha, last);
+    const int cw = cta_warps();
+    dim3 grid(dc.tw, dc.th * (WARPS / cw));
+    blend_fwd_lq_kernel<CH, NW><<<grid, 32 * cw, smem / WARPS * cw, stream>>>(dc, (const float4*)rec, vals, ranges, render, alpha, last);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
 }
@@ -440,8 +499,9 @@ int launch(const DevCam& dc, const float* rec, const int32_t* vals, const int32_
                                         (int)smem));
         attr_dev = dev;
     }
-    dim3 grid(dc.tw, dc.th);
-    blend_bwd_lq_kernel<CH, NW, GEOM, VEC, IDG><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last,
+    const int cw = cta_warps();
+    dim3 grid(dc.tw, dc.th * (WARPS / cw));
+    blend_bwd_lq_kernel<CH, NW, GEOM, VEC, IDG><<<grid, 32 * cw, smem / WARPS * cw, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last,
                                                                             v_render, v_alpha, v_rec);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
