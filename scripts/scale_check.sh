@@ -9,5 +9,6 @@ run() { # $1 = ranks, $2 = out suffix, rest = extra bench flags
 }
 run $N ${N}gpu
 run $N ${N}gpu_nccl --allreduce nccl
-timeout 200 python -m pytest tests/test_gpu_peer.py -q -m gpu 2>&1 | tail -3 > gpurun_out/${TAG}_pytest_peer.log; cat gpurun_out/${TAG}_pytest_peer.log
+if [ -n "$SCALE_PEER_TEST" ]; then timeout 200 python -m pytest tests/test_gpu_peer.py -q -m gpu 2>&1 | tail -3 > gpurun_out/${TAG}_pytest_peer.log; cat gpurun_out/${TAG}_pytest_peer.log; fi
 if [ $N -gt 4 ]; then run 4 4gpu; fi
+if [ $N -gt 2 ]; then run 2 2gpu; fi
