@@ -9,7 +9,8 @@ Workload at N=1: BASELINE.json configs[2] shape -- Replica-shaped 1200x680, 1 M 
   python bench.py [--gpus N --steps K --warmup W] [--impl reference]
 
 N > 1 (torchrun): every rank renders a DIFFERENT keyframe of the 8-keyframe window against the
-replicated map; one NCCL all-reduce of the flat gradient buffer per iteration; weak scaling,
+replicated map; one average of the flat gradient buffer per iteration (own NVLink peer-memory kernel,
+--allreduce nccl for ncclAllReduce); weak scaling,
 value = keyframe-renders (iterations x ranks) per second.
 """
 import argparse

@@ -574,6 +574,7 @@ extern "C" int isogs_blend_fwd(const isogs_camera* cam, int ch, const float* rec
                                void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (!cam || (ch != 4 && ch != 5)) { set_error("isogs_blend_fwd: ch must be 4 or 5"); return ISOGS_E_ARG; }
+    if ((uintptr_t)rec & 15) { set_error("isogs_blend_fwd: rec must be 16-byte aligned"); return ISOGS_E_ARG; }
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
     // default: the lane-per-quad kernel of blend_lq.cu with a ring of 8 words; ISOGS_FWD_LQ=0 selects the
@@ -594,6 +595,7 @@ extern "C" int isogs_blend_bwd(const isogs_camera* cam, int ch, int64_t N, const
     cudaStream_t stream = (cudaStream_t)stream_;
     (void)N;
     if (!cam || (ch != 4 && ch != 5)) { set_error("isogs_blend_bwd: ch must be 4 or 5"); return ISOGS_E_ARG; }
+    if (((uintptr_t)rec | (uintptr_t)v_rec) & 15) { set_error("isogs_blend_bwd: rec and v_rec must be 16-byte aligned"); return ISOGS_E_ARG; }
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
     static const int lq = env_int("ISOGS_BWD_LQ", 1); // 1 (default): lane-per-quad kernel (blend_lq.cu), 2: same with scalar REDs, 0: quad-of-lanes kernel
@@ -615,6 +617,7 @@ extern "C" int isogs_blend_bwd_geom(const isogs_camera* cam, int ch, int64_t N, 
     cudaStream_t stream = (cudaStream_t)stream_;
     (void)N;
     if (!cam || (ch != 4 && ch != 5)) { set_error("isogs_blend_bwd_geom: ch must be 4 or 5"); return ISOGS_E_ARG; }
+    if (((uintptr_t)rec | (uintptr_t)v_rec) & 15) { set_error("isogs_blend_bwd_geom: rec and v_rec must be 16-byte aligned"); return ISOGS_E_ARG; }
     DevCam dc = make_devcam(*cam);
     static const int lq = env_int("ISOGS_BWD_LQ", 1);
     if (lq) return launch_blend_bwd_lq(dc, ch, env_nw("ISOGS_NW_BWD", NW_LQ), true, true, lq == 3, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);

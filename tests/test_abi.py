@@ -34,6 +34,19 @@ def test_version_and_error_string(pkg):
     assert b"isogs_blend_fwd" in L.isogs_last_error()
 
 
+def test_blend_rejects_misaligned_records(pkg):
+    # rec / v_rec are read and accumulated as 16-byte rows (float4 loads, red.global.add.v4.f32): a misaligned
+    # pointer is an argument error, reported before any CUDA call
+    L = pkg.lib()
+    cam = pkg._lib.Camera()
+    cam.width, cam.height = 64, 48
+    rc = L.isogs_blend_fwd(ctypes.byref(cam), 5, 0x1004, None, None, None, None, None, None)
+    assert rc == pkg._lib.E_ARG and b"16-byte" in L.isogs_last_error()
+    for fn in (L.isogs_blend_bwd, L.isogs_blend_bwd_geom):
+        rc = fn(ctypes.byref(cam), 5, 0, 0x1000, None, None, None, None, None, None, 0x2008, None)
+        assert rc == pkg._lib.E_ARG and b"16-byte" in L.isogs_last_error()
+
+
 def test_struct_layout_matches_header(pkg):
     # isogs_camera: 2 i32 + 4 f + 9 f + 3 f + 3 f + 3 f = 96 bytes; isogs_pose 28 bytes
     assert ctypes.sizeof(pkg._lib.Camera) == 96
