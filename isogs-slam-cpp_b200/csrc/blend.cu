@@ -3,6 +3,9 @@
 // no-return atomics (RED).  Reference: gsplat RasterizeToPixels3DGSFwd.cu:17-188,
 // RasterizeToPixels3DGSBwd.cu:15-278.
 //
+// These are the four-lanes-per-quad kernels (ISOGS_FWD_LQ=0 / ISOGS_BWD_LQ=0); the default kernels live in
+// blend_lq.cu and share this file's C entry points.
+//
 // Design: warp-autonomous, no CTA barrier.  A CTA is one tile, a warp owns an 8x4
 // pixel block of it and walks the tile's depth-sorted list on its own through a warp-private RING
 // of NW words x 32 Gaussians in shared memory: staging a word, lane L loads Gaussian L and tests

@@ -1,16 +1,18 @@
-// blend_lq.cu -- north_star (4) backward alpha-blend, "lane-per-quad" variant.
-// Reference: gsplat RasterizeToPixels3DGSBwd.cu:15-278.
+// blend_lq.cu -- north_star (3) forward and (4) backward alpha-blend, "lane-per-quad" kernels;
+// the default since round 1m (blend.cu keeps the four-lanes-per-quad kernels as the A/B baseline).
+// Reference: gsplat RasterizeToPixels3DGSFwd.cu:17-188, RasterizeToPixels3DGSBwd.cu:15-278.
 //
 // Same warp-autonomous ring walk as blend.cu, but a LANE owns a whole 2x2 pixel quad (its four pixels
 // live in registers and are processed one after the other) and a warp owns a 16x8 half tile = 32 quads.
 // In one warp iteration every lane blends a different Gaussian (its quad's next hit) into its four
-// pixels, so the per-quad partial gradients are summed INSIDE the lane: no shuffle reduction, no
-// select network, and one quad's 11 gradient components leave as three 16-byte vector REDs into the
-// 48-byte gradient record instead of 12 scalar REDs from four lanes.  The cursor / ring bookkeeping
-// (about 35 instructions per warp iteration) is shared by 32 (quad, Gaussian) pairs instead of 8.
+// pixels.  Backward: the per-quad partial gradients are summed INSIDE the lane -- no shuffle reduction, no
+// select network -- and one quad's 11 gradient components leave as three 16-byte vector REDs
+// (red.global.add.v4.f32) into the 48-byte gradient record instead of 12 scalar REDs from four lanes.  The
+// cursor / ring bookkeeping (about 45 instructions per warp iteration) is shared by up to 32 (quad, Gaussian)
+// pairs instead of 8.
 //
 // The sigma expression is the one of blend.cu / the oracle (explicit round-to-nearest intrinsics), so the
-// contribute / skip decision of every pixel is the forward's.
+// contribute / skip decision of every pixel, `last` and the images are the same as before.
 #include <cstdlib>
 
 #include "common.cuh"
