@@ -3,9 +3,9 @@
 // libisogs_rast.so instead of gsplat's ATen ops.  Only cudart + the C ABI.
 //
 // It back-projects a synthetic RGB-D frame into isotropic Gaussians (Mapper::addNewGaussians through
-// isogs_backproject_append on an empty map), perturbs their colours / positions, and runs mapping iterations
-//     preprocess -> tile_bin_async -> blend_fwd -> loss_l1 (+ SSIM) -> blend_bwd -> preprocess_bwd -> adam
-// printing the loss, which must fall.  Exit code 0 on success.
+// isogs_backproject_append on an empty map), perturbs their colours, captures ONE mapping iteration
+//     isogs_map_step = preprocess -> tile_bin_async -> blend_fwd -> loss_l1 + SSIM -> blend_bwd -> preprocess_bwd -> adam
+// in a CUDA graph (isogs_graph_begin / _end) and replays it, printing the loss, which must fall.  Exit code 0 on success.
 //
 // Build:  g++ -O2 -std=c++17 -I include -I /usr/local/cuda/include examples/cabi_mapping.cpp \
 //             -L isogs-slam-cpp_b200 -lisogs_rast -L /usr/local/cuda/lib64 -lcudart -Wl,-rpath,'$ORIGIN/../isogs-slam-cpp_b200' \
@@ -103,26 +103,42 @@ int main(int argc, char** argv) {
             *totals = dalloc<int32_t>(2), *last = dalloc<int32_t>(P);
     uint64_t* bucket = dalloc<uint64_t>(isect_cap);
     float *render = dalloc<float>(5 * P), *v_render = dalloc<float>(5 * P), *alpha = dalloc<float>(P),
-          *losses = dalloc<float>(8), *dmaps = dalloc<float>(9 * P);
-    const int flags = ISOGS_F_LOG_SCALES | ISOGS_F_LOGIT_OPAC;
+          *dmaps = dalloc<float>(9 * P);
+    float* small = dalloc<float>(32);
+    isogs_adam_state* adam_state = reinterpret_cast<isogs_adam_state*>(dalloc<unsigned char>(sizeof(isogs_adam_state)));
+    // the device-side frame slot: ground truth, keyframe pose, 1 / #valid depth (all pixels are valid here)
+    isogs_frame fr_h{};
+    fr_h.gt_rgb = d_rgb; fr_h.gt_depth = d_depth;
+    for (int k = 0; k < 4; ++k) fr_h.pose[k] = pose.q[k];
+    for (int k = 0; k < 3; ++k) fr_h.pose[4 + k] = pose.t[k];
+    fr_h.inv_n_depth = 1.0f / (float)P;
+    isogs_frame* fr_d = reinterpret_cast<isogs_frame*>(dalloc<unsigned char>(sizeof(isogs_frame)));
+    CU(cudaMemcpy(fr_d, &fr_h, sizeof(fr_h), cudaMemcpyHostToDevice));
+    isogs_workspace ws{};
+    ws.rec = rec; ws.v_rec = v_rec; ws.radii = radii; ws.bucket = bucket; ws.vals = vals; ws.ranges = ranges;
+    ws.totals = totals; ws.sort_temp = sort_tmp; ws.sort_temp_bytes = sort_b; ws.isect_cap = isect_cap;
+    ws.render = render; ws.v_render = v_render; ws.alpha = alpha; ws.last = last; ws.small = small;
+    ws.adam_state = adam_state; ws.dmaps = dmaps;
+    isogs_gaussians gs{};
+    gs.N = N; gs.scale_dim = 1;
+    gs.p[0] = means; gs.p[1] = cols; gs.p[2] = quats; gs.p[3] = logit; gs.p[4] = ls;
+    const int slot[4] = {0, 1, 3, 4};                       // par / grad / moments above: means, colours, opacity, scale
+    for (int g = 0; g < 4; ++g) { gs.g[slot[g]] = grad[g]; gs.m[slot[g]] = mom1[g]; gs.v[slot[g]] = mom2[g]; }
+    isogs_step_params prm{};
+    prm.flags = ISOGS_STEP_SSIM; prm.phases = ISOGS_PHASE_RENDER | ISOGS_PHASE_ADAM;
+    prm.w_im = 0.5f; prm.w_depth = 1.0f; prm.sil_thres = 0.99f;
+    for (int g = 0; g < 4; ++g) prm.lr[slot[g]] = lr[g];
+    prm.beta1 = 0.9f; prm.beta2 = 0.999f; prm.eps = 1e-15f;
+    // capture ONE mapping iteration (Mapper::optimize's loop body) and replay it: a single launch per iteration
+    void* graph = nullptr;
+    CK(isogs_graph_begin(st));
+    CK(isogs_map_step(&cam, fr_d, &ws, &gs, &prm, nullptr, st));
+    CK(isogs_graph_end(st, &graph));
+    float* losses = small;
     float first = 0.f, lastv = 0.f;
     for (int it = 0; it < iters; ++it) {
-        CU(cudaMemsetAsync(losses, 0, 8 * sizeof(float), st));
-        CK(isogs_preprocess_fwd(&cam, &pose, nullptr, N, means, ls, 1, nullptr, logit, cols, 5, flags, rec, radii, nullptr,
-                                nullptr, nullptr, 0, nullptr, st));
-        CK(isogs_tile_bin_async(&cam, N, isect_cap, rec, radii, bucket, nullptr, vals, ranges, totals, sort_tmp, sort_b, st));
-        CK(isogs_blend_fwd(&cam, 5, rec, vals, ranges, render, alpha, last, st));
-        CK(isogs_loss_l1_fused(&cam, 1, render, alpha, d_rgb, d_depth, 0.5f * 0.8f, 1.0f, 0.99f, 1, 1.0f / (float)P, nullptr,
-                               v_render, losses, st));
-        CK(isogs_ssim_loss_fused(&cam, render, d_rgb, 0.5f * 0.2f, dmaps, v_render, losses, losses + 4, st));
-        CU(cudaMemsetAsync(v_rec, 0, ISOGS_REC * N * sizeof(float), st));
-        CK(isogs_blend_bwd(&cam, 5, N, rec, vals, ranges, alpha, last, v_render, nullptr, v_rec, st));
-        CK(isogs_preprocess_bwd(&cam, &pose, nullptr, N, means, ls, 1, nullptr, logit, 5, flags, radii, v_rec, grad[0], grad[3],
-                                nullptr, grad[2], grad[1], nullptr, nullptr, nullptr, st));
-        isogs_adam_group groups[4];
-        for (int g = 0; g < 4; ++g) groups[g] = {par[g], grad[g], mom1[g], mom2[g], width[g] * N, lr[g]};
-        CK(isogs_adam_fused(groups, 4, 0.9f, 0.999f, 1e-15f, it + 1, st));
-        float h[8];
+        CK(isogs_graph_launch(graph, st));
+        float h[32];
         int32_t tot[2];
         CU(cudaMemcpyAsync(h, losses, sizeof(h), cudaMemcpyDeviceToHost, st));
         CU(cudaMemcpyAsync(tot, totals, sizeof(tot), cudaMemcpyDeviceToHost, st));
@@ -132,9 +148,10 @@ int main(int argc, char** argv) {
         lastv = h[0];
         if (it % 5 == 0 || it == iters - 1)
             std::printf("iter %3d  loss %.6f  (colour L1 %.5f, depth L1 %.5f, SSIM %.4f)  intersections %d\n", it, h[0], h[1],
-                        h[2], h[4], tot[0]);
+                        h[2], h[27], tot[0]);
     }
     if (!(lastv < 0.7f * first) || !std::isfinite(lastv)) { std::fprintf(stderr, "loss did not fall: %f -> %f\n", first, lastv); return 7; }
-    std::printf("ok: loss %.6f -> %.6f over %d iterations, no torch involved\n", first, lastv, iters);
+    CK(isogs_graph_destroy(graph));
+    std::printf("ok: loss %.6f -> %.6f over %d replays of one captured graph, no torch involved\n", first, lastv, iters);
     return 0;
 }

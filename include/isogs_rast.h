@@ -52,6 +52,28 @@ typedef struct isogs_pose {
     float t[3];
 } isogs_pose;
 
+/* DEVICE-resident step state of the fused Adam: advanced by isogs_step_begin, read by isogs_adam_fused, so a
+ * captured CUDA graph of the step stays replayable (torch.optim.Adam keeps `step` on the host and the
+ * reference re-creates the optimizer per frame, python_ordinary/scripts/splatam.py:402-408,1237,1406: zero this
+ * struct to do the same).  32 bytes, 8-byte aligned. */
+typedef struct isogs_adam_state {
+    int64_t step;
+    double inv_bc1;      /* 1 / (1 - beta1^step) */
+    double inv_bc2_sqrt; /* 1 / sqrt(1 - beta2^step) */
+    double reserved;
+} isogs_adam_state;
+
+/* DEVICE-resident "current frame" slot read by the fused steps: ground-truth planes, the frame's pose (the
+ * keyframe's fixed pose for mapping; ignored by tracking, whose pose is the optimised variable) and
+ * 1 / #(gt_depth > 0).  Lets ONE captured graph serve every keyframe of the window: the caller copies 48 bytes
+ * into the slot (stream-ordered) before each launch.  gt_rgb [3,H,W] and gt_depth [H,W] must be 16-byte aligned. */
+typedef struct isogs_frame {
+    const float* gt_rgb;
+    const float* gt_depth;
+    float pose[7]; /* q (w,x,y,z un-normalised), t */
+    float inv_n_depth;
+} isogs_frame;
+
 const char* isogs_last_error(void);
 int isogs_version(void);
 
@@ -72,14 +94,16 @@ int isogs_temp_bytes(int64_t N, int64_t cap, size_t* scan_bytes, size_t* sort_by
  * If n_isects_host (PINNED or pageable HOST int64*) is non-null the call copies cum[N-1]
  * there and synchronises the stream (the one sync of a forward, == Intersect.cpp:80).
  * tiles and cum may both be null (then n_isects_host must be null too): the sync-free pipeline
- * (isogs_tile_bin_async) counts intersections per tile itself and needs neither. */
+ * (isogs_tile_bin_async) counts intersections per tile itself and needs neither.
+ * v_rec_zero (nullable, [N,12], 16-byte aligned): rows are cleared by the same kernel -- the gradient record
+ * that isogs_blend_bwd accumulates into, so the step needs no separate memset launch. */
 int isogs_preprocess_fwd(const isogs_camera* cam, const isogs_pose* pose, const float* pose_dev,
                          int64_t N, const float* means, const float* scales, int scale_dim,
                          const float* quats, const float* opacities, const float* colors,
                          int ch, int flags,
                          float* rec, int32_t* radii, int32_t* tiles, int32_t* cum,
                          void* scan_temp, size_t scan_temp_bytes,
-                         int64_t* n_isects_host, void* stream);
+                         int64_t* n_isects_host, float* v_rec_zero, void* stream);
 
 /* duplicateWithKeys + radix sort + identifyTileRanges: replaces gsplat intersect_tile pass 2,
  * radix_sort_double_buffer and intersect_offset (Ops.h:186-204; IntersectTile.cu:87-113,
@@ -94,8 +118,10 @@ int isogs_tile_bin(const isogs_camera* cam, int64_t N, int64_t M,
  * `n_isects = cum[-1].item()` of gsplat Intersect.cpp:80.  The intersection count is NOT known on
  * the host; `capacity` is the size of bucket / keys_sorted / vals_sorted.  totals (DEVICE int32[2])
  * receives {n_isects, overflow}: when n_isects > capacity the tile lists are truncated to the
- * capacity (no out-of-bounds access), overflow = 1, and the caller must grow the buffers and redo
- * the step.  bucket [capacity] u64 is scratch; keys_sorted may be null.  Output order is
+ * capacity (no out-of-bounds access) and overflow is set to 1.  The overflow word is STICKY: the library never
+ * clears it (while it is set totals[0] keeps the largest count seen); hand `totals + 1` to isogs_adam_fused /
+ * isogs_pose_keep_best as skip_flag so the affected steps update nothing, and clear it on the host after
+ * growing the buffers.  bucket [capacity] u64 is scratch; keys_sorted may be null.  Output order is
  * bit-identical to isogs_tile_bin. */
 int isogs_tile_bin_async(const isogs_camera* cam, int64_t N, int64_t capacity,
                          const float* rec, const int32_t* radii,
@@ -186,8 +212,15 @@ typedef struct isogs_adam_group {
     float* param; const float* grad; float* exp_avg; float* exp_avg_sq;
     int64_t numel; float lr;
 } isogs_adam_group;
+/* `step` (>= 1) is torch's host-side step count; if `state` (DEVICE, nullable) is given the bias corrections are
+ * read from it instead (see isogs_step_begin) and `step` is ignored.  skip_flag (DEVICE int32*, nullable): the
+ * launch is a no-op when *skip_flag != 0 (the sticky overflow word of isogs_tile_bin_async). */
 int isogs_adam_fused(const isogs_adam_group* groups /*HOST*/, int n_groups, float beta1, float beta2,
-                     float eps, int step, void* stream);
+                     float eps, int step, const isogs_adam_state* state, const int32_t* skip_flag, void* stream);
+
+/* First launch of a fused step: small[0..n_small) = 0 (losses, pose gradient and accumulators), and, if state
+ * is non-null, state->step += 1 with the bias corrections of that step (double precision, like torch). */
+int isogs_step_begin(float* small, int n_small, isogs_adam_state* state, float beta1, float beta2, void* stream);
 
 /* ---- gradient-driven densification (off in every reference config, part of the operator surface) ---- */
 
@@ -267,7 +300,8 @@ int isogs_iso_flat_loss(int64_t N, const float* means, const float* log_scales, 
  * on the device so the loop needs no host sync: if losses[0] (evaluated BEFORE this iteration's
  * Adam step) < best[7], then best[0..6] = pose (the values AFTER the step) and best[7] = losses[0].
  * best: DEVICE float[8] = {q[4], t[3], min_loss}; initialise best[7] to 1e20 (splatam.py:1242). */
-int isogs_pose_keep_best(const float* losses, const float* pose, float* best, void* stream);
+int isogs_pose_keep_best(const float* losses, const float* pose, float* best, const int32_t* skip_flag /*nullable*/,
+                         void* stream);
 
 /* silhouette-driven prune compaction: replaces prune_gaussians + remove_points
  * (python_ordinary/utils/slam_external.py:139-188) and GaussianModel::prune
@@ -299,6 +333,88 @@ int isogs_backproject_append(const isogs_camera* cam, const isogs_pose* pose,
                              int64_t capacity,
                              int32_t* scan /*[2*H*W] scratch*/, void* scan_temp, size_t scan_temp_bytes,
                              int32_t* count, void* stream);
+
+/* ---- the fused steps: ONE host call enqueues a whole iteration ------------------------- */
+
+/* Parameters, gradients and Adam moments of the map in the reference's order (splatam.py:351-399):
+ * 0 means3D [N,3], 1 rgb_colors [N,3], 2 unnorm_rotations [N,4], 3 logit_opacities [N,1], 4 log_scales [N,sd].
+ * g / m / v entries may be null where no gradient is wanted (all of them for tracking; index 2 when sd == 1). */
+typedef struct isogs_gaussians {
+    int64_t N;
+    int32_t scale_dim, reserved;
+    float* p[5];
+    float* g[5];
+    float* m[5];
+    float* v[5];
+} isogs_gaussians;
+
+/* Caller-allocated DEVICE scratch of a step (nothing is allocated or freed by the library). */
+typedef struct isogs_workspace {
+    float* rec;            /* [n_cap,12] */
+    float* v_rec;          /* [n_cap,12] */
+    int32_t* radii;        /* [n_cap,2] */
+    uint64_t* bucket;      /* [isect_cap] */
+    int32_t* vals;         /* [isect_cap] */
+    int32_t* ranges;       /* [n_tiles+1] */
+    int32_t* totals;       /* [2] {n_isects, sticky overflow} */
+    void* sort_temp;
+    size_t sort_temp_bytes;
+    int64_t isect_cap;
+    float* render;         /* [5,H,W] */
+    float* v_render;       /* [5,H,W] */
+    float* alpha;          /* [H,W] */
+    int32_t* last;         /* [H,W] */
+    float* small;          /* [32]: losses[4] | v_pose[7] | pose_acc[16] | ssim | outlier thr | geo[3] */
+    isogs_adam_state* adam_state;
+    float* dmaps;          /* [9,H,W] SSIM derivative maps (nullable unless ISOGS_STEP_SSIM) */
+    float* median_scratch; /* [2,H,W]  (nullable unless ISOGS_STEP_OUTLIER) */
+    void* median_temp;
+    size_t median_temp_bytes;
+} isogs_workspace;
+
+#define ISOGS_STEP_SSIM 1     /* colour term 0.8*L1 + 0.2*(1-SSIM) (splatam.py:568) instead of pure L1 */
+#define ISOGS_STEP_OUTLIER 2  /* tracking: ignore_outlier_depth_loss (splatam.py:551-554) */
+#define ISOGS_STEP_NO_SIL 4   /* tracking: use_sil_for_loss = False */
+#define ISOGS_PHASE_RENDER 1  /* begin + forward + loss + backward (gradients land in gaussians->g) */
+#define ISOGS_PHASE_ADAM 2    /* fused Adam on every group with a gradient */
+#define ISOGS_STEP_EVENTS 9   /* begin, preprocess_fwd, tile_bin, blend_fwd, loss, ssim, blend_bwd, preprocess_bwd, adam */
+
+typedef struct isogs_step_params {
+    int32_t flags, phases;
+    float w_im, w_depth, sil_thres;
+    float lr[5];            /* mapping: per parameter group; tracking: lr[0] = rotation, lr[1] = translation */
+    float beta1, beta2, eps;
+} isogs_step_params;
+
+/* One mapping iteration on one keyframe == get_loss(mapping=True) + loss.backward() + optimizer.step()
+ * (python_ordinary/scripts/splatam.py:1412-1476; transform_to_frame + both renders + masked L1 (+ SSIM) +
+ * autograd + torch.optim.Adam; Mapper::optimize, cpp/src/slam/mapper.cpp:34-151).  frame: DEVICE slot (pose,
+ * ground truth, 1/n_valid_depth).  No host sync, no allocation: capturable in a CUDA graph.  Split the phases to
+ * put a gradient exchange (or the iso / flat terms) between backward and Adam.  events (nullable): HOST array of
+ * ISOGS_STEP_EVENTS cudaEvent_t recorded after the stages for per-stage timing. */
+int isogs_map_step(const isogs_camera* cam, const isogs_frame* frame /*DEVICE*/, const isogs_workspace* ws,
+                   const isogs_gaussians* gs, const isogs_step_params* prm, void* const* events, void* stream);
+
+/* One tracking iteration == get_loss(tracking=True) + backward + Adam on the pose + best-candidate rule
+ * (splatam.py:1247-1290; Tracker::optimizePose, cpp/src/slam/tracker.cpp:15-115).  pose / pose_m / pose_v:
+ * DEVICE float[7] (cam_unnorm_rots | cam_trans of the frame and their Adam moments), best: DEVICE float[8],
+ * pose_state: the pose optimizer's step state.  frame->pose is ignored. */
+int isogs_track_step(const isogs_camera* cam, const isogs_frame* frame /*DEVICE*/, const isogs_workspace* ws,
+                     const isogs_gaussians* gs, float* pose, float* pose_m, float* pose_v, float* best,
+                     isogs_adam_state* pose_state, const isogs_step_params* prm, void* const* events, void* stream);
+
+/* uint8 HWC colour + uint16 depth (the reference's source formats, python_ordinary/datasets/gradslam_datasets/
+ * basedataset.py:299-340: color / 255 -> [3,H,W], depth / png_depth_scale) unpacked into the fp32 planes the
+ * step reads: 5 bytes per pixel cross PCIe instead of 16. */
+int isogs_unpack_rgbd(const isogs_camera* cam, const uint8_t* rgb_hwc, const uint16_t* depth_u16,
+                      float inv_depth_scale, float* gt_rgb, float* gt_depth, void* stream);
+
+/* CUDA-graph capture of anything enqueued on `stream` between begin and end (thread-local capture mode);
+ * launch replays it.  graph_exec is an opaque handle. */
+int isogs_graph_begin(void* stream);
+int isogs_graph_end(void* stream, void** graph_exec);
+int isogs_graph_launch(void* graph_exec, void* stream);
+int isogs_graph_destroy(void* graph_exec);
 
 /* keyframe-sharded mapping, SURVEY 8(e): the average of the flat gradient buffer over the ranks as ONE kernel over
  * NVLink peer memory (two-shot: every rank reduces the 1/world slice it owns from all ranks in rank order and stores the

@@ -42,6 +42,43 @@ class Rows(C.Structure):
     _fields_ = [("inp", C.c_void_p), ("out", C.c_void_p), ("width", C.c_int32)]
 
 
+class AdamState(C.Structure):
+    """isogs_adam_state: DEVICE-resident; this mirror only gives its size / layout (32 bytes)."""
+    _fields_ = [("step", C.c_int64), ("inv_bc1", C.c_double), ("inv_bc2_sqrt", C.c_double), ("reserved", C.c_double)]
+
+
+class Frame(C.Structure):
+    """isogs_frame: the DEVICE-side current-frame slot (48 bytes); built on the host, copied to the device."""
+    _fields_ = [("gt_rgb", C.c_void_p), ("gt_depth", C.c_void_p), ("pose", C.c_float * 7), ("inv_n_depth", C.c_float)]
+
+
+class Gaussians(C.Structure):
+    _fields_ = [("N", C.c_int64), ("scale_dim", C.c_int32), ("reserved", C.c_int32),
+                ("p", C.c_void_p * 5), ("g", C.c_void_p * 5), ("m", C.c_void_p * 5), ("v", C.c_void_p * 5)]
+
+
+class Workspace(C.Structure):
+    _fields_ = [("rec", C.c_void_p), ("v_rec", C.c_void_p), ("radii", C.c_void_p), ("bucket", C.c_void_p),
+                ("vals", C.c_void_p), ("ranges", C.c_void_p), ("totals", C.c_void_p), ("sort_temp", C.c_void_p),
+                ("sort_temp_bytes", C.c_size_t), ("isect_cap", C.c_int64), ("render", C.c_void_p),
+                ("v_render", C.c_void_p), ("alpha", C.c_void_p), ("last", C.c_void_p), ("small", C.c_void_p),
+                ("adam_state", C.c_void_p), ("dmaps", C.c_void_p), ("median_scratch", C.c_void_p),
+                ("median_temp", C.c_void_p), ("median_temp_bytes", C.c_size_t)]
+
+
+class StepParams(C.Structure):
+    _fields_ = [("flags", C.c_int32), ("phases", C.c_int32), ("w_im", C.c_float), ("w_depth", C.c_float),
+                ("sil_thres", C.c_float), ("lr", C.c_float * 5), ("beta1", C.c_float), ("beta2", C.c_float),
+                ("eps", C.c_float)]
+
+
+STEP_SSIM, STEP_OUTLIER, STEP_NO_SIL = 1, 2, 4
+PHASE_RENDER, PHASE_ADAM = 1, 2
+STEP_EVENTS = 9
+STEP_EVENT_NAMES = ("begin", "preprocess_fwd", "tile_bin", "blend_fwd", "loss", "ssim", "blend_bwd", "preprocess_bwd",
+                    "adam")
+
+
 def build(force=False):
     """Compile the CUDA library for sm_100a (nvcc cross-compiles without a GPU)."""
     src_dir = os.path.join(_HERE, "csrc")
@@ -63,7 +100,7 @@ _SIGS = {
     "isogs_version": (C.c_int, []),
     "isogs_temp_bytes": (C.c_int, [_I64, _I64, C.POINTER(_SZ), C.POINTER(_SZ)]),
     "isogs_preprocess_fwd": (C.c_int, [C.POINTER(Camera), C.POINTER(Pose), _VP, _I64, _VP, _VP, _I32, _VP, _VP, _VP,
-                                       _I32, _I32, _VP, _VP, _VP, _VP, _VP, _SZ, C.POINTER(_I64), _VP]),
+                                       _I32, _I32, _VP, _VP, _VP, _VP, _VP, _SZ, C.POINTER(_I64), _VP, _VP]),
     "isogs_tile_bin": (C.c_int, [C.POINTER(Camera), _I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "isogs_tile_bin_async": (C.c_int, [C.POINTER(Camera), _I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "isogs_blend_fwd": (C.c_int, [C.POINTER(Camera), _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
@@ -75,8 +112,18 @@ _SIGS = {
                                     _VP]),
     "isogs_depth_outlier_threshold": (C.c_int, [C.POINTER(Camera), _VP, _VP, _F, _VP, _VP, _SZ, _VP, _VP]),
     "isogs_ssim_loss_fused": (C.c_int, [C.POINTER(Camera), _VP, _VP, _F, _VP, _VP, _VP, _VP, _VP]),
-    "isogs_adam_fused": (C.c_int, [C.POINTER(AdamGroup), _I32, _F, _F, _F, _I32, _VP]),
-    "isogs_pose_keep_best": (C.c_int, [_VP, _VP, _VP, _VP]),
+    "isogs_adam_fused": (C.c_int, [C.POINTER(AdamGroup), _I32, _F, _F, _F, _I32, _VP, _VP, _VP]),
+    "isogs_step_begin": (C.c_int, [_VP, _I32, _VP, _F, _F, _VP]),
+    "isogs_pose_keep_best": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
+    "isogs_map_step": (C.c_int, [C.POINTER(Camera), _VP, C.POINTER(Workspace), C.POINTER(Gaussians),
+                                 C.POINTER(StepParams), C.POINTER(_VP), _VP]),
+    "isogs_track_step": (C.c_int, [C.POINTER(Camera), _VP, C.POINTER(Workspace), C.POINTER(Gaussians), _VP, _VP, _VP,
+                                   _VP, _VP, C.POINTER(StepParams), C.POINTER(_VP), _VP]),
+    "isogs_unpack_rgbd": (C.c_int, [C.POINTER(Camera), _VP, _VP, _F, _VP, _VP, _VP]),
+    "isogs_graph_begin": (C.c_int, [_VP]),
+    "isogs_graph_end": (C.c_int, [_VP, C.POINTER(_VP)]),
+    "isogs_graph_launch": (C.c_int, [_VP, _VP]),
+    "isogs_graph_destroy": (C.c_int, [_VP]),
     "isogs_densify_stats": (C.c_int, [_I64, _VP, _VP, _I32, _F, _F, _VP, _VP, _VP, _VP]),
     "isogs_densify_select": (C.c_int, [_I64, _VP, _VP, _VP, _I32, _F, _F, _I32, _VP, _VP, _SZ, _VP, _VP]),
     "isogs_densify_emit": (C.c_int, [_I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _I32, _I32, _VP, C.c_uint64, _VP, _VP]),

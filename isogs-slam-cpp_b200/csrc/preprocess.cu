@@ -12,9 +12,14 @@ __global__ void __launch_bounds__(256)
 preprocess_fwd_kernel(DevCam cam, DevPose pose, int64_t N, const float* __restrict__ means,
                       const float* __restrict__ scales, const float* __restrict__ quats,
                       const float* __restrict__ opacities, const float* __restrict__ colors, int ch, int flags,
-                      float4* __restrict__ rec, int2* __restrict__ radii, int32_t* __restrict__ tiles) {
+                      float4* __restrict__ rec, int2* __restrict__ radii, int32_t* __restrict__ tiles,
+                      float4* __restrict__ v_rec_zero) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
+    if (v_rec_zero != nullptr) { // the gradient record the blend backward accumulates into (saves a memset launch)
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        v_rec_zero[3 * i] = z; v_rec_zero[3 * i + 1] = z; v_rec_zero[3 * i + 2] = z;
+    }
     FrameXf xf;
     load_frame(pose, xf);
     constexpr int SD = ISO ? 1 : 3;
@@ -311,7 +316,7 @@ extern "C" int isogs_preprocess_fwd(const isogs_camera* cam, const isogs_pose* p
                                     const float* quats, const float* opacities, const float* colors, int ch,
                                     int flags, float* rec, int32_t* radii, int32_t* tiles, int32_t* cum,
                                     void* scan_temp, size_t scan_temp_bytes, int64_t* n_isects_host,
-                                    void* stream_) {
+                                    float* v_rec_zero, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (!cam || N < 0 || (scale_dim != 1 && scale_dim != 3) || (ch != 4 && ch != 5) || (scale_dim == 3 && !quats)) {
         set_error("isogs_preprocess_fwd: bad argument (scale_dim=%d ch=%d)", scale_dim, ch);
@@ -322,8 +327,8 @@ extern "C" int isogs_preprocess_fwd(const isogs_camera* cam, const isogs_pose* p
         return ISOGS_OK;
     }
     if (N >= (1ll << 31)) { set_error("N too large"); return ISOGS_E_ARG; }
-    if ((((uintptr_t)rec | (uintptr_t)quats) & 15) || ((uintptr_t)radii & 7)) {
-        set_error("isogs_preprocess_fwd: rec / quats must be 16-byte aligned, radii 8-byte aligned");
+    if ((((uintptr_t)rec | (uintptr_t)quats | (uintptr_t)v_rec_zero) & 15) || ((uintptr_t)radii & 7)) {
+        set_error("isogs_preprocess_fwd: rec / quats / v_rec_zero must be 16-byte aligned, radii 8-byte aligned");
         return ISOGS_E_ARG;
     }
     DevCam dc = make_devcam(*cam);
@@ -332,10 +337,11 @@ extern "C" int isogs_preprocess_fwd(const isogs_camera* cam, const isogs_pose* p
     const unsigned grid = (unsigned)((N + block - 1) / block);
     if (scale_dim == 1)
         preprocess_fwd_kernel<true><<<grid, block, 0, stream>>>(dc, dp, N, means, scales, quats, opacities, colors,
-                                                                 ch, flags, (float4*)rec, (int2*)radii, tiles);
+                                                                 ch, flags, (float4*)rec, (int2*)radii, tiles, (float4*)v_rec_zero);
     else
         preprocess_fwd_kernel<false><<<grid, block, 0, stream>>>(dc, dp, N, means, scales, quats, opacities, colors,
-                                                                  ch, flags, (float4*)rec, (int2*)radii, tiles);
+                                                                  ch, flags, (float4*)rec, (int2*)radii, tiles,
+                                                                  (float4*)v_rec_zero);
     ISOGS_CUDA(cudaGetLastError());
     if (!tiles || !cum) { // sync-free pipeline (isogs_tile_bin_async counts per tile itself)
         if (n_isects_host) { set_error("n_isects_host needs tiles and cum"); return ISOGS_E_ARG; }

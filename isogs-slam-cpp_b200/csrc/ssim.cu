@@ -66,7 +66,8 @@ constexpr int P1_ITEMS = SIY * (STX / SEG); // 42 rows x 4 runs = 168 threads bu
 __global__ void __launch_bounds__(256)
 ssim_fwd_kernel(int W, int H, const float* __restrict__ img_x, const float* __restrict__ img_y,
                 float* __restrict__ dmaps, float add_const, float scale, float* __restrict__ losses,
-                float* __restrict__ ssim_out, const Window win) {
+                float* __restrict__ ssim_out, const Window win, const isogs_frame* __restrict__ fr) {
+    if (fr != nullptr) img_y = fr->gt_rgb;   // current keyframe through the device-side frame slot (graph replay)
     __shared__ float sx[SIY][SPAD], sy[SIY][SPAD];
     __shared__ float sh[5][SIY][HP];
     __shared__ float red[8];
@@ -147,7 +148,9 @@ ssim_fwd_kernel(int W, int H, const float* __restrict__ img_x, const float* __re
 
 __global__ void __launch_bounds__(256)
 ssim_bwd_kernel(int W, int H, const float* __restrict__ img_x, const float* __restrict__ img_y,
-                const float* __restrict__ dmaps, float coef, float* __restrict__ v_x, const Window win) {
+                const float* __restrict__ dmaps, float coef, float* __restrict__ v_x, const Window win,
+                const isogs_frame* __restrict__ fr) {
+    if (fr != nullptr) img_y = fr->gt_rgb;
     __shared__ float sd[3][SIY][SPAD];
     __shared__ float sh[3][SIY][HP];
     const int64_t P = (int64_t)W * H;
@@ -211,10 +214,20 @@ ssim_bwd_kernel(int W, int H, const float* __restrict__ img_x, const float* __re
 
 using namespace isogs;
 
+namespace isogs {
+int launch_ssim_loss(const isogs_camera* cam, const float* render, const float* gt_rgb, const isogs_frame* frame_dev,
+                     float weight, float* dmaps, float* v_render, float* losses, float* ssim_out, cudaStream_t stream);
+}
+
 extern "C" int isogs_ssim_loss_fused(const isogs_camera* cam, const float* render, const float* gt_rgb, float weight,
                                      float* dmaps, float* v_render, float* losses, float* ssim_out, void* stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
-    if (!cam || !render || !gt_rgb || !dmaps || !ssim_out || cam->width <= 0 || cam->height <= 0) {
+    return launch_ssim_loss(cam, render, gt_rgb, nullptr, weight, dmaps, v_render, losses, ssim_out, (cudaStream_t)stream_);
+}
+
+int isogs::launch_ssim_loss(const isogs_camera* cam, const float* render, const float* gt_rgb,
+                            const isogs_frame* frame_dev, float weight, float* dmaps, float* v_render, float* losses,
+                            float* ssim_out, cudaStream_t stream) {
+    if (!cam || !render || (!gt_rgb && !frame_dev) || !dmaps || !ssim_out || cam->width <= 0 || cam->height <= 0) {
         set_error("isogs_ssim_loss_fused: bad argument");
         return ISOGS_E_ARG;
     }
@@ -222,10 +235,10 @@ extern "C" int isogs_ssim_loss_fused(const isogs_camera* cam, const float* rende
     const int W = cam->width, H = cam->height;
     const dim3 grid((W + STX - 1) / STX, (H + STY - 1) / STY, 3);
     const float inv_n = 1.0f / (3.0f * (float)W * (float)H);
-    ssim_fwd_kernel<<<grid, 256, 0, stream>>>(W, H, render, gt_rgb, dmaps, weight, inv_n, losses, ssim_out, win);
+    ssim_fwd_kernel<<<grid, 256, 0, stream>>>(W, H, render, gt_rgb, dmaps, weight, inv_n, losses, ssim_out, win, frame_dev);
     ISOGS_CUDA(cudaGetLastError());
     if (v_render) {
-        ssim_bwd_kernel<<<grid, 256, 0, stream>>>(W, H, render, gt_rgb, dmaps, -weight * inv_n, v_render, win);
+        ssim_bwd_kernel<<<grid, 256, 0, stream>>>(W, H, render, gt_rgb, dmaps, -weight * inv_n, v_render, win, frame_dev);
         ISOGS_CUDA(cudaGetLastError());
     }
     return ISOGS_OK;

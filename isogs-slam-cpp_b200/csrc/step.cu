@@ -35,7 +35,16 @@ __global__ void __launch_bounds__(256)
 loss_l1_kernel(int64_t P, int mode, const float* __restrict__ render, const float* __restrict__ alpha,
                const float* __restrict__ gt_rgb, const float* __restrict__ gt_depth, float w_im, float w_depth,
                float sil_thres, int use_sil, float inv_nd, float inv_nc, const float* __restrict__ outlier_thresh,
-               float* __restrict__ v_render, float* __restrict__ losses) {
+               float* __restrict__ v_render, float* __restrict__ losses, const isogs_frame* __restrict__ fr) {
+    if (fr != nullptr) {   // current frame through the device-side frame slot (CUDA-graph replay)
+        gt_rgb = fr->gt_rgb;
+        gt_depth = fr->gt_depth;
+        if (mode == 1) inv_nd = fr->inv_n_depth;
+        if (V == 4 && ((((uintptr_t)gt_rgb | (uintptr_t)gt_depth) & 15) != 0)) { // documented requirement
+            if (blockIdx.x == 0 && threadIdx.x == 0) losses[0] = __int_as_float(0x7fc00000);
+            return;
+        }
+    }
     float sum_d = 0.f, sum_c = 0.f, cnt = 0.f;
     const bool outl = outlier_thresh != nullptr;
     const float othr = outl ? *outlier_thresh : 0.f;
@@ -105,22 +114,26 @@ struct AdamArgs {
     float* p[MAX_GROUPS]; const float* g[MAX_GROUPS]; float* m[MAX_GROUPS]; float* v[MAX_GROUPS];
     int64_t numel[MAX_GROUPS];
     int64_t block_start[MAX_GROUPS + 1]; // in units of blocks
-    float step_size[MAX_GROUPS];
+    float step_size[MAX_GROUPS];     // host-step mode: lr / (1 - b1^t); device-step mode: lr
     int n;
     float b1, b2, one_minus_b1, one_minus_b2, inv_bc2_sqrt, eps;
+    const isogs_adam_state* state;   // nullable: bias corrections written by step_begin_kernel (graph-replayable)
+    const int32_t* skip;             // nullable: *skip != 0 turns the launch into a no-op (overflowed forward)
 };
 
 constexpr int ADAM_BLOCK = 256, ADAM_VEC = 4;
 
-__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamArgs& a, float step_size) {
+__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamArgs& a, float step_size,
+                                         float inv_bc2_sqrt) {
     const float mi = m + (g - m) * a.one_minus_b1;
     const float vi = v * a.b2 + a.one_minus_b2 * g * g;
     m = mi; v = vi;
-    const float denom = sqrtf(vi) * a.inv_bc2_sqrt + a.eps;
+    const float denom = sqrtf(vi) * inv_bc2_sqrt + a.eps;
     p = p - step_size * (mi / denom);
 }
 
 __global__ void __launch_bounds__(ADAM_BLOCK) adam_kernel(AdamArgs a) {
+    if (a.skip != nullptr && *a.skip != 0) return;
     int grp = 0;
 #pragma unroll
     for (int k = 1; k < MAX_GROUPS; ++k)
@@ -130,7 +143,11 @@ __global__ void __launch_bounds__(ADAM_BLOCK) adam_kernel(AdamArgs a) {
     const int64_t n = a.numel[grp];
     if (base >= n) return;
     float* p = a.p[grp]; const float* g = a.g[grp]; float* m = a.m[grp]; float* v = a.v[grp];
-    const float ss = a.step_size[grp];
+    float ss = a.step_size[grp], ib2 = a.inv_bc2_sqrt;
+    if (a.state != nullptr) {   // the same double -> float roundings as the host-step path
+        ss = (float)((double)ss * a.state->inv_bc1);
+        ib2 = (float)a.state->inv_bc2_sqrt;
+    }
     const bool vec_ok = (base + ADAM_VEC <= n) &&
                         ((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0);
     if (vec_ok) {
@@ -138,15 +155,15 @@ __global__ void __launch_bounds__(ADAM_BLOCK) adam_kernel(AdamArgs a) {
         const float4 G4 = *reinterpret_cast<const float4*>(g + base);
         float4 M4 = *reinterpret_cast<float4*>(m + base);
         float4 V4 = *reinterpret_cast<float4*>(v + base);
-        adam_one(P4.x, G4.x, M4.x, V4.x, a, ss);
-        adam_one(P4.y, G4.y, M4.y, V4.y, a, ss);
-        adam_one(P4.z, G4.z, M4.z, V4.z, a, ss);
-        adam_one(P4.w, G4.w, M4.w, V4.w, a, ss);
+        adam_one(P4.x, G4.x, M4.x, V4.x, a, ss, ib2);
+        adam_one(P4.y, G4.y, M4.y, V4.y, a, ss, ib2);
+        adam_one(P4.z, G4.z, M4.z, V4.z, a, ss, ib2);
+        adam_one(P4.w, G4.w, M4.w, V4.w, a, ss, ib2);
         *reinterpret_cast<float4*>(p + base) = P4;
         *reinterpret_cast<float4*>(m + base) = M4;
         *reinterpret_cast<float4*>(v + base) = V4;
     } else {
-        for (int64_t i = base; i < n && i < base + ADAM_VEC; ++i) adam_one(p[i], g[i], m[i], v[i], a, ss);
+        for (int64_t i = base; i < n && i < base + ADAM_VEC; ++i) adam_one(p[i], g[i], m[i], v[i], a, ss, ib2);
     }
 }
 
@@ -267,8 +284,9 @@ __global__ void densify_count_kernel(int64_t P, const int32_t* __restrict__ scan
 // keep the best tracking candidate (splatam.py:1287-1290): the pose AFTER this iteration's Adam step
 // is saved when the loss evaluated BEFORE the step is the smallest seen so far
 __global__ void pose_keep_best_kernel(const float* __restrict__ losses, const float* __restrict__ pose,
-                                      float* __restrict__ best) {
+                                      float* __restrict__ best, const int32_t* __restrict__ skip) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (skip != nullptr && *skip != 0) return;
     const float loss = losses[0];
     if (loss < best[7]) {
         best[7] = loss;
@@ -276,23 +294,62 @@ __global__ void pose_keep_best_kernel(const float* __restrict__ losses, const fl
     }
 }
 
-} // namespace isogs
+// Start of a fused step: clears the per-step scalars (losses, pose gradient, pose accumulators ...) and advances the
+// DEVICE-side Adam step counter with its bias corrections, so that the whole step can be replayed from a CUDA graph
+// (the host-side `step` argument of isogs_adam_fused would be frozen into the captured launch).
+__global__ void step_begin_kernel(float* __restrict__ small, int n_small, isogs_adam_state* __restrict__ st, double b1,
+                                  double b2) {
+    for (int i = threadIdx.x; i < n_small; i += blockDim.x) small[i] = 0.f;
+    if (threadIdx.x == 0 && st != nullptr) {
+        const int64_t t = st->step + 1;
+        st->step = t;
+        st->inv_bc1 = 1.0 / (1.0 - pow(b1, (double)t));
+        st->inv_bc2_sqrt = 1.0 / sqrt(1.0 - pow(b2, (double)t));
+    }
+}
 
+} // namespace isogs
 using namespace isogs;
 
-extern "C" int isogs_pose_keep_best(const float* losses, const float* pose, float* best, void* stream_) {
-    if (!losses || !pose || !best) { set_error("isogs_pose_keep_best: null argument"); return ISOGS_E_ARG; }
-    pose_keep_best_kernel<<<1, 32, 0, (cudaStream_t)stream_>>>(losses, pose, best);
+extern "C" int isogs_step_begin(float* small, int n_small, isogs_adam_state* state, float beta1, float beta2,
+                                void* stream_) {
+    if (n_small < 0 || (n_small > 0 && !small)) { set_error("isogs_step_begin: bad argument"); return ISOGS_E_ARG; }
+    step_begin_kernel<<<1, 64, 0, (cudaStream_t)stream_>>>(small, n_small, state, (double)beta1, (double)beta2);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
+}
+
+extern "C" int isogs_pose_keep_best(const float* losses, const float* pose, float* best, const int32_t* skip_flag,
+                                    void* stream_) {
+    if (!losses || !pose || !best) { set_error("isogs_pose_keep_best: null argument"); return ISOGS_E_ARG; }
+    pose_keep_best_kernel<<<1, 32, 0, (cudaStream_t)stream_>>>(losses, pose, best, skip_flag);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
+
+namespace isogs {
+int launch_loss_l1(const isogs_camera* cam, int mode, const float* render, const float* alpha, const float* gt_rgb,
+                   const float* gt_depth, const isogs_frame* frame_dev, float w_im, float w_depth, float sil_thres,
+                   int use_sil, float inv_n_depth, const float* outlier_thresh, float* v_render, float* losses,
+                   cudaStream_t stream);
 }
 
 extern "C" int isogs_loss_l1_fused(const isogs_camera* cam, int mode, const float* render, const float* alpha,
                                    const float* gt_rgb, const float* gt_depth, float w_im, float w_depth,
                                    float sil_thres, int use_sil, float inv_n_depth, const float* outlier_thresh,
                                    float* v_render, float* losses, void* stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
-    if (!cam || (mode != 0 && mode != 1)) { set_error("isogs_loss_l1_fused: bad argument"); return ISOGS_E_ARG; }
+    return launch_loss_l1(cam, mode, render, alpha, gt_rgb, gt_depth, nullptr, w_im, w_depth, sil_thres, use_sil,
+                          inv_n_depth, outlier_thresh, v_render, losses, (cudaStream_t)stream_);
+}
+
+int isogs::launch_loss_l1(const isogs_camera* cam, int mode, const float* render, const float* alpha, const float* gt_rgb,
+                          const float* gt_depth, const isogs_frame* frame_dev, float w_im, float w_depth,
+                          float sil_thres, int use_sil, float inv_n_depth, const float* outlier_thresh,
+                          float* v_render, float* losses, cudaStream_t stream) {
+    if (!cam || (mode != 0 && mode != 1) || (!frame_dev && (!gt_rgb || !gt_depth))) {
+        set_error("isogs_loss_l1_fused: bad argument");
+        return ISOGS_E_ARG;
+    }
     if (mode == 1 && outlier_thresh) {
         set_error("isogs_loss_l1_fused: the outlier mask is supported for tracking (mode 0) only");
         return ISOGS_E_ARG;
@@ -306,11 +363,11 @@ extern "C" int isogs_loss_l1_fused(const isogs_camera* cam, int mode, const floa
     if (vec) {
         const int blocks = (int)std::min<int64_t>((P / 4 + 255) / 256, 148 * 8);
         loss_l1_kernel<4><<<blocks, 256, 0, stream>>>(P, mode, render, alpha, gt_rgb, gt_depth, w_im, w_depth, sil_thres,
-                                                      use_sil, inv_nd, inv_nc, outlier_thresh, v_render, losses);
+                                                      use_sil, inv_nd, inv_nc, outlier_thresh, v_render, losses, frame_dev);
     } else {
         const int blocks = (int)std::min<int64_t>((P + 255) / 256, 148 * 8);
         loss_l1_kernel<1><<<blocks, 256, 0, stream>>>(P, mode, render, alpha, gt_rgb, gt_depth, w_im, w_depth, sil_thres,
-                                                      use_sil, inv_nd, inv_nc, outlier_thresh, v_render, losses);
+                                                      use_sil, inv_nd, inv_nc, outlier_thresh, v_render, losses, frame_dev);
     }
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
@@ -319,7 +376,8 @@ extern "C" int isogs_loss_l1_fused(const isogs_camera* cam, int mode, const floa
 // depth_error = |gt - d| * (gt > 0); threshold = factor * lower median (torch.median), splatam.py:552-553
 __global__ void __launch_bounds__(256)
 depth_error_kernel(int64_t P, const float* __restrict__ render_depth, const float* __restrict__ gt_depth,
-                   float* __restrict__ err) {
+                   float* __restrict__ err, const isogs_frame* __restrict__ fr) {
+    if (fr != nullptr) gt_depth = fr->gt_depth;
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < P) { const float gd = gt_depth[i]; err[i] = fabsf(gd - render_depth[i]) * ((gd > 0.f) ? 1.f : 0.f); }
 }
@@ -327,17 +385,29 @@ __global__ void median_pick_kernel(int64_t P, const float* __restrict__ sorted, 
     if (threadIdx.x == 0 && blockIdx.x == 0) *out = factor * sorted[(P - 1) / 2];
 }
 
+namespace isogs {
+int launch_outlier_threshold(const isogs_camera* cam, const float* render_depth, const float* gt_depth,
+                             const isogs_frame* frame_dev, float factor, float* scratch, void* sort_temp,
+                             size_t sort_temp_bytes, float* thresh_out, cudaStream_t stream);
+}
+
 extern "C" int isogs_depth_outlier_threshold(const isogs_camera* cam, const float* render_depth, const float* gt_depth,
                                              float factor, float* scratch, void* sort_temp, size_t sort_temp_bytes,
                                              float* thresh_out, void* stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
-    if (!cam || !render_depth || !gt_depth || !scratch || !thresh_out) {
+    return launch_outlier_threshold(cam, render_depth, gt_depth, nullptr, factor, scratch, sort_temp, sort_temp_bytes,
+                                    thresh_out, (cudaStream_t)stream_);
+}
+
+int isogs::launch_outlier_threshold(const isogs_camera* cam, const float* render_depth, const float* gt_depth,
+                                    const isogs_frame* frame_dev, float factor, float* scratch, void* sort_temp,
+                                    size_t sort_temp_bytes, float* thresh_out, cudaStream_t stream) {
+    if (!cam || !render_depth || (!gt_depth && !frame_dev) || !scratch || !thresh_out) {
         set_error("isogs_depth_outlier_threshold: bad argument");
         return ISOGS_E_ARG;
     }
     const int64_t P = (int64_t)cam->width * cam->height;
     if (P <= 0 || P >= (1ll << 31)) { set_error("isogs_depth_outlier_threshold: bad image size"); return ISOGS_E_ARG; }
-    depth_error_kernel<<<(unsigned)((P + 255) / 256), 256, 0, stream>>>(P, render_depth, gt_depth, scratch);
+    depth_error_kernel<<<(unsigned)((P + 255) / 256), 256, 0, stream>>>(P, render_depth, gt_depth, scratch, frame_dev);
     size_t need = 0;
     ISOGS_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, need, scratch, scratch + P, (int)P, 0, 32, stream));
     if (need > sort_temp_bytes) { set_error("sort temp too small (%zu needed)", need); return ISOGS_E_ARG; }
@@ -347,9 +417,33 @@ extern "C" int isogs_depth_outlier_threshold(const isogs_camera* cam, const floa
     return ISOGS_OK;
 }
 
+// uint8 HWC colour + uint16 depth -> fp32 planes (basedataset.py:299-340: color / 255, depth / png_depth_scale)
+__global__ void __launch_bounds__(256)
+unpack_rgbd_kernel(int64_t P, const uint8_t* __restrict__ rgb, const uint16_t* __restrict__ depth, float inv_scale,
+                   float* __restrict__ gt_rgb, float* __restrict__ gt_depth) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    gt_rgb[i] = (float)rgb[3 * i] / 255.0f;
+    gt_rgb[P + i] = (float)rgb[3 * i + 1] / 255.0f;
+    gt_rgb[2 * P + i] = (float)rgb[3 * i + 2] / 255.0f;
+    gt_depth[i] = (float)depth[i] * inv_scale;
+}
+
+extern "C" int isogs_unpack_rgbd(const isogs_camera* cam, const uint8_t* rgb_hwc, const uint16_t* depth_u16,
+                                 float inv_depth_scale, float* gt_rgb, float* gt_depth, void* stream_) {
+    if (!cam || !rgb_hwc || !depth_u16 || !gt_rgb || !gt_depth) { set_error("isogs_unpack_rgbd: null argument"); return ISOGS_E_ARG; }
+    const int64_t P = (int64_t)cam->width * cam->height;
+    if (P == 0) return ISOGS_OK;
+    unpack_rgbd_kernel<<<(unsigned)((P + 255) / 256), 256, 0, (cudaStream_t)stream_>>>(P, rgb_hwc, depth_u16, inv_depth_scale,
+                                                                                      gt_rgb, gt_depth);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
+
 extern "C" int isogs_adam_fused(const isogs_adam_group* groups, int n_groups, float beta1, float beta2, float eps,
-                                int step, void* stream_) {
+                                int step, const isogs_adam_state* state, const int32_t* skip_flag, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
+    if (state != nullptr) step = 1;   // ignored: the bias corrections come from the device
     if (!groups || n_groups < 0 || n_groups > MAX_GROUPS || step < 1) {
         set_error("isogs_adam_fused: bad argument (n_groups=%d, max %d, step=%d)", n_groups, MAX_GROUPS, step);
         return ISOGS_E_ARG;
@@ -362,6 +456,8 @@ extern "C" int isogs_adam_fused(const isogs_adam_group* groups, int n_groups, fl
     a.one_minus_b1 = 1.0f - beta1; a.one_minus_b2 = 1.0f - beta2;
     a.inv_bc2_sqrt = (float)(1.0 / std::sqrt(bc2));
     a.eps = eps;
+    a.state = state;
+    a.skip = skip_flag;
     int64_t blocks = 0;
     for (int k = 0; k < n_groups; ++k) {
         const isogs_adam_group& g = groups[k];
@@ -369,7 +465,7 @@ extern "C" int isogs_adam_fused(const isogs_adam_group* groups, int n_groups, fl
         const int j = a.n++;
         a.p[j] = g.param; a.g[j] = g.grad; a.m[j] = g.exp_avg; a.v[j] = g.exp_avg_sq;
         a.numel[j] = g.numel;
-        a.step_size[j] = (float)((double)g.lr / bc1);
+        a.step_size[j] = state ? g.lr : (float)((double)g.lr / bc1);
         a.block_start[j] = blocks;
         blocks += (g.numel + (int64_t)ADAM_BLOCK * ADAM_VEC - 1) / ((int64_t)ADAM_BLOCK * ADAM_VEC);
     }

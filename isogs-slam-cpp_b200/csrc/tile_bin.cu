@@ -118,7 +118,13 @@ tile_scan_kernel(int n, const int32_t* __restrict__ counts, int32_t* __restrict_
         const int32_t total = s_carry;
         ranges[n] = capacity >= 0 ? min(total, capacity) : total;
         if (true_ranges) true_ranges[n] = total;
-        if (totals) { totals[0] = total; totals[1] = (capacity >= 0 && total > capacity) ? 1 : 0; }
+        if (totals) {
+            // the overflow word is STICKY (only the host clears it, after growing the buffers): while it is set the
+            // step's Adam / best-pose kernels are no-ops, and totals[0] keeps the largest count seen
+            const bool over = capacity >= 0 && total > capacity;
+            if (over) { totals[0] = totals[1] ? max(totals[0], total) : total; totals[1] = 1; }
+            else if (!totals[1]) totals[0] = total;
+        }
     }
 }
 
@@ -521,7 +527,7 @@ extern "C" int isogs_tile_bin_async(const isogs_camera* cam, int64_t N, int64_t 
     const int tw = (cam->width + TILE - 1) / TILE, th = (cam->height + TILE - 1) / TILE;
     if (N == 0) {
         ISOGS_CUDA(cudaMemsetAsync(tile_ranges, 0, sizeof(int32_t) * (tw * th + 1), stream));
-        ISOGS_CUDA(cudaMemsetAsync(totals, 0, sizeof(int32_t) * 2, stream));
+        ISOGS_CUDA(cudaMemsetAsync(totals, 0, sizeof(int32_t), stream)); // the sticky overflow word stays
         return ISOGS_OK;
     }
     return counting_bin(tw, th, N, (int32_t)capacity, /*clamp=*/true, rec, radii, bucket, keys_sorted, vals_sorted,

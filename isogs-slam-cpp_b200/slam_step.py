@@ -58,6 +58,25 @@ class GaussianMap:
         self.grad_flat = self._new_grad_flat(total)
         self._carve()
         self.step_count = 0
+        # isogs_adam_state on the DEVICE (step, bias corrections): advanced by the step's first kernel
+        self.adam_state = torch.zeros((4,), dtype=torch.float64, device=self.device)
+
+    def c_struct(self, with_grads=True):
+        """isogs_gaussians over the current buffers (pointers only)."""
+        key = (self.count, with_grads, tuple(self.p[k].data_ptr() for k in PARAM_ORDER), self.grad_flat.data_ptr())
+        hit = getattr(self, "_cs", None)
+        if hit is not None and hit[0] == key:
+            return hit[1]
+        g = _lib.Gaussians()
+        g.N, g.scale_dim = self.count, self.sd
+        for i, k in enumerate(PARAM_ORDER):
+            g.p[i] = self.p[k].data_ptr()
+            has = with_grads and k in self.g
+            g.g[i] = self.g[k].data_ptr() if has else None
+            g.m[i] = self.m[k].data_ptr() if has else None
+            g.v[i] = self.v[k].data_ptr() if has else None
+        self._cs = (key, g)
+        return g
 
     def _new_grad_flat(self, total):
         if self.grad_alloc is None:
@@ -86,6 +105,7 @@ class GaussianMap:
             self.m[k].zero_()
             self.v[k].zero_()
         self.step_count = 0
+        self.adam_state.zero_()
 
     def reset_stats(self):
         """add_new_gaussians and densify re-create the three statistics as zeros (splatam.py:835-837,
@@ -145,12 +165,73 @@ class StepWorkspace:
         self.ssim = self.small[27:28]                               # mean SSIM of the last map_step(ssim=True)
         self.dmaps = None                                           # [9,H,W] SSIM derivative maps, on first use
         self.outlier_scratch = None                                 # [2,H,W] depth-error sort buffers, on first use
+        self.median_tmp, self.median_b = None, 0                    # CUB temp of the median sort (its OWN buffer)
         self.isect_cap = 0
         self._grow_isects(max(1024, 3 * n_cap))
         # device-side intersection count {n_isects, overflow} + its lagged pinned mirror
         self.totals = torch.zeros((2,), dtype=i32, device=device)
         self.totals_host = torch.zeros((2,), dtype=i32).pin_memory()
         self._totals_ev = None
+        # the DEVICE-side current-frame slot (isogs_frame) a captured graph reads, per-keyframe frame structs and
+        # the captured graphs themselves
+        self.cur_frame = torch.zeros((C.sizeof(_lib.Frame),), dtype=torch.uint8, device=device)
+        self._frames = {}
+        self._graphs = {}
+        self._cws = None
+
+    def c_struct(self):
+        """isogs_workspace over the current buffers (rebuilt when a buffer was re-allocated)."""
+        bufs = (self.rec, self.v_rec, self.radii, self.ku, self.vs, self.ranges, self.totals, self.sort_tmp, self.render,
+                self.v_render, self.alpha, self.last, self.small, self.dmaps, self.outlier_scratch, self.median_tmp)
+        key = tuple(0 if b is None else b.data_ptr() for b in bufs) + (self.isect_cap,)
+        if self._cws is not None and self._cws[0] == key:
+            return self._cws[1]
+        w = _lib.Workspace()
+        w.rec, w.v_rec, w.radii = self.rec.data_ptr(), self.v_rec.data_ptr(), self.radii.data_ptr()
+        w.bucket, w.vals, w.ranges = self.ku.data_ptr(), self.vs.data_ptr(), self.ranges.data_ptr()
+        w.totals, w.sort_temp, w.sort_temp_bytes = self.totals.data_ptr(), self.sort_tmp.data_ptr(), self.sort_b
+        w.isect_cap = self.isect_cap
+        w.render, w.v_render = self.render.data_ptr(), self.v_render.data_ptr()
+        w.alpha, w.last, w.small = self.alpha.data_ptr(), self.last.data_ptr(), self.small.data_ptr()
+        w.adam_state = None                                   # filled per call (the map's or the pose's state)
+        w.dmaps = None if self.dmaps is None else self.dmaps.data_ptr()
+        w.median_scratch = None if self.outlier_scratch is None else self.outlier_scratch.data_ptr()
+        w.median_temp = None if self.median_tmp is None else self.median_tmp.data_ptr()
+        w.median_temp_bytes = self.median_b
+        self._cws = (key, w)
+        self.drop_graphs()                                    # captured launches hold the old pointers
+        return w
+
+    def frame(self, gt_rgb, gt_depth, pose=None, inv_n_depth=1.0):
+        """DEVICE isogs_frame for (ground truth, keyframe pose, 1/n_valid): built once per distinct value (one small
+        H2D copy), then reused -- the per-iteration path has no host->device traffic for it."""
+        q = (1.0, 0.0, 0.0, 0.0) if pose is None else tuple(float(v) for v in pose.q)
+        t = (0.0, 0.0, 0.0) if pose is None else tuple(float(v) for v in pose.t)
+        key = (gt_rgb.data_ptr(), gt_depth.data_ptr(), q, t, float(inv_n_depth))
+        hit = self._frames.get(key)
+        if hit is not None:
+            return hit
+        f = _lib.Frame()
+        f.gt_rgb, f.gt_depth = gt_rgb.data_ptr(), gt_depth.data_ptr()
+        f.pose[:] = list(q) + list(t)
+        f.inv_n_depth = float(inv_n_depth)
+        host = torch.frombuffer(bytearray(bytes(f)), dtype=torch.uint8)
+        dev = host.to(self.device)
+        if len(self._frames) >= 256:
+            self._frames.pop(next(iter(self._frames)))
+        self._frames[key] = dev
+        return dev
+
+    def drop_graphs(self):
+        for ge in self._graphs.values():
+            lib().isogs_graph_destroy(ge)
+        self._graphs = {}
+
+    def __del__(self):
+        try:
+            self.drop_graphs()
+        except Exception:
+            pass
 
     @property
     def M(self):
@@ -160,26 +241,40 @@ class StepWorkspace:
     def post_totals(self):
         """Queue an async copy of {n_isects, overflow} to pinned memory (no sync)."""
         self.totals_host.copy_(self.totals, non_blocking=True)
-        self._totals_ev = torch.cuda.Event()
+        if self._totals_ev is None:
+            self._totals_ev = torch.cuda.Event()
         self._totals_ev.record()
 
     def check_overflow(self, wait=False):
-        """Look at the PREVIOUS forward's count if its copy has landed.  On overflow the tile lists of
-        that forward were truncated (never out of bounds): grow the buffers and report it."""
-        ev = self._totals_ev
-        if ev is None or not (wait or ev.query()):
+        """The overflow word is STICKY on the device (tile_scan_kernel ORs into totals[1]; the largest count seen
+        while it is set is kept in totals[0]) and mirrored to pinned memory after every forward, so the host reads
+        the mirror WITHOUT gating on the newest copy: whichever copy has landed carries the flag.  While the flag is
+        set the Adam / best-pose kernels of the affected steps are device-side no-ops (they are handed totals + 1),
+        so no parameter was updated from a truncated render.  On overflow: grow the buffers, clear the flag."""
+        if wait and self._totals_ev is not None:
+            self._totals_ev.synchronize()
+        if int(self.totals_host[1]) == 0:
             return False
-        if wait:
-            ev.synchronize()
-        self._totals_ev = None
-        n, over = int(self.totals_host[0]), int(self.totals_host[1])
-        if over:
-            self._grow_isects(int(n * 1.25) + 1024)
-            import warnings
-            warnings.warn(f"tile-intersection buffers overflowed (needed {n}); grown to {self.isect_cap}. "
-                          "The affected step rendered truncated tile lists.")
-            return True
-        return False
+        torch.cuda.current_stream().synchronize()              # rare path: settle, then read the final count
+        n = int(self.totals[0].item())
+        self._grow_isects(max(int(n * 1.25) + 1024, self.isect_cap))
+        self.totals.zero_()
+        self.totals_host.zero_()
+        import warnings
+        warnings.warn(f"tile-intersection buffers overflowed (needed {n}); grown to {self.isect_cap}. "
+                      "The affected steps were skipped on the device (no Adam / best-pose update).")
+        return True
+
+    def median_temp(self):
+        """Temp storage of the device-side median (CUB key sort over P depth errors).  Its own buffer: the
+        intersection buffers (vs / ku / sort_tmp) must not be re-allocated between a forward and its backward."""
+        P = self.cam.width * self.cam.height
+        if self.outlier_scratch is None:
+            self.outlier_scratch = torch.empty((2 * P,), dtype=torch.float32, device=self.device)
+        if self.median_tmp is None:
+            _, self.median_b = _lib.temp_bytes(0, P)
+            self.median_tmp = torch.empty((self.median_b,), dtype=torch.uint8, device=self.device)
+        return self.outlier_scratch, self.median_tmp, self.median_b
 
     def ensure_gaussians(self, n):
         """Grow the per-Gaussian scratch when the map has grown (densification)."""
@@ -207,7 +302,7 @@ class StepWorkspace:
         self.sort_tmp = torch.empty((self.sort_b,), dtype=torch.uint8, device=dev)
 
 
-def render_forward(ws, gmap, pose=None, pose_dev=None, ch=5, marks=None):
+def render_forward(ws, gmap, pose=None, pose_dev=None, ch=5, marks=None, zero_v_rec=False):
     """preprocess (raw params, fused activations + frame transform) -> bin -> blend, with NO host sync:
     the intersection count stays on the device (ws.totals) and is checked one step late
     (StepWorkspace.check_overflow), replacing the blocking `.item()` of gsplat Intersect.cpp:80."""
@@ -219,7 +314,8 @@ def render_forward(ws, gmap, pose=None, pose_dev=None, ch=5, marks=None):
     check(L.isogs_preprocess_fwd(C.byref(cam), C.byref(pose) if pose is not None else None, _ptr(pose_dev), N,
                                  _ptr(gmap.p["means3D"]), _ptr(gmap.p["log_scales"]), gmap.sd, _ptr(quats),
                                  _ptr(gmap.p["logit_opacities"]), _ptr(gmap.p["rgb_colors"]), ch, flags,
-                                 _ptr(ws.rec), _ptr(ws.radii), None, None, None, 0, None, st))
+                                 _ptr(ws.rec), _ptr(ws.radii), None, None, None, 0, None,
+                                 _ptr(ws.v_rec) if zero_v_rec else None, st))
     _mark(marks, "preprocess_fwd")
     check(L.isogs_tile_bin_async(C.byref(cam), N, ws.isect_cap, _ptr(ws.rec), _ptr(ws.radii), _ptr(ws.ku), None,
                                  _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.totals), _ptr(ws.sort_tmp), ws.sort_b, st))
@@ -229,12 +325,16 @@ def render_forward(ws, gmap, pose=None, pose_dev=None, ch=5, marks=None):
     ws.post_totals()
 
 
-def render_backward(ws, gmap, pose=None, pose_dev=None, ch=5, want_gaussians=True, want_pose=False, marks=None):
+def render_backward(ws, gmap, pose=None, pose_dev=None, ch=5, want_gaussians=True, want_pose=False, marks=None,
+                    zero_v_rec=True):
+    """Per-op backward (the fused steps do not use it).  zero_v_rec=False when the forward already cleared v_rec
+    (render_forward(zero_v_rec=True))."""
     cam, N = ws.cam, gmap.count
     flags = _lib.F_LOG_SCALES | _lib.F_LOGIT_OPAC
     L, st = lib(), _stream()
-    ws.v_rec[:N].zero_()
-    _mark(marks, "zero_v_rec")
+    if zero_v_rec:
+        ws.v_rec[:N].zero_()
+        _mark(marks, "zero_v_rec")
     if N > 0:
         # tracking needs only the geometric + depth-channel gradients (the pose's inputs)
         bwd = L.isogs_blend_bwd if want_gaussians else L.isogs_blend_bwd_geom
@@ -256,15 +356,10 @@ def loss_l1(ws, mode, gt_rgb, gt_depth, inv_n_depth=1.0, w_im=0.5, w_depth=1.0, 
             ignore_outlier_depth=False):
     thr = None
     if ignore_outlier_depth:    # splatam.py:551-554: 10 x median depth error, computed on the device (no sync)
-        P = ws.cam.width * ws.cam.height
-        if ws.outlier_scratch is None:
-            ws.outlier_scratch = torch.empty((2 * P,), dtype=torch.float32, device=ws.device)
-        if ws.sort_b < _lib.temp_bytes(0, P)[1]:
-            ws._grow_isects(max(ws.isect_cap, P))
+        scratch, tmp, tmp_b = ws.median_temp()
         thr = ws.small[28:29]
         check(lib().isogs_depth_outlier_threshold(C.byref(ws.cam), _ptr(ws.render[3]), _ptr(gt_depth), 10.0,
-                                                  _ptr(ws.outlier_scratch), _ptr(ws.sort_tmp), ws.sort_b, _ptr(thr),
-                                                  _stream()))
+                                                  _ptr(scratch), _ptr(tmp), tmp_b, _ptr(thr), _stream()))
     check(lib().isogs_loss_l1_fused(C.byref(ws.cam), mode, _ptr(ws.render), _ptr(ws.alpha), _ptr(gt_rgb),
                                     _ptr(gt_depth), w_im, w_depth, sil_thres, int(use_sil), inv_n_depth, _ptr(thr),
                                     _ptr(ws.v_render), _ptr(ws.losses), _stream()))
@@ -323,7 +418,9 @@ def iso_flat_loss(ws, gmap, w_flat=50.0, w_iso=2.0, seed=0, query_idx=None, samp
                                 _ptr(g.get("logit_opacities")), _ptr(ws.losses), _ptr(ws.geo), st))
 
 
-def adam_gaussians(gmap, lrs=MAPPING_LRS, eps=1e-15, beta1=0.9, beta2=0.999):
+def adam_gaussians(gmap, lrs=MAPPING_LRS, eps=1e-15, beta1=0.9, beta2=0.999, skip_flag=None):
+    """Stand-alone fused Adam with the HOST step count (torch.optim.Adam); the fused map_step keeps its own count on
+    the device (gmap.adam_state) -- do not mix the two on one map without reset_optimizer()."""
     gmap.step_count += 1
     names = gmap.grad_names
     arr = (_lib.AdamGroup * len(names))()
@@ -334,7 +431,7 @@ def adam_gaussians(gmap, lrs=MAPPING_LRS, eps=1e-15, beta1=0.9, beta2=0.999):
         arr[i].exp_avg_sq = gmap.v[k].data_ptr()
         arr[i].numel = gmap.count * gmap.widths[k]
         arr[i].lr = lrs[k]
-    check(lib().isogs_adam_fused(arr, len(names), beta1, beta2, eps, gmap.step_count, _stream()))
+    check(lib().isogs_adam_fused(arr, len(names), beta1, beta2, eps, gmap.step_count, None, _ptr(skip_flag), _stream()))
 
 
 def _mark(marks, name):
@@ -344,32 +441,93 @@ def _mark(marks, name):
         marks.append((name, ev))
 
 
+def _params(flags, phases, w_im, w_depth, sil_thres, lr5, eps, beta1=0.9, beta2=0.999):
+    p = _lib.StepParams()
+    p.flags, p.phases = int(flags), int(phases)
+    p.w_im, p.w_depth, p.sil_thres = float(w_im), float(w_depth), float(sil_thres)
+    p.lr[:] = [float(v) for v in lr5]
+    p.beta1, p.beta2, p.eps = float(beta1), float(beta2), float(eps)
+    return p
+
+
+def _event_array(marks):
+    """ISOGS_STEP_EVENTS timing events for one fused step; appended to `marks` as (stage, event) pairs."""
+    if marks is None:
+        return None
+    arr = (C.c_void_p * _lib.STEP_EVENTS)()
+    for i, name in enumerate(_lib.STEP_EVENT_NAMES):
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()                               # creates the underlying cudaEvent_t; re-recorded by the step
+        arr[i] = ev.cuda_event
+        marks.append((name, ev))
+    return arr
+
+
+def _graph_launch(ws, key, enqueue):
+    """Replay the captured launch sequence for `key`, capturing it on first use (capture does not execute)."""
+    L, st = lib(), _stream()
+    ge = ws._graphs.get(key)
+    if ge is None:
+        check(L.isogs_graph_begin(st))
+        try:
+            enqueue()
+        finally:
+            h = C.c_void_p()
+            rc = L.isogs_graph_end(st, C.byref(h))
+        check(rc)
+        ge = ws._graphs[key] = h
+    check(L.isogs_graph_launch(ge, st))
+
+
 def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, allreduce=None, marks=None, w_im=0.5,
-             w_depth=1.0, ssim=False, isoflat=False, iso_seed=0):
-    """One mapping iteration on one keyframe (splatam.py:1412-1476, L1 terms).  `pose` is the keyframe's
-    HOST pose (camera_grad=False).  `allreduce(flat_grad_tensor)` is called between backward and Adam.
-    `marks` (a list) receives (stage, cuda event) pairs for per-stage timing.  `w_im` weighs the mean colour
-    term; `ssim=True` makes that term the reference's 0.8 * L1 + 0.2 * (1 - SSIM) (splatam.py:568), else pure L1;
-    `isoflat=True` adds 50 * flat + 2 * iso (:572-675,733-739; three-axis scales) -- with both flags the loss is the
-    reference's complete mapping loss."""
-    _mark(marks, "begin")
-    ws.small.zero_()
-    render_forward(ws, gmap, pose=pose, marks=marks)
-    _mark(marks, "blend_fwd")
-    loss_l1(ws, 1, gt_rgb, gt_depth, inv_n_depth, w_im=(0.8 * w_im if ssim else w_im), w_depth=w_depth)
-    _mark(marks, "loss")
-    if ssim:
-        loss_ssim(ws, gt_rgb, 0.2 * w_im)
-        _mark(marks, "ssim")
-    render_backward(ws, gmap, pose=pose, want_gaussians=True, marks=marks)
-    if isoflat:
-        iso_flat_loss(ws, gmap, seed=iso_seed)
-        _mark(marks, "isoflat")
-    if allreduce is not None:
-        allreduce(gmap.grad_flat[:gmap.grad_used])
-        _mark(marks, "allreduce")
-    adam_gaussians(gmap, lrs)
-    _mark(marks, "adam")
+             w_depth=1.0, ssim=False, isoflat=False, iso_seed=0, graph=False, eps=1e-15):
+    """One mapping iteration on one keyframe (splatam.py:1412-1476): ONE host call (isogs_map_step) enqueues
+    transform_to_frame + activations + projection, binning, the 5-channel blend, the masked-L1 (+ SSIM) loss, both
+    backwards and the fused Adam; no host sync.  `pose` is the keyframe's HOST pose (camera_grad=False).
+    `allreduce(flat_grad_tensor)` runs between backward and Adam, as do the iso / flat terms (`isoflat=True`, :572-675,
+    three-axis scales) -- with ssim and isoflat the loss is the reference's complete mapping loss.  `marks` (a list)
+    receives (stage, cuda event) pairs.  graph=True replays a captured CUDA graph of the step: one graph serves
+    every keyframe, because the frame is read through the device-side slot ws.cur_frame."""
+    if ssim and ws.dmaps is None:
+        ws.dmaps = torch.empty((9, ws.cam.height, ws.cam.width), dtype=torch.float32, device=ws.device)
+    ws.check_overflow()
+    L, st = lib(), _stream()
+    frame = ws.frame(gt_rgb, gt_depth, pose, inv_n_depth)
+    cws, cgs = ws.c_struct(), gmap.c_struct()
+    cws.adam_state = gmap.adam_state.data_ptr()
+    flags = _lib.STEP_SSIM if ssim else 0
+    lr5 = [lrs.get(k, 0.0) for k in PARAM_ORDER]
+    split = allreduce is not None or isoflat
+    ev = _event_array(marks)
+    gmap.step_count += 1
+    if graph and marks is None:
+        ws.cur_frame.copy_(frame, non_blocking=True)
+        fr = ws.cur_frame.data_ptr()
+        key = ("map", flags, split, id(gmap), gmap.count, gmap.grad_flat.data_ptr(), tuple(lr5), w_im, w_depth, eps)
+        p1 = _params(flags, _lib.PHASE_RENDER if split else _lib.PHASE_RENDER | _lib.PHASE_ADAM, w_im, w_depth, 0.99, lr5, eps)
+        _graph_launch(ws, key, lambda: check(L.isogs_map_step(C.byref(ws.cam), fr, C.byref(cws), C.byref(cgs),
+                                                              C.byref(p1), None, st)))
+    else:
+        p1 = _params(flags, _lib.PHASE_RENDER if split else _lib.PHASE_RENDER | _lib.PHASE_ADAM, w_im, w_depth, 0.99, lr5, eps)
+        check(L.isogs_map_step(C.byref(ws.cam), frame.data_ptr(), C.byref(cws), C.byref(cgs), C.byref(p1), ev, st))
+    if split:
+        if isoflat:
+            iso_flat_loss(ws, gmap, seed=iso_seed)
+            _mark(marks, "isoflat")
+        if allreduce is not None:
+            allreduce(gmap.grad_flat[:gmap.grad_used])
+            _mark(marks, "allreduce")
+        p2 = _params(flags, _lib.PHASE_ADAM, w_im, w_depth, 0.99, lr5, eps)
+        if graph and marks is None:
+            key2 = ("adam", id(gmap), gmap.count, gmap.grad_flat.data_ptr(), tuple(lr5), eps)
+            _graph_launch(ws, key2, lambda: check(L.isogs_map_step(C.byref(ws.cam), ws.cur_frame.data_ptr(), C.byref(cws),
+                                                                   C.byref(cgs), C.byref(p2), None, st)))
+        else:
+            check(L.isogs_map_step(C.byref(ws.cam), frame.data_ptr(), C.byref(cws), C.byref(cgs), C.byref(p2), ev, st))
+            if marks is not None:                  # keep the stage order: the Adam mark goes last
+                k = next(i for i, m in enumerate(marks) if m[0] == "adam")
+                marks.append(marks.pop(k))
+    ws.post_totals()
     return ws.losses
 
 
@@ -389,13 +547,9 @@ def add_new_gaussians(ws, gmap, pose, gt_rgb, gt_depth, sil_thres=0.5, noise_std
     ws.ensure_gaussians(gmap.count)
     render_forward(ws, gmap, pose=pose)
     # 50 x median(|gt_d - d| * (gt_d > 0)) (splatam.py:811-812) by the device-side median kernel; one host read
-    if ws.outlier_scratch is None:
-        ws.outlier_scratch = torch.empty((2 * P,), dtype=torch.float32, device=ws.device)
-    if ws.sort_b < _lib.temp_bytes(0, P)[1]:
-        ws._grow_isects(max(ws.isect_cap, P))
+    scratch, tmp, tmp_b = ws.median_temp()
     check(lib().isogs_depth_outlier_threshold(C.byref(cam), _ptr(ws.render[3]), _ptr(gt_depth), 50.0,
-                                              _ptr(ws.outlier_scratch), _ptr(ws.sort_tmp), ws.sort_b,
-                                              _ptr(ws.small[28:29]), _stream()))
+                                              _ptr(scratch), _ptr(tmp), tmp_b, _ptr(ws.small[28:29]), _stream()))
     thr = float(ws.small[28])
     gmap.reserve(gmap.count + P)
     count = torch.tensor([gmap.count], dtype=torch.int32, device=gmap.device)
@@ -457,12 +611,18 @@ def prune_gaussians(ws, gmap, opac_thres=0.005, max_scale=float("inf")):
     return N - _compact(gmap, keep, N)
 
 
-def accumulate_densify_stats(ws, gmap, v_xy=None, scale=(1.0, 1.0)):
+def accumulate_densify_stats(ws, gmap, v_xy=None, scale=None):
     """accumulate_mean2d_gradient + the max_2D_radius update of get_loss (slam_external.py:100-104,
-    splatam.py:751-753) for the Gaussians seen by the last render.  v_xy defaults to the screen-space gradient
-    of the last backward (ws.v_rec, pixel units).  NOTE: the reference accumulates the gradient of the COLOUR
-    render only (splatam.py:528-530); the fused 5-channel step's v_rec also carries the depth-loss part -- use
+    splatam.py:751-753) for the Gaussians seen by the last render.  ONE convention everywhere: the
+    accumulated number is the norm of `means2D.grad` as the Inria rasterizer writes it, i.e. the screen-space
+    gradient in NDC units v_xy * (W/2, H/2) -- the unit the reference's grad_thresh = 2e-4 was tuned on
+    (configs/replica/splatam.py:135).  v_xy=None takes the pixel-unit gradient of the last backward (ws.v_rec) and
+    applies that scaling; an explicit v_xy is a `means2D.grad` tensor (already scaled, e.g. from the drop-in
+    GaussianRasterizer) and is accumulated as-is.  NOTE: the reference accumulates the gradient of the COLOUR render
+    only (splatam.py:528-530); the fused 5-channel step's v_rec also carries the depth-loss part -- use
     `colour_only_screen_gradient` for the reference's exact statistic."""
+    if scale is None:
+        scale = (0.5 * ws.cam.width, 0.5 * ws.cam.height) if v_xy is None else (1.0, 1.0)
     v = ws.v_rec if v_xy is None else v_xy
     check(lib().isogs_densify_stats(gmap.count, _ptr(ws.radii), _ptr(v), v.shape[1], scale[0], scale[1],
                                     _ptr(gmap.vars["means2D_gradient_accum"]), _ptr(gmap.vars["denom"]),
@@ -471,7 +631,8 @@ def accumulate_densify_stats(ws, gmap, v_xy=None, scale=(1.0, 1.0)):
 
 def colour_only_screen_gradient(ws, gmap):
     """Second blend backward with the depth planes of v_render zeroed: dL_colour/d(mean2D) exactly as the
-    reference's separate colour render sees it.  Costs one extra blend_bwd; only for densification statistics."""
+    reference's separate colour render sees it, in PIXEL units (v_rec rows): pass it as
+    accumulate_densify_stats(ws, gmap, v_xy=..., scale=(W/2, H/2)).  Costs one extra blend_bwd."""
     N = gmap.count
     if getattr(ws, "v_rec2", None) is None or ws.v_rec2.shape[0] < ws.v_rec.shape[0]:
         ws.v_rec2 = torch.empty_like(ws.v_rec)
@@ -578,6 +739,22 @@ class PoseState:
         # best candidate {q, t, min loss} (splatam.py:1240-1242,1287-1290), kept on the device
         self.best = torch.tensor(list(q) + list(t) + [1e20], dtype=torch.float32, device=device)
         self.step_count = 0
+        self.adam_state = torch.zeros((4,), dtype=torch.float64, device=device)   # isogs_adam_state of the pose optimizer
+        self._stage = torch.zeros((15,), dtype=torch.float32).pin_memory()
+
+    def reset(self, q, t):
+        """Start the next frame IN PLACE (same device buffers, so a captured tracking graph stays valid): the
+        reference re-creates the pose optimizer per frame (splatam.py:1237)."""
+        self._stage[:7] = torch.tensor(list(q) + list(t), dtype=torch.float32)
+        self._stage[7:14] = self._stage[:7]
+        self._stage[14] = 1e20
+        self.pose.copy_(self._stage[:7], non_blocking=True)
+        self.best.copy_(self._stage[7:15], non_blocking=True)
+        self.m.zero_()
+        self.v.zero_()
+        self.adam_state.zero_()
+        self.step_count = 0
+        return self
 
     def best_pose(self):
         """(q, t) of the best candidate -- what the reference writes back (splatam.py:1321-1323)."""
@@ -601,22 +778,30 @@ def init_camera_pose(prev1, prev2=None, forward_prop=True):
 
 
 def track_step(ws, gmap, ps, gt_rgb, gt_depth, lrs=TRACKING_LRS, eps=1e-8, use_sil=True, sil_thres=0.99,
-               ignore_outlier_depth=False):
-    """One tracking iteration (splatam.py:1247-1290): only the pose gets a gradient and a step."""
-    ws.small.zero_()
-    render_forward(ws, gmap, pose_dev=ps.pose)
-    loss_l1(ws, 0, gt_rgb, gt_depth, 1.0, sil_thres=sil_thres, use_sil=use_sil,
-            ignore_outlier_depth=ignore_outlier_depth)
-    render_backward(ws, gmap, pose_dev=ps.pose, want_gaussians=False, want_pose=True)
+               ignore_outlier_depth=False, graph=False, marks=None):
+    """One tracking iteration (splatam.py:1247-1290) as ONE host call (isogs_track_step): only the pose gets a
+    gradient and an Adam step; the best candidate is kept on the device.  graph=True replays a captured graph (the
+    same graph serves every frame as long as `ps` and the ground-truth buffers are reused in place)."""
+    if ignore_outlier_depth:
+        ws.median_temp()
+    ws.check_overflow()
+    L, st = lib(), _stream()
+    frame = ws.frame(gt_rgb, gt_depth)
+    cws, cgs = ws.c_struct(), gmap.c_struct(with_grads=False)
+    cws.adam_state = None
+    flags = (_lib.STEP_OUTLIER if ignore_outlier_depth else 0) | (0 if use_sil else _lib.STEP_NO_SIL)
+    prm = _params(flags, _lib.PHASE_RENDER | _lib.PHASE_ADAM, 0.5, 1.0, sil_thres,
+                  [lrs["cam_unnorm_rots"], lrs["cam_trans"], 0.0, 0.0, 0.0], eps)
     ps.step_count += 1
-    arr = (_lib.AdamGroup * 2)()
-    for i, (off, n, lr) in enumerate(((0, 4, lrs["cam_unnorm_rots"]), (4, 3, lrs["cam_trans"]))):
-        arr[i].param = ps.pose.data_ptr() + 4 * off
-        arr[i].grad = ws.v_pose.data_ptr() + 4 * off
-        arr[i].exp_avg = ps.m.data_ptr() + 4 * off
-        arr[i].exp_avg_sq = ps.v.data_ptr() + 4 * off
-        arr[i].numel = n
-        arr[i].lr = lr
-    check(lib().isogs_adam_fused(arr, 2, 0.9, 0.999, eps, ps.step_count, _stream()))
-    check(lib().isogs_pose_keep_best(_ptr(ws.losses), _ptr(ps.pose), _ptr(ps.best), _stream()))
+    args = (_ptr(ps.pose), _ptr(ps.m), _ptr(ps.v), _ptr(ps.best), _ptr(ps.adam_state))
+    if graph and marks is None:
+        ws.cur_frame.copy_(frame, non_blocking=True)
+        fr = ws.cur_frame.data_ptr()
+        key = ("track", flags, id(gmap), gmap.count, ps.pose.data_ptr(), float(sil_thres), tuple(prm.lr), eps)
+        _graph_launch(ws, key, lambda: check(L.isogs_track_step(C.byref(ws.cam), fr, C.byref(cws), C.byref(cgs), *args,
+                                                                C.byref(prm), None, st)))
+    else:
+        check(L.isogs_track_step(C.byref(ws.cam), frame.data_ptr(), C.byref(cws), C.byref(cgs), *args, C.byref(prm),
+                                 _event_array(marks), st))
+    ws.post_totals()
     return ws.losses

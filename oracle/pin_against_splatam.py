@@ -108,8 +108,11 @@ class _OracleRasterize(torch.autograd.Function):
         v_rec = orc.blend_bwd(cam, 4, r["rec"], r["vals"], r["ranges"], r["alpha"], r["last"], v_render)
         g = orc.preprocess_bwd(cam, *a, r["radii"], r["rec"], v_rec, ch=4, flags=0)
         t = torch.from_numpy
+        # means2D.grad as the Inria rasterizer writes it: the screen-space gradient in NDC units,
+        # v_xy * (W/2, H/2) -- the one convention of the repo (csrc/preprocess.cu, slam_step.py)
         v_m2d = torch.zeros((a[0].shape[0], 3))
-        v_m2d[:, :2] = t(v_rec[:, :2].copy())
+        v_m2d[:, 0] = t(v_rec[:, 0].copy()) * (0.5 * W)
+        v_m2d[:, 1] = t(v_rec[:, 1].copy()) * (0.5 * H)
         return (t(g["means"]), v_m2d, t(g["colors"]), t(g["opacities"]).reshape(ctx.oshape), t(g["scales"]),
                 t(g["quats"]), None)
 

@@ -53,6 +53,24 @@ def test_struct_layout_matches_header(pkg):
     assert ctypes.sizeof(pkg._lib.Pose) == 28
 
 
+def test_step_struct_layouts_match_the_compiler(pkg, tmp_path):
+    """The ctypes mirrors of the fused-step structs against sizeof / offsetof as gcc sees the header."""
+    import subprocess
+    src = tmp_path / "sz.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "isogs_rast.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n",'
+                   'sizeof(isogs_adam_state), sizeof(isogs_frame), offsetof(isogs_frame, pose), sizeof(isogs_gaussians),'
+                   'sizeof(isogs_workspace), offsetof(isogs_workspace, adam_state), sizeof(isogs_step_params),'
+                   'offsetof(isogs_step_params, lr));return 0;}\n')
+    exe = tmp_path / "sz"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    got = [int(v) for v in subprocess.check_output([str(exe)], text=True).split()]
+    L = pkg._lib
+    want = [ctypes.sizeof(L.AdamState), ctypes.sizeof(L.Frame), L.Frame.pose.offset, ctypes.sizeof(L.Gaussians),
+            ctypes.sizeof(L.Workspace), L.Workspace.adam_state.offset, ctypes.sizeof(L.StepParams), L.StepParams.lr.offset]
+    assert got == want, (got, want)
+    assert ctypes.sizeof(L.AdamState) == 32 and ctypes.sizeof(L.Frame) == 48
+
+
 def test_no_cpu_fallback(pkg):
     import torch
     import pytest

@@ -98,7 +98,7 @@ def test_adam_kernel_matches_torch(pkg, eps):
             arr[i].param, arr[i].grad = gp[i].data_ptr(), gg[i].data_ptr()
             arr[i].exp_avg, arr[i].exp_avg_sq = gm[i].data_ptr(), gv[i].data_ptr()
             arr[i].numel, arr[i].lr = gp[i].numel(), lrs[i]
-        pkg._lib.check(pkg.lib().isogs_adam_fused(arr, len(shapes), 0.9, 0.999, eps, step, _stream()))
+        pkg._lib.check(pkg.lib().isogs_adam_fused(arr, len(shapes), 0.9, 0.999, eps, step, None, None, _stream()))
     torch.cuda.synchronize()
     for i, (a, b) in enumerate(zip(gp, tp)):
         d = (a.cpu() - b.detach()).abs().max().item()

@@ -224,9 +224,14 @@ def test_gpu_map_step_matches_reference(fx):
         if it == 0:
             g = {k: gmap.g[k].cpu().numpy() for k in GAUSS}
             rows = _check_map_gradients(lambda k: g[k], fx)
-            # (means2D.grad of the reference comes from the colour render alone, splatam.py:528-530; the fused
-            # 5-channel step has no separate colour-only screen gradient, so it is not compared here -- the
-            # drop-in rasterizer's means2D.grad is covered by test_dropin_rasterizer_forward_backward.)
+            # a12: means2D.grad of the reference comes from the colour render alone (splatam.py:528-530) and carries
+            # the Inria NDC scaling v_xy * (W/2, H/2) -- the repo's one convention for the screen-space gradient
+            v = ss.colour_only_screen_gradient(ws, gmap)[:gmap.count, :2].cpu().numpy()
+            W, H = gcam.width, gcam.height
+            ref2d = fx["map_means2D_grad"]
+            assert np.all(ref2d[:, 2] == 0)
+            got2d = v * np.array([0.5 * W, 0.5 * H], np.float32)
+            assert np.abs(got2d - ref2d[:, :2]).max() <= 1e-3 * np.abs(ref2d).max()
     for k in GAUSS:
         _check_adam_update(gmap.view(k).cpu().numpy(), fx[f"map_out_{k}"], fx[f"map_grad_{k}"], ss.MAPPING_LRS[k], 2,
                            rows, k)
