@@ -20,12 +20,18 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-O3 --use_fast_math -std=c++17 -gencode arch=compute_100a,code=sm_100a --expt-relaxed-constexpr \
  -ccbin /usr/bin/g++ -Xcompiler -fPIC -I$GS/include -I$GS/csrc -I$GS/csrc/third_party/glm $TINC $PINC \
  -D_GLIBCXX_USE_CXX11_ABI=$ABI -DTORCH_EXTENSION_NAME=gsplat_ref -DTORCH_API_INCLUDE_EXTENSION_H -w"
-# the two kernel files take ~70 s each (19 channel-count instantiations): keep their objects
+# the two rasterize kernel files take ~70 s each (19 channel-count instantiations): keep their objects
 [ -f "$OUT/rast_fwd.o" ] || $NVCC $FLAGS -c "$GS/csrc/RasterizeToPixels3DGSFwd.cu" -o "$OUT/rast_fwd.o" &
 [ -f "$OUT/rast_bwd.o" ] || $NVCC $FLAGS -c "$GS/csrc/RasterizeToPixels3DGSBwd.cu" -o "$OUT/rast_bwd.o" &
+# projection (with the opacity-aware extent, ProjectionEWA3DGSFused.cu:164-184) and the tile intersection:
+# the kernels, their CUB sort and the reference's own host wrapper intersect_tile / intersect_offset (Intersect.cpp)
+[ -f "$OUT/proj.o" ] || $NVCC $FLAGS -c "$GS/csrc/ProjectionEWA3DGSFused.cu" -o "$OUT/proj.o" &
+[ -f "$OUT/isect_tile.o" ] || $NVCC $FLAGS -c "$GS/csrc/IntersectTile.cu" -o "$OUT/isect_tile.o" &
+[ -f "$OUT/isect_host.o" ] || $NVCC $FLAGS -x cu -c "$GS/csrc/Intersect.cpp" -o "$OUT/isect_host.o" &
 $NVCC $FLAGS -x cu -c "$HERE/ref_gsplat/binding.cpp" -o "$OUT/binding.o" &
 wait
-/usr/bin/g++ -shared -o "$SO" "$OUT/binding.o" "$OUT/rast_fwd.o" "$OUT/rast_bwd.o" -L"$TLIB" -Wl,-rpath,"$TLIB" \
+/usr/bin/g++ -shared -o "$SO" "$OUT/binding.o" "$OUT/rast_fwd.o" "$OUT/rast_bwd.o" "$OUT/proj.o" "$OUT/isect_tile.o" \
+  "$OUT/isect_host.o" -L"$TLIB" -Wl,-rpath,"$TLIB" \
   -ltorch -ltorch_cpu -ltorch_cuda -lc10 -lc10_cuda -ltorch_python -L/usr/local/cuda/lib64 -lcudart
 rm -f "$OUT/binding.o"
 echo "built $SO"

@@ -317,6 +317,14 @@ inline Rect tile_rect(float mx, float my, int rx, int ry, int tw, int th) {
 
 } // namespace
 
+extern "C" void orc_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 extern "C" int orc_num_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

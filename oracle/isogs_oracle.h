@@ -135,6 +135,8 @@ void orc_adam(int64_t n, float* p, const float* g, float* m, float* v, float lr,
 int64_t orc_compact_rows(int64_t N, int width, const uint8_t* keep, const float* in, float* out);
 
 int orc_num_threads(void);
+/* launchers such as torchrun export OMP_NUM_THREADS=1: the timed CPU baseline asks for the host's cores explicitly */
+void orc_set_num_threads(int n);
 
 #ifdef __cplusplus
 }

@@ -83,6 +83,10 @@ def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
+def set_num_threads(n):
+    lib().orc_set_num_threads(C.c_int(int(n)))
+
+
 def n_tiles(cam):
     return ((cam.width + 15) // 16) * ((cam.height + 15) // 16)
 

@@ -96,3 +96,96 @@ def test_blend_matches_reference_kernels(pkg, syn, gsref, kind, iso, ch):
     assert rel(v_rec[:, 2:5], vc[0]) <= 2e-3, "v_conics"
     assert rel(v_rec[:, 5], vo[0]) <= 2e-3, "v_opacities"
     assert rel(v_rec[:, 6:6 + ch], vcol[0]) <= 2e-3, "v_colors"
+
+
+# ---------------------------------------------------------------------------------------------
+# projection (WITH the opacity-aware extent) and tile intersection against the reference's kernels
+# ---------------------------------------------------------------------------------------------
+def _quat_R(q):
+    q = q / np.linalg.norm(q)
+    w, x, y, z = q
+    return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+                     [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                     [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]], np.float32)
+
+
+def _proj_scene(iso, n=20000, seed=12):
+    rng = np.random.RandomState(seed)
+    W, H, f = 320, 208, 260.0
+    cx, cy = W / 2 - 0.5, H / 2 - 0.5
+    z = 0.6 + 4.0 * rng.rand(n)
+    u, v = rng.rand(n) * (W + 60) - 30, rng.rand(n) * (H + 60) - 30     # some off-image, some straddling the border
+    means = np.stack([(u - cx) / f * z, (v - cy) / f * z, z], -1).astype(np.float32)
+    means[: n // 60, 2] = rng.rand(n // 60) * 0.02 - 0.005               # behind / at the near plane
+    s = (np.abs(z) / f * (0.5 + 5.0 * rng.rand(n))).astype(np.float32)
+    scales = np.repeat(s[:, None], 3, 1) if iso else (s[:, None] * (0.3 + rng.rand(n, 3))).astype(np.float32)
+    quats = rng.randn(n, 4).astype(np.float32)
+    quats /= np.linalg.norm(quats, axis=1, keepdims=True)
+    opac = rng.rand(n).astype(np.float32)
+    opac[: n // 30] = 0.002 + 0.004 * rng.rand(n // 30)                   # around the 1/255 cull threshold
+    vm = np.eye(4, dtype=np.float32)
+    vm[:3, :3] = _quat_R(np.array([0.995, 0.03, -0.05, 0.02]))
+    vm[:3, 3] = [0.04, -0.03, 0.06]
+    return dict(W=W, H=H, f=f, cx=cx, cy=cy, means=means, scales=scales, quats=quats, opac=opac, vm=vm)
+
+
+@pytest.mark.parametrize("iso", [True, False])
+def test_projection_matches_reference_kernel_with_opacity_extent(pkg, gsref, iso):
+    """isogs_preprocess_fwd with its DEFAULT flags -- the opacity-aware extent min(3.33, sqrt(2 ln(255 o))) of
+    ProjectionEWA3DGSFused.cu:164-184 included -- against projection_ewa_3dgs_fused_fwd_kernel itself
+    (launcher of ProjectionEWA3DGSFused.cu:214-291, opacities passed).  Tolerances of the vendored gsplat's own
+    test_projection (tests/test_basic.py:167-268): means2d / depth / conic 1e-4 relative-ish; the int radii
+    equal except where the reference's fast-math __logf / rsqrt moves a ceil() across an integer."""
+    sc = _proj_scene(iso)
+    W, H = sc["W"], sc["H"]
+    cam = pkg.make_camera(W, H, sc["f"], sc["f"], sc["cx"], sc["cy"], sc["vm"])
+    K = torch.tensor([[sc["f"], 0, sc["cx"]], [0, sc["f"], sc["cy"]], [0, 0, 1]], dtype=torch.float32, device="cuda")
+    means, quats, opac = t(sc["means"]), t(sc["quats"]), t(sc["opac"])
+    scales3 = t(sc["scales"])
+    r_ref, m_ref, d_ref, c_ref = gsref.proj_fwd(means, quats, scales3, opac, t(sc["vm"]), K, W, H, 0.3, 0.01, 100.0)
+    ours_scales = scales3[:, :1].contiguous() if iso else scales3
+    rec, radii, tiles, cum, M = pkg.raster.preprocess(cam, means, ours_scales, None if iso else quats, opac,
+                                                      torch.zeros_like(means), ch=4, flags=0)
+    torch.cuda.synchronize()
+    r_ref, radii = r_ref.cpu().numpy(), radii.cpu().numpy()
+    vis_ref, vis = (r_ref > 0).all(1), (radii > 0).all(1)
+    n = len(vis)
+    assert (vis_ref != vis).sum() <= max(2, int(1e-3 * n)), "visibility differs beyond threshold-level flips"
+    both = vis_ref & vis
+    assert both.sum() > 0.5 * n
+    mism = (r_ref[both] != radii[both]).any(1)
+    assert mism.mean() <= 1e-3, f"radii differ on {mism.mean():.2%} of the visible Gaussians"
+    assert np.abs(r_ref[both] - radii[both]).max() <= 1
+    rec = rec.cpu().numpy()[both]
+    m_ref, d_ref, c_ref = m_ref.cpu().numpy()[both], d_ref.cpu().numpy()[both], c_ref.cpu().numpy()[both]
+    assert np.abs(rec[:, 0:2] - m_ref).max() <= 2e-3, "means2d (pixels)"
+    assert np.abs(rec[:, 10] - d_ref).max() <= 1e-5 * np.abs(d_ref).max()
+    conic = np.stack([2 * rec[:, 2], rec[:, 3], 2 * rec[:, 4]], -1)
+    assert np.abs(conic - c_ref).max() <= 1e-4 * max(1.0, np.abs(c_ref).max())
+    # the extent really is the opacity-aware one: with the flag that disables it the radii of faint splats grow
+    rec2, radii2, _, _, _ = pkg.raster.preprocess(cam, means, ours_scales, None if iso else quats, opac,
+                                                  torch.zeros_like(means), ch=4, flags=pkg._lib.F_NO_OPAC_EXTENT)
+    assert (radii2.cpu().numpy()[both] > radii[both]).any()
+
+
+def test_tile_keys_match_reference_intersect_exactly(pkg, gsref):
+    """isogs_tile_bin against the reference's own intersect_tile (two kernel passes + cumsum + CUB radix sort) and
+    intersect_offset (Intersect.cpp:15-186, IntersectTile.cu:24-114,209-339) on IDENTICAL (means2d, radii, depths):
+    tiles_per_gauss, sorted isect_ids, flatten_ids and offsets must be EQUAL -- the bar of gsplat's test_isect
+    (tests/test_basic.py:451-489)."""
+    sc = _proj_scene(True, n=30000, seed=5)
+    W, H = sc["W"], sc["H"]
+    cam = pkg.make_camera(W, H, sc["f"], sc["f"], sc["cx"], sc["cy"], sc["vm"])
+    means, opac = t(sc["means"]), t(sc["opac"])
+    rec, radii, tiles, cum, M = pkg.raster.preprocess(cam, means, t(sc["scales"][:, :1]), None, opac,
+                                                      torch.zeros_like(means), ch=4, flags=0)
+    ks, vs, ranges, ku, vu = pkg.raster.tile_bin(cam, rec, radii, cum, M)
+    tw, th = (W + 15) // 16, (H + 15) // 16
+    tpg, ids_ref, flat_ref, off_ref = gsref.isect(rec[:, 0:2].contiguous(), radii.contiguous(), rec[:, 10].contiguous(), tw, th)
+    torch.cuda.synchronize()
+    assert M == ids_ref.numel() > 3 * 10000
+    assert torch.equal(tpg.to(torch.int32), tiles), "tiles_per_gauss"
+    assert torch.equal(ids_ref, ks), "sorted (tile | depth) keys"
+    assert torch.equal(flat_ref.to(torch.int32), vs), "sorted Gaussian ids"
+    assert torch.equal(off_ref.reshape(-1).to(torch.int32), ranges[:-1]), "tile offsets"
+    assert int(ranges[-1]) == M
