@@ -136,6 +136,11 @@ int isogs_blend_fwd(const isogs_camera* cam, int ch, const float* rec, const int
                     const int32_t* tile_ranges, float* render, float* alpha, int32_t* last,
                     void* stream);
 
+/* Diagnostic: the blend kernels fill their per-tile ring with bulk asynchronous copies that complete on mbarriers; every
+ * wait is bounded (about a second), so a protocol error can not hang a GPU.  Returns the number of waits that timed out
+ * since the last call (0 in a healthy run) and resets the counter.  Synchronises the device. */
+unsigned int isogs_debug_blend_timeouts(void);
+
 /* ---- rasterizer backward --------------------------------------------------------------- */
 
 /* renderCUDA backward: replaces rasterize_to_pixels_3dgs_bwd (Ops.h:239-264;

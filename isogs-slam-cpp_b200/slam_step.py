@@ -177,6 +177,7 @@ class StepWorkspace:
         self.cur_frame = torch.zeros((C.sizeof(_lib.Frame),), dtype=torch.uint8, device=device)
         self._frames = {}
         self._graphs = {}
+        self._cap_stream = None
         self._cws = None
 
     def c_struct(self):
@@ -464,19 +465,24 @@ def _event_array(marks):
 
 
 def _graph_launch(ws, key, enqueue):
-    """Replay the captured launch sequence for `key`, capturing it on first use (capture does not execute)."""
-    L, st = lib(), _stream()
+    """Replay the captured launch sequence for `key`, capturing it on first use (capture does not execute).
+    `enqueue(stream)` issues the work.  Capture happens on a private side stream (the legacy default stream cannot
+    capture); the replay is launched on the caller's current stream."""
+    L = lib()
     ge = ws._graphs.get(key)
     if ge is None:
-        check(L.isogs_graph_begin(st))
+        if ws._cap_stream is None:
+            ws._cap_stream = torch.cuda.Stream(device=ws.device)
+        cs = C.c_void_p(ws._cap_stream.cuda_stream)
+        check(L.isogs_graph_begin(cs))
         try:
-            enqueue()
+            enqueue(cs)
         finally:
             h = C.c_void_p()
-            rc = L.isogs_graph_end(st, C.byref(h))
+            rc = L.isogs_graph_end(cs, C.byref(h))
         check(rc)
         ge = ws._graphs[key] = h
-    check(L.isogs_graph_launch(ge, st))
+    check(L.isogs_graph_launch(ge, _stream()))
 
 
 def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, allreduce=None, marks=None, w_im=0.5,
@@ -505,8 +511,8 @@ def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, all
         fr = ws.cur_frame.data_ptr()
         key = ("map", flags, split, id(gmap), gmap.count, gmap.grad_flat.data_ptr(), tuple(lr5), w_im, w_depth, eps)
         p1 = _params(flags, _lib.PHASE_RENDER if split else _lib.PHASE_RENDER | _lib.PHASE_ADAM, w_im, w_depth, 0.99, lr5, eps)
-        _graph_launch(ws, key, lambda: check(L.isogs_map_step(C.byref(ws.cam), fr, C.byref(cws), C.byref(cgs),
-                                                              C.byref(p1), None, st)))
+        _graph_launch(ws, key, lambda cs: check(L.isogs_map_step(C.byref(ws.cam), fr, C.byref(cws), C.byref(cgs),
+                                                                 C.byref(p1), None, cs)))
     else:
         p1 = _params(flags, _lib.PHASE_RENDER if split else _lib.PHASE_RENDER | _lib.PHASE_ADAM, w_im, w_depth, 0.99, lr5, eps)
         check(L.isogs_map_step(C.byref(ws.cam), frame.data_ptr(), C.byref(cws), C.byref(cgs), C.byref(p1), ev, st))
@@ -520,8 +526,8 @@ def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, all
         p2 = _params(flags, _lib.PHASE_ADAM, w_im, w_depth, 0.99, lr5, eps)
         if graph and marks is None:
             key2 = ("adam", id(gmap), gmap.count, gmap.grad_flat.data_ptr(), tuple(lr5), eps)
-            _graph_launch(ws, key2, lambda: check(L.isogs_map_step(C.byref(ws.cam), ws.cur_frame.data_ptr(), C.byref(cws),
-                                                                   C.byref(cgs), C.byref(p2), None, st)))
+            _graph_launch(ws, key2, lambda cs: check(L.isogs_map_step(C.byref(ws.cam), ws.cur_frame.data_ptr(),
+                                                                      C.byref(cws), C.byref(cgs), C.byref(p2), None, cs)))
         else:
             check(L.isogs_map_step(C.byref(ws.cam), frame.data_ptr(), C.byref(cws), C.byref(cgs), C.byref(p2), ev, st))
             if marks is not None:                  # keep the stage order: the Adam mark goes last
@@ -798,8 +804,8 @@ def track_step(ws, gmap, ps, gt_rgb, gt_depth, lrs=TRACKING_LRS, eps=1e-8, use_s
         ws.cur_frame.copy_(frame, non_blocking=True)
         fr = ws.cur_frame.data_ptr()
         key = ("track", flags, id(gmap), gmap.count, ps.pose.data_ptr(), float(sil_thres), tuple(prm.lr), eps)
-        _graph_launch(ws, key, lambda: check(L.isogs_track_step(C.byref(ws.cam), fr, C.byref(cws), C.byref(cgs), *args,
-                                                                C.byref(prm), None, st)))
+        _graph_launch(ws, key, lambda cs: check(L.isogs_track_step(C.byref(ws.cam), fr, C.byref(cws), C.byref(cgs), *args,
+                                                                   C.byref(prm), None, cs)))
     else:
         check(L.isogs_track_step(C.byref(ws.cam), frame.data_ptr(), C.byref(cws), C.byref(cgs), *args, C.byref(prm),
                                  _event_array(marks), st))
