@@ -303,7 +303,19 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps, marks_list=None, first=0):
+    init_p = {k: gmap.p[k][:gmap.count].clone() for k in ss.PARAM_ORDER}
+
+    def restore(g=None, init=None):
+        """Every timed block starts from the SAME map (the initial one) with a fresh optimizer, as every mapping call
+        of the reference does (splatam.py:1406): thousands of back-to-back Adam steps would otherwise let the scene
+        drift (larger splats, more tile intersections) and later blocks / legs would time a different workload."""
+        g, init = g or gmap, init or init_p
+        for k in ss.PARAM_ORDER:
+            g.p[k][:g.count].copy_(init[k])
+        g.reset_optimizer()
+
+    def timed(fn, steps, marks_list=None, first=0, reset=None):
+        (reset or restore)()
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -323,12 +335,12 @@ def run_ours(args):
             ms = float(t.item())
         return ms
 
-    def timed_blocks(fn, steps, min_s=MIN_TIMED_S, max_blocks=4000):
+    def timed_blocks(fn, steps, min_s=MIN_TIMED_S, max_blocks=4000, reset=None):
         """Blocks of exactly `steps` steps until min_s of device time is covered; every rank derives the same block
-        count from the max-over-ranks time of the first block."""
-        first = timed(fn, steps)
+        count from the max-over-ranks time of the first block.  Every block starts from the initial map."""
+        first = timed(fn, steps, reset=reset)
         n_more = int(min(max_blocks, max(0, np.ceil(min_s * 1e3 / max(first, 1e-3)) - 1)))
-        blocks = [first] + [timed(fn, steps, first=(b + 1) * steps) for b in range(n_more)]
+        blocks = [first] + [timed(fn, steps, first=(b + 1) * steps, reset=reset) for b in range(n_more)]
         return blocks
 
     barrier()                                      # ranks leave the (CPU-side) workload build seconds apart
@@ -350,6 +362,7 @@ def run_ours(args):
             ar.release()
             ar = dp.allreduce_mean_
             gmap = ss.GaussianMap(params, device=dev)
+            init_p = {k: gmap.p[k][:gmap.count].clone() for k in ss.PARAM_ORDER}
             barrier()
             for i in range(max(3, args.warmup)):
                 step_resident(i)
@@ -424,6 +437,8 @@ def run_ours(args):
         p3["log_scales"] = (np.tile(np.asarray(params["log_scales"]).reshape(-1, 1), (1, 3)) +
                             0.01 * rs.randn(gmap.count, 3)).astype(np.float32)
         gmap3 = ss.GaussianMap(p3, device=dev)
+        init3 = {k: gmap3.p[k][:gmap3.count].clone() for k in ss.PARAM_ORDER}
+        reset3 = lambda: restore(gmap3, init3)
 
         def step_full(i, marks=None):
             k = kfs[i % WINDOW]
@@ -431,10 +446,10 @@ def run_ours(args):
                                isoflat=True, iso_seed=i, graph=use_graph)
         for i in range(3):
             step_full(i)
-        fb = timed_blocks(step_full, args.steps, 0.3)
+        fb = timed_blocks(step_full, args.steps, 0.3, reset=reset3)
         extras["mapping_full_loss_3axis_iters_per_s"] = args.steps / (float(np.median(fb)) * 1e-3)
         full_marks = []
-        timed(step_full, args.steps, full_marks)
+        timed(step_full, args.steps, full_marks, reset=reset3)
         tot = 0.0
         for m in full_marks:
             names = [n for n, _ in m]

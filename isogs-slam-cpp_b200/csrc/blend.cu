@@ -559,9 +559,9 @@ int launch_blend_bwd_lq(const DevCam& dc, int ch, int nw, bool geom, bool vec, b
                         const float* v_alpha, float* v_rec, cudaStream_t stream); // blend_lq.cu
 int launch_blend_fwd_lq(const DevCam& dc, int ch, int nw, const float* rec, const int32_t* vals, const int32_t* ranges,
                         float* render, float* alpha, int32_t* last, cudaStream_t stream);
-int launch_blend_fwd_ts(const DevCam& dc, int ch, const float* rec, const int32_t* vals, const int32_t* ranges, float* render,
+int launch_blend_fwd_ts(const DevCam& dc, int ch, bool bulk, const float* rec, const int32_t* vals, const int32_t* ranges, float* render,
                         float* alpha, int32_t* last, cudaStream_t stream); // blend_ts.cu
-int launch_blend_bwd_ts(const DevCam& dc, int ch, bool geom, const float* rec, const int32_t* vals, const int32_t* ranges,
+int launch_blend_bwd_ts(const DevCam& dc, int ch, bool geom, bool bulk, const float* rec, const int32_t* vals, const int32_t* ranges,
                         const float* alpha, const int32_t* last, const float* v_render, const float* v_alpha, float* v_rec,
                         cudaStream_t stream);
 }
@@ -589,7 +589,8 @@ extern "C" int isogs_blend_fwd(const isogs_camera* cam, int ch, const float* rec
     // quad-of-lanes kernel above (ring of 4 words), kept as the A/B baseline
     // default: the tile-shared-ring lane-per-quad kernel of blend_ts.cu; ISOGS_TS=0 falls back to the families below
     static const int cqsel = env_int("ISOGS_TS", 1);
-    if (cqsel) return launch_blend_fwd_ts(dc, ch, rec, vals_sorted, tile_ranges, render, alpha, last, stream);
+    static const int bulk = env_int("ISOGS_TS_BULK", 0);
+    if (cqsel) return launch_blend_fwd_ts(dc, ch, bulk != 0, rec, vals_sorted, tile_ranges, render, alpha, last, stream);
     static const int lq = env_int("ISOGS_FWD_LQ", 1);
     static const int nw = env_nw("ISOGS_NW_FWD", lq ? NW_LQ : NW_FWD); // ring words per warp (tuning knob)
     if (lq) return launch_blend_fwd_lq(dc, ch, nw, rec, vals_sorted, tile_ranges, render, alpha, last, stream);
@@ -610,7 +611,8 @@ extern "C" int isogs_blend_bwd(const isogs_camera* cam, int ch, int64_t N, const
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
     static const int cqsel = env_int("ISOGS_TS", 1);
-    if (cqsel) return launch_blend_bwd_ts(dc, ch, false, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
+    static const int bulk = env_int("ISOGS_TS_BULK", 0);
+    if (cqsel) return launch_blend_bwd_ts(dc, ch, false, bulk != 0, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
     static const int lq = env_int("ISOGS_BWD_LQ", 1); // 1: lane-per-quad kernel (blend_lq.cu), 2: same with scalar REDs, 0: quad-of-lanes kernel
     static const int nw = env_nw("ISOGS_NW_BWD", lq ? NW_LQ : NW_BWD);
     if (lq) return launch_blend_bwd_lq(dc, ch, nw, false, lq != 2, lq == 3, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
@@ -633,7 +635,8 @@ extern "C" int isogs_blend_bwd_geom(const isogs_camera* cam, int ch, int64_t N, 
     if (((uintptr_t)rec | (uintptr_t)v_rec) & 15) { set_error("isogs_blend_bwd_geom: rec and v_rec must be 16-byte aligned"); return ISOGS_E_ARG; }
     DevCam dc = make_devcam(*cam);
     static const int cqsel = env_int("ISOGS_TS", 1);
-    if (cqsel) return launch_blend_bwd_ts(dc, ch, true, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
+    static const int bulk = env_int("ISOGS_TS_BULK", 0);
+    if (cqsel) return launch_blend_bwd_ts(dc, ch, true, bulk != 0, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
     static const int lq = env_int("ISOGS_BWD_LQ", 1);
     if (lq) return launch_blend_bwd_lq(dc, ch, env_nw("ISOGS_NW_BWD", NW_LQ), true, true, lq == 3, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);
     if (ch == 4) return launch_bwd<4, 4, true>(dc, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream);

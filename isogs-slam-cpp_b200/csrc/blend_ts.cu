@@ -110,13 +110,20 @@ __device__ __forceinline__ int ld_volatile_shared(const int* p) {
 __device__ __forceinline__ void st_volatile_shared(int* p, int v) {
     asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
 }
-// one warp-uniform value of a shared word another warp updates (lane 0 reads, acquire fence, broadcast)
+// one warp-uniform value of a shared word another warp updates (lane 0 reads, broadcast).  No fence: what is ordered
+// against it is either an mbarrier wait (its own acquire) or a write into a slot whose last readers have CONSUMED
+// the values they loaded before they published their base (see publish_base).
 __device__ __forceinline__ int peek(const int* p, int lane) {
     int v = 0;
-    if (lane == 0) { v = ld_volatile_shared(p); __threadfence_block(); }
-    v = __shfl_sync(FULL, v, 0);
-    __syncwarp(); // memory ordering for the lanes that did not read the word themselves
-    return v;
+    if (lane == 0) v = ld_volatile_shared(p);
+    return __shfl_sync(FULL, v, 0);
+}
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
+// the barrier receives one (pre-counted) arrival when all cp.async of this thread issued so far have landed
+__device__ __forceinline__ void cp_async_arrive_noinc(void* bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void note_timeout(int lane) {
     if (lane == 0) atomicAdd(&g_timeouts, 1u);
@@ -132,25 +139,37 @@ __device__ __forceinline__ int load_id(int word, int first, int n_entries, const
 
 // Issue word `word` (its ids are in `id`, one per lane): every lane copies its 48-byte record into the ring with one
 // bulk asynchronous copy that completes on the word's mbarrier; lane 0 arms the barrier with the byte count.
-template <int NW, bool WITH_ID>
+// BULK = true: one cp.async.bulk (48 B, bulk-copy engine, completes by transaction bytes; barrier count 1);
+// BULK = false: three 16-byte cp.async per lane + cp.async.mbarrier.arrive.noinc (barrier count 32, one per lane).
+template <int NW, bool WITH_ID, bool BULK>
 __device__ __forceinline__ void issue_word(TileRing<NW, WITH_ID>& st, int word, int id, int n_entries,
                                            const float4* __restrict__ rec, int lane) {
     const unsigned slotw = (unsigned)word & (NW - 1);
     const unsigned slot = slotw * 32u + lane;
-    // the slot's previous word was read through the generic proxy (by both warps, before they published their ring
-    // base); order those reads before the asynchronous-proxy writes below
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    if (id >= 0) {
-        if (WITH_ID) st.id[slot] = id;
-        bulk_g2s(&st.rec[3 * slot], rec + 3 * (int64_t)id, 48u, &st.full[slotw]);
+    if (BULK) {
+        // the slot's previous word was read through the generic proxy; order those reads before the async-proxy writes
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        if (id >= 0) {
+            if (WITH_ID) st.id[slot] = id;
+            bulk_g2s(&st.rec[3 * slot], rec + 3 * (int64_t)id, 48u, &st.full[slotw]);
+        }
+        __syncwarp(); // the id stores of all lanes precede lane 0's (releasing) arrive
+        if (lane == 0) {
+            const int n_valid = min(32, n_entries - 32 * word);
+            mbar_arrive_expect_tx(&st.full[slotw], 48u * (uint32_t)n_valid);
+        }
+    } else {
+        if (id >= 0) {
+            if (WITH_ID) st.id[slot] = id;
+            const float4* r = rec + 3 * (int64_t)id;
+            cp_async16(&st.rec[3 * slot], r);
+            cp_async16(&st.rec[3 * slot + 1], r + 1);
+            cp_async16(&st.rec[3 * slot + 2], r + 2);
+        }
+        cp_async_arrive_noinc(&st.full[slotw]); // every lane, with or without an entry: 32 arrivals per phase
+        __syncwarp();
     }
-    __syncwarp(); // the id stores of all lanes precede lane 0's (releasing) arrive
-    if (lane == 0) {
-        const int n_valid = min(32, n_entries - 32 * word);
-        mbar_arrive_expect_tx(&st.full[slotw], 48u * (uint32_t)n_valid);
-        __threadfence_block();
-        st_volatile_shared(&st.issued, word + 1);
-    }
+    if (lane == 0) st_volatile_shared(&st.issued, word + 1);
 }
 
 // Hit masks of the 32 entries of ring word slot base `wsl` (lane L tests entry L) against the warp's 32 quads, written
@@ -196,6 +215,7 @@ struct WS {
     int base;     // this warp's ring base (published to prog[wid])
     int issued;   // warp 0: words issued so far; warp 1: the last value of the producer's counter it has seen
     int next_id;  // producer only: this lane's Gaussian id of word `issued` (prefetched)
+    int other;    // producer only: the last value of warp 1's ring base it has seen
     bool dead;    // a bounded wait timed out
 };
 
@@ -229,16 +249,18 @@ __device__ __forceinline__ bool try_publish(TileRing<NW, WITH_ID>& st, WS& s, in
 }
 
 // Producer step of warp 0: issue the next word if its slot has been retired by both warps.
-template <int NW, bool WITH_ID, int DIR>
+template <int NW, bool WITH_ID, int DIR, bool BULK>
 __device__ __forceinline__ bool try_issue(TileRing<NW, WITH_ID>& st, WS& s, int own_base, int first, int n_entries,
                                           const float4* __restrict__ rec, const int32_t* __restrict__ vals, int lane) {
     if (s.issued >= s.n_words) return false;
     if (s.issued >= NW) {
         if (s.issued - own_base >= NW) return false;
-        const int other = peek(&st.prog[1], lane); // acquire: the other warp's reads of the slot precede its base update
-        if (s.issued - other >= NW) return false;
+        if (s.issued - s.other >= NW) {          // the cached value blocks: look again
+            s.other = peek(&st.prog[1], lane);
+            if (s.issued - s.other >= NW) return false;
+        }
     }
-    issue_word<NW, WITH_ID>(st, s.issued, s.next_id, n_entries, rec, lane);
+    issue_word<NW, WITH_ID, BULK>(st, s.issued, s.next_id, n_entries, rec, lane);
     ++s.issued;
     s.next_id = load_id<DIR>(s.issued, first, n_entries, vals, lane);
     return true;
@@ -247,43 +269,42 @@ __device__ __forceinline__ bool try_issue(TileRing<NW, WITH_ID>& st, WS& s, int 
 // Retire: publish this warp's ring base (the producer recycles a slot once both warps are past it).
 template <int NW, bool WITH_ID>
 __device__ __forceinline__ void publish_base(TileRing<NW, WITH_ID>& st, int wid, int base, int lane) {
-    __syncwarp();               // every lane's reads of the retired word are done
-    if (lane == 0) {
-        __threadfence_block();  // release
-        st_volatile_shared(&st.prog[wid], base);
-    }
+    // every lane has CONSUMED (in arithmetic, in program order) what it loaded from the retired word, so those
+    // loads are complete; __syncwarp orders the lanes, the volatile store publishes
+    __syncwarp();
+    if (lane == 0) st_volatile_shared(&st.prog[wid], base);
 }
 
-// Nothing is consumable: wait until the next word's masks can be published.  Warp 0 keeps producing while it waits
-// (it must never block without feeding the ring: warp 1 may be waiting for a word that is not issued yet).
-template <int NW, bool WITH_ID, int DIR>
-__device__ __forceinline__ void publish_wait(TileRing<NW, WITH_ID>& st, WS& s, int wid, int first, int n_entries,
-                                             const float4* __restrict__ rec, const int32_t* __restrict__ vals, float bx0,
-                                             float by0, int lane) {
-    const long long t0 = clock64();
-    while (s.pub < s.n_words && s.pub - s.base < NW) {
-        if (try_publish<NW, WITH_ID>(st, s, wid, n_entries, bx0, by0, lane)) return;
-        if (wid == 0 && try_issue<NW, WITH_ID, DIR>(st, s, s.base, first, n_entries, rec, vals, lane)) continue;
-        if (s.pub < s.issued) { // issued, in flight: let the hardware suspend the warp until it lands
-            const unsigned slotw = (unsigned)s.pub & (NW - 1);
-            if (!mbar_wait_warp(&st.full[slotw], ((unsigned)s.pub / NW) & 1u)) break;
-            continue;
-        }
-        __nanosleep(32);
-        if (clock64() - t0 > WAIT_CYCLES) break;
+// One service step of the ring, called when something can have changed (a word was retired, the warp is starved, or an
+// unpublished word is inside the window): warp 0 issues at most one word, then the warp publishes its hit masks for
+// the next word if that one has landed.  Returns whether more service is pending (an unpublished word in the window).
+// A STARVED warp (nothing consumable) that could not publish backs off briefly; its waiting is bounded.
+template <int NW, bool WITH_ID, int DIR, bool BULK>
+__device__ __forceinline__ bool service(TileRing<NW, WITH_ID>& st, WS& s, int wid, bool starved, long long& t_starve,
+                                        int first, int n_entries, const float4* __restrict__ rec,
+                                        const int32_t* __restrict__ vals, float bx0, float by0, int lane) {
+    if (wid == 0) try_issue<NW, WITH_ID, DIR, BULK>(st, s, s.base, first, n_entries, rec, vals, lane);
+    const bool published = try_publish<NW, WITH_ID>(st, s, wid, n_entries, bx0, by0, lane);
+    if (starved && !published) {
+        const long long now = clock64();
+        if (t_starve == 0) t_starve = now;
+        else if (now - t_starve > WAIT_CYCLES) { s.dead = true; note_timeout(lane); }
+        __nanosleep(20);
+    } else {
+        t_starve = 0;
     }
-    if (s.pub < s.n_words && s.pub - s.base < NW) { s.dead = true; note_timeout(lane); }
+    return s.pub < s.n_words && s.pub - s.base < NW;
 }
 
 // After its own walk, warp 0 keeps the ring fed until warp 1 is finished, then waits for every copy it issued (the
 // CTA's shared memory must not be released with bulk copies in flight).
-template <int NW, bool WITH_ID, int DIR>
+template <int NW, bool WITH_ID, int DIR, bool BULK>
 __device__ __forceinline__ void producer_tail(TileRing<NW, WITH_ID>& st, WS& s, int first, int n_entries,
                                               const float4* __restrict__ rec, const int32_t* __restrict__ vals, int lane) {
     const long long t0 = clock64();
     while (s.issued < s.n_words && !s.dead) {
         if (peek(&st.prog[1], lane) == FIN) break;
-        if (try_issue<NW, WITH_ID, DIR>(st, s, FIN, first, n_entries, rec, vals, lane)) continue;
+        if (try_issue<NW, WITH_ID, DIR, BULK>(st, s, FIN, first, n_entries, rec, vals, lane)) continue;
         __nanosleep(64);
         if (clock64() - t0 > WAIT_CYCLES) { s.dead = true; note_timeout(lane); }
     }
@@ -295,11 +316,11 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-template <int NW, bool WITH_ID>
+template <int NW, bool WITH_ID, bool BULK>
 __device__ __forceinline__ void ring_init(TileRing<NW, WITH_ID>& st) {
     if (threadIdx.x == 0) {
 #pragma unroll
-        for (int i = 0; i < NW; ++i) mbar_init(&st.full[i], 1u);
+        for (int i = 0; i < NW; ++i) mbar_init(&st.full[i], BULK ? 1u : 32u);
         st.prog[0] = 0;
         st.prog[1] = 0;
         st.issued = 0;
@@ -308,7 +329,7 @@ __device__ __forceinline__ void ring_init(TileRing<NW, WITH_ID>& st) {
 }
 
 // GEOM = true: tracking (only x, y, conic, z, z^2 gradients are produced).
-template <int CH, int NW, bool GEOM>
+template <int CH, int NW, bool GEOM, bool BULK>
 __global__ void __launch_bounds__(THREADS, 7)
 blend_bwd_ts_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
                     const int32_t* __restrict__ ranges, const float* __restrict__ alpha,
@@ -327,7 +348,7 @@ blend_bwd_ts_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
     const float pxa = (float)x0 + 0.5f, pxb = (float)x0 + 1.5f, pya = (float)y0 + 0.5f, pyb = (float)y0 + 1.5f;
     const int start = ranges[tile];
     const int64_t P = (int64_t)cam.width * cam.height;
-    ring_init<NW, true>(st);
+    ring_init<NW, true, BULK>(st);
 
     int first[4]; // first walk position (back to front from the TILE's last contributor) that contributed to pixel p
     float T[4], bdot[4], va_eff[4], vr[4][CH];
@@ -361,6 +382,7 @@ blend_bwd_ts_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
     s.n_words = (n_entries + 31) >> 5;
     s.issued = 0;
     s.next_id = -1;
+    s.other = 0;
     s.dead = false;
     // this warp's quads only need the walk from its own last contributor on: skip the words in front of it
     const bool idle = warp_last < start;
@@ -368,7 +390,7 @@ blend_bwd_ts_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
     if (s.base > 0 || idle) publish_base<NW, true>(st, wid, idle ? FIN : s.base, lane);
     if (wid == 0) {
         s.next_id = load_id<-1>(0, tile_last, n_entries, vals, lane);
-        while (try_issue<NW, true, -1>(st, s, s.base, tile_last, n_entries, rec, vals, lane)) {}
+        while (try_issue<NW, true, -1, BULK>(st, s, s.base, tile_last, n_entries, rec, vals, lane)) {}
     }
     if (!idle) {
         const int e_first = tile_last - quad_last; // entries in front of it lie behind this quad's last contributor
@@ -380,25 +402,26 @@ blend_bwd_ts_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
             const int cut = e_first - 32 * w;
             return cut <= 0 ? m : (cut >= 32 ? 0u : (m & ~((1u << cut) - 1u)));
         };
-        publish_wait<NW, true, -1>(st, s, wid, tile_last, n_entries, rec, vals, bx0, by0, lane);
         int jq = s.base;
         unsigned wsl = ((unsigned)jq & (NW - 1)) * 32u;
-        uint32_t bits = s.pub > s.base ? fetch(jq, wsl) : 0u;
-        if (quad_last < start) { jq = FAR; bits = 0u; wsl = 0u; }
+        uint32_t bits = 0u;
+        bool fresh = true;   // the cursor's current word has not been fetched yet (it was not published)
+        bool poll = true;    // an unpublished word is inside the window
+        long long t_starve = 0;
+        if (quad_last < start) { jq = FAR; fresh = false; wsl = 0u; }
         while (!s.dead) {
-            if (bits == 0u && jq + 1 < s.pub) {
+            if (fresh) {
+                if (jq < s.pub) { bits = fetch(jq, wsl); fresh = false; }
+            } else if (bits == 0u && jq + 1 < s.pub) {
                 ++jq;
                 wsl = (wsl + 32u) & (32u * NW - 1u);
                 bits = fetch(jq, wsl);
             }
             const bool act = bits != 0u;
-            const int wmin = __reduce_min_sync(FULL, act ? jq : jq + 1);
+            const int wmin = __reduce_min_sync(FULL, fresh ? jq : (act ? jq : jq + 1));
             if (wmin >= s.n_words) break;
-            if (wmin >= s.pub) { // nothing consumable: wait for the next word (warp 0 keeps the ring fed meanwhile)
-                if (wmin > s.base && s.base < s.pub) { ++s.base; publish_base<NW, true>(st, wid, s.base, lane); }
-                publish_wait<NW, true, -1>(st, s, wid, tile_last, n_entries, rec, vals, bx0, by0, lane);
-                continue;
-            }
+            const bool starved = wmin >= s.pub; // nothing consumable
+            if (!starved) {
             const int sb = act ? __ffs(bits) - 1 : 0;
             bits &= bits - 1u;
             const unsigned slot = wsl + sb;
@@ -474,18 +497,20 @@ blend_bwd_ts_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                     }
                 }
             }
-            if (wmin > s.base) { ++s.base; publish_base<NW, true>(st, wid, s.base, lane); }
-            if (wid == 0) try_issue<NW, true, -1>(st, s, s.base, tile_last, n_entries, rec, vals, lane);
-            try_publish<NW, true>(st, s, wid, n_entries, bx0, by0, lane);
+            } // !starved
+            bool retired = false;
+            if (wmin > s.base && s.base < s.pub) { ++s.base; publish_base<NW, true>(st, wid, s.base, lane); retired = true; }
+            if (starved || retired || poll)
+                poll = service<NW, true, -1, BULK>(st, s, wid, starved, t_starve, tile_last, n_entries, rec, vals, bx0, by0, lane);
         }
         publish_base<NW, true>(st, wid, FIN, lane);
     }
-    if (wid == 0) producer_tail<NW, true, -1>(st, s, tile_last, n_entries, rec, vals, lane);
+    if (wid == 0) producer_tail<NW, true, -1, BULK>(st, s, tile_last, n_entries, rec, vals, lane);
 }
 
 // Forward, same organisation.  Reference: gsplat RasterizeToPixels3DGSFwd.cu:17-188.  The per-pixel body is
 // predicated, not branched; the contribute / saturate decisions are those of blend_lq.cu::blend_fwd_lq_kernel.
-template <int CH, int NW>
+template <int CH, int NW, bool BULK>
 __global__ void __launch_bounds__(THREADS, 7)
 blend_fwd_ts_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
                     const int32_t* __restrict__ ranges, float* __restrict__ render, float* __restrict__ alpha,
@@ -502,7 +527,7 @@ blend_fwd_ts_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
     const float pxa = (float)x0 + 0.5f, pxb = (float)x0 + 1.5f, pya = (float)y0 + 0.5f, pyb = (float)y0 + 1.5f;
     const int start = ranges[tile], end = ranges[tile + 1];
     const int n_entries = end - start;
-    ring_init<NW, false>(st);
+    ring_init<NW, false, BULK>(st);
 
     float T[4], acc[4][CH];
     int last_idx[4];
@@ -523,35 +548,37 @@ blend_fwd_ts_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
         s.n_words = (n_entries + 31) >> 5;
         s.issued = 0;
         s.next_id = -1;
+        s.other = 0;
         s.dead = false;
         s.base = s.pub = 0;
         const bool idle = __all_sync(FULL, quad_done); // half tile entirely outside the image
         if (idle) publish_base<NW, false>(st, wid, FIN, lane);
         if (wid == 0) {
             s.next_id = load_id<1>(0, start, n_entries, vals, lane);
-            while (try_issue<NW, false, 1>(st, s, s.base, start, n_entries, rec, vals, lane)) {}
+            while (try_issue<NW, false, 1, BULK>(st, s, s.base, start, n_entries, rec, vals, lane)) {}
         }
         if (!idle) {
             const uint32_t* hq = st.hits[wid] + lane;
-            publish_wait<NW, false, 1>(st, s, wid, start, n_entries, rec, vals, bx0, by0, lane);
             int jq = 0;
             unsigned wsl = 0u;
-            uint32_t bits = s.pub > 0 ? hq[0] : 0u;
-            if (quad_done) { jq = FAR; bits = 0u; }
+            uint32_t bits = 0u;
+            bool fresh = true;   // the cursor's current word has not been fetched yet (it was not published)
+            bool poll = true;    // an unpublished word is inside the window
+            long long t_starve = 0;
+            if (quad_done) { jq = FAR; fresh = false; }
             while (!s.dead) {
-                if (bits == 0u && jq + 1 < s.pub) {
+                if (fresh) {
+                    if (jq < s.pub) { bits = hq[wsl]; fresh = false; }
+                } else if (bits == 0u && jq + 1 < s.pub) {
                     ++jq;
                     wsl = (wsl + 32u) & (32u * NW - 1u);
                     bits = hq[wsl];
                 }
                 const bool act = bits != 0u;
-                const int wmin = __reduce_min_sync(FULL, act ? jq : jq + 1);
+                const int wmin = __reduce_min_sync(FULL, fresh ? jq : (act ? jq : jq + 1));
                 if (wmin >= s.n_words) break; // list exhausted, or every quad saturated (FAR)
-                if (wmin >= s.pub) {
-                    if (wmin > s.base && s.base < s.pub) { ++s.base; publish_base<NW, false>(st, wid, s.base, lane); }
-                    publish_wait<NW, false, 1>(st, s, wid, start, n_entries, rec, vals, bx0, by0, lane);
-                    continue;
-                }
+                const bool starved = wmin >= s.pub;
+                if (!starved) {
                 const int sb = act ? __ffs(bits) - 1 : 0;
                 bits &= bits - 1u;
                 const unsigned slot = wsl + sb;
@@ -594,13 +621,15 @@ blend_fwd_ts_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                     }
                     if (done[0] && done[1] && done[2] && done[3]) { jq = FAR; bits = 0u; } // quad saturated
                 }
-                if (wmin > s.base) { ++s.base; publish_base<NW, false>(st, wid, s.base, lane); }
-                if (wid == 0) try_issue<NW, false, 1>(st, s, s.base, start, n_entries, rec, vals, lane);
-                try_publish<NW, false>(st, s, wid, n_entries, bx0, by0, lane);
+                } // !starved
+                bool retired = false;
+                if (wmin > s.base && s.base < s.pub) { ++s.base; publish_base<NW, false>(st, wid, s.base, lane); retired = true; }
+                if (starved || retired || poll)
+                    poll = service<NW, false, 1, BULK>(st, s, wid, starved, t_starve, start, n_entries, rec, vals, bx0, by0, lane);
             }
             publish_base<NW, false>(st, wid, FIN, lane);
         }
-        if (wid == 0) producer_tail<NW, false, 1>(st, s, start, n_entries, rec, vals, lane);
+        if (wid == 0) producer_tail<NW, false, 1, BULK>(st, s, start, n_entries, rec, vals, lane);
     }
     const int64_t P = (int64_t)cam.width * cam.height;
 #pragma unroll
@@ -616,7 +645,7 @@ blend_fwd_ts_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
     }
 }
 
-template <int CH, int NW>
+template <int CH, int NW, bool BULK>
 int launch_fwd(const DevCam& dc, const float* rec, const int32_t* vals, const int32_t* ranges, float* render, float* alpha,
                int32_t* last, cudaStream_t stream) {
     constexpr size_t smem = sizeof(TileRing<NW, false>);
@@ -624,16 +653,16 @@ int launch_fwd(const DevCam& dc, const float* rec, const int32_t* vals, const in
     int dev = 0;
     ISOGS_CUDA(cudaGetDevice(&dev));
     if (attr_dev != dev) {
-        ISOGS_CUDA(cudaFuncSetAttribute(blend_fwd_ts_kernel<CH, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ISOGS_CUDA(cudaFuncSetAttribute(blend_fwd_ts_kernel<CH, NW, BULK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_dev = dev;
     }
     dim3 grid(dc.tw, dc.th);
-    blend_fwd_ts_kernel<CH, NW><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, render, alpha, last);
+    blend_fwd_ts_kernel<CH, NW, BULK><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, render, alpha, last);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
 }
 
-template <int CH, int NW, bool GEOM>
+template <int CH, int NW, bool GEOM, bool BULK>
 int launch_bwd(const DevCam& dc, const float* rec, const int32_t* vals, const int32_t* ranges, const float* alpha,
                const int32_t* last, const float* v_render, const float* v_alpha, float* v_rec, cudaStream_t stream) {
     constexpr size_t smem = sizeof(TileRing<NW, true>);
@@ -641,12 +670,12 @@ int launch_bwd(const DevCam& dc, const float* rec, const int32_t* vals, const in
     int dev = 0;
     ISOGS_CUDA(cudaGetDevice(&dev));
     if (attr_dev != dev) {
-        ISOGS_CUDA(cudaFuncSetAttribute(blend_bwd_ts_kernel<CH, NW, GEOM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        ISOGS_CUDA(cudaFuncSetAttribute(blend_bwd_ts_kernel<CH, NW, GEOM, BULK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)smem));
         attr_dev = dev;
     }
     dim3 grid(dc.tw, dc.th);
-    blend_bwd_ts_kernel<CH, NW, GEOM><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last,
+    blend_bwd_ts_kernel<CH, NW, GEOM, BULK><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last,
                                                                         v_render, v_alpha, v_rec);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
@@ -655,18 +684,24 @@ int launch_bwd(const DevCam& dc, const float* rec, const int32_t* vals, const in
 } // namespace ts
 
 // called by isogs_blend_fwd / isogs_blend_bwd / isogs_blend_bwd_geom (blend.cu)
-int launch_blend_fwd_ts(const DevCam& dc, int ch, const float* rec, const int32_t* vals, const int32_t* ranges, float* render,
-                        float* alpha, int32_t* last, cudaStream_t stream) {
-    if (ch == 4) return ts::launch_fwd<4, 16>(dc, rec, vals, ranges, render, alpha, last, stream);
-    return ts::launch_fwd<5, 16>(dc, rec, vals, ranges, render, alpha, last, stream);
+int launch_blend_fwd_ts(const DevCam& dc, int ch, bool bulk, const float* rec, const int32_t* vals, const int32_t* ranges,
+                        float* render, float* alpha, int32_t* last, cudaStream_t stream) {
+#define TSF(CHN, B) ts::launch_fwd<CHN, 16, B>(dc, rec, vals, ranges, render, alpha, last, stream)
+    if (bulk) return ch == 4 ? TSF(4, true) : TSF(5, true);
+    return ch == 4 ? TSF(4, false) : TSF(5, false);
+#undef TSF
 }
 
-int launch_blend_bwd_ts(const DevCam& dc, int ch, bool geom, const float* rec, const int32_t* vals, const int32_t* ranges,
+int launch_blend_bwd_ts(const DevCam& dc, int ch, bool geom, bool bulk, const float* rec, const int32_t* vals, const int32_t* ranges,
                         const float* alpha, const int32_t* last, const float* v_render, const float* v_alpha, float* v_rec,
                         cudaStream_t stream) {
-#define TS(CHN, G) ts::launch_bwd<CHN, 16, G>(dc, rec, vals, ranges, alpha, last, v_render, v_alpha, v_rec, stream)
-    if (geom) return ch == 4 ? TS(4, true) : TS(5, true);
-    return ch == 4 ? TS(4, false) : TS(5, false);
+#define TS(CHN, G, B) ts::launch_bwd<CHN, 16, G, B>(dc, rec, vals, ranges, alpha, last, v_render, v_alpha, v_rec, stream)
+    if (bulk) {
+        if (geom) return ch == 4 ? TS(4, true, true) : TS(5, true, true);
+        return ch == 4 ? TS(4, false, true) : TS(5, false, true);
+    }
+    if (geom) return ch == 4 ? TS(4, true, false) : TS(5, true, false);
+    return ch == 4 ? TS(4, false, false) : TS(5, false, false);
 #undef TS
 }
 

@@ -90,6 +90,53 @@ def walk(hits_per_lane, n_entries, nw, skip):
     return iters, live
 
 
+def walk_shared(hits_a, hits_b, n_entries, nw):
+    """Two warps (lists of 32 hit arrays each) over ONE ring of nw words: a word is recycled when both warps are past
+    it.  The warps are advanced in lock step (one iteration each per round).  Returns (iterations a+b, live a+b)."""
+    n_words = (n_entries + 31) >> 5
+    if n_words == 0:
+        return 0, 0
+    W = []
+    for hits in (hits_a, hits_b):
+        nh = np.array([len(h) for h in hits])
+        pad = [np.concatenate([h, [1 << 40]]) for h in hits]
+        W.append(dict(ptr=np.zeros(32, np.int64), nh=nh, pad=pad, done=nh == 0, base=0, fin=bool((nh == 0).all()),
+                      jq=np.minimum(np.array([p[0] for p in pad]) >> 5, min(nw, n_words) - 1)))
+    staged = min(nw, n_words)
+    iters = live = 0
+    FAR = 1 << 30
+    guard = 0
+    while not (W[0]["fin"] and W[1]["fin"]):
+        guard += 1
+        if guard > 100000:
+            break
+        for w in W:
+            if w["fin"]:
+                continue
+            nxt = np.array([w["pad"][l][w["ptr"][l]] for l in range(32)])
+            nxt_word = nxt >> 5
+            in_ring = nxt < staged * 32
+            cur_has = in_ring & (nxt_word == w["jq"])
+            adv = (~cur_has) & (w["jq"] + 1 < staged)
+            w["jq"] = w["jq"] + adv
+            act = in_ring & (nxt_word == w["jq"]) & ~w["done"]
+            eff = np.where(w["done"], FAR, np.where(act, w["jq"], w["jq"] + 1))
+            wmin = eff.min()
+            if wmin >= n_words:
+                w["fin"] = True
+                w["base"] = FAR
+                continue
+            iters += 1
+            live += int(act.sum())
+            w["ptr"] = w["ptr"] + act
+            w["done"] = w["done"] | (w["ptr"] >= w["nh"])
+            if wmin > w["base"]:
+                w["base"] += 1
+        base = min(W[0]["base"], W[1]["base"])
+        staged = min(n_words, max(staged, min(base + nw, n_words)))
+    return iters, live
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--shape", default="replica")
@@ -116,6 +163,30 @@ def main():
         s, e = int(ranges[t]), int(ranges[t + 1])
         if e <= s:
             continue
+        # tile-shared ring: both halves walk from the TILE's last contributor
+        blk = last[ty * 16:ty * 16 + 16, tx * 16:tx * 16 + 16]
+        tile_last = int(blk.max()) if blk.size else s - 1
+        if tile_last >= s:
+            n_t = tile_last - s + 1
+            ids_t = vals[s:tile_last + 1][::-1]
+            hh = []
+            for half in (0, 1):
+                x0, y0 = tx * 16, ty * 16 + 8 * half
+                b2 = last[y0:y0 + 8, x0:x0 + 16]
+                full = np.full((8, 16), s - 1, np.int64)
+                full[:b2.shape[0], :b2.shape[1]] = b2
+                ql = full.reshape(4, 2, 8, 2).max(axis=(1, 3)).reshape(32)
+                mt = hit_masks(rec[ids_t], x0 + 0.5, y0 + 0.5)
+                mt = mt & (np.arange(n_t)[:, None] >= (tile_last - ql)[None, :]) & (ql[None, :] >= s)
+                hh.append([np.nonzero(mt[:, q])[0] for q in range(32)])
+            for nw in (16, 24):
+                it, lv = walk_shared(hh[0], hh[1], n_t, nw)
+                key = f"tile-shared nw{nw}"
+                if key not in tot:
+                    tot[key] = [0, 0, 0]
+                tot[key][0] += it
+                tot[key][1] += lv
+                tot[key][2] += (n_t + 31) >> 5
         for half in (0, 1):
             x0, y0 = tx * 16, ty * 16 + 8 * half
             blk = last[y0:y0 + 8, x0:x0 + 16]
