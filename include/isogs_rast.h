@@ -114,6 +114,17 @@ int isogs_tile_bin(const isogs_camera* cam, int64_t N, int64_t M,
                    uint64_t* keys_sorted, int32_t* vals_sorted, int32_t* tile_ranges,
                    void* sort_temp, size_t sort_temp_bytes, void* stream);
 
+/* Same arguments and bit-identical outputs, computed by the LITERAL pipeline north_star (2) names: emit the (tile | depth)
+ * keys (intersect_tile pass 2, IntersectTile.cu:87-113), cub::DeviceRadixSort::SortPairs over the used key bits
+ * (:296-339), identifyTileRanges (:209-257).  isogs_tile_bin reaches the same result by a counting sort by tile plus a
+ * per-tile depth sort, in about half the time; this entry is the cross-check and the reference's own kernel sequence.
+ * cum must be given. */
+int isogs_tile_bin_cub(const isogs_camera* cam, int64_t N, int64_t M,
+                       const float* rec, const int32_t* radii, const int32_t* cum,
+                       uint64_t* keys_unsorted, int32_t* vals_unsorted,
+                       uint64_t* keys_sorted, int32_t* vals_sorted, int32_t* tile_ranges,
+                       void* sort_temp, size_t sort_temp_bytes, void* stream);
+
 /* Sync-free variant of isogs_tile_bin for the fused step: removes the blocking
  * `n_isects = cum[-1].item()` of gsplat Intersect.cpp:80.  The intersection count is NOT known on
  * the host; `capacity` is the size of bucket / keys_sorted / vals_sorted.  totals (DEVICE int32[2])
@@ -135,11 +146,6 @@ int isogs_tile_bin_async(const isogs_camera* cam, int64_t N, int64_t capacity,
 int isogs_blend_fwd(const isogs_camera* cam, int ch, const float* rec, const int32_t* vals_sorted,
                     const int32_t* tile_ranges, float* render, float* alpha, int32_t* last,
                     void* stream);
-
-/* Diagnostic: the blend kernels fill their per-tile ring with bulk asynchronous copies that complete on mbarriers; every
- * wait is bounded (about a second), so a protocol error can not hang a GPU.  Returns the number of waits that timed out
- * since the last call (0 in a healthy run) and resets the counter.  Synchronises the device. */
-unsigned int isogs_debug_blend_timeouts(void);
 
 /* ---- rasterizer backward --------------------------------------------------------------- */
 

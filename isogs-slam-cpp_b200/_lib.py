@@ -102,9 +102,9 @@ _SIGS = {
     "isogs_preprocess_fwd": (C.c_int, [C.POINTER(Camera), C.POINTER(Pose), _VP, _I64, _VP, _VP, _I32, _VP, _VP, _VP,
                                        _I32, _I32, _VP, _VP, _VP, _VP, _VP, _SZ, C.POINTER(_I64), _VP, _VP]),
     "isogs_tile_bin": (C.c_int, [C.POINTER(Camera), _I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
+    "isogs_tile_bin_cub": (C.c_int, [C.POINTER(Camera), _I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "isogs_tile_bin_async": (C.c_int, [C.POINTER(Camera), _I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "isogs_blend_fwd": (C.c_int, [C.POINTER(Camera), _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
-    "isogs_debug_blend_timeouts": (C.c_uint, []),
     "isogs_blend_bwd": (C.c_int, [C.POINTER(Camera), _I32, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "isogs_blend_bwd_geom": (C.c_int, [C.POINTER(Camera), _I32, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "isogs_preprocess_bwd": (C.c_int, [C.POINTER(Camera), C.POINTER(Pose), _VP, _I64, _VP, _VP, _I32, _VP, _VP, _I32,

@@ -1,9 +1,12 @@
-// blend_lq.cu -- north_star (3) forward and (4) backward alpha-blend, "lane-per-quad" kernels;
-// the default since round 1m (blend.cu keeps the four-lanes-per-quad kernels as the A/B baseline).
+// blend_lq.cu -- north_star (3) renderCUDA forward (per 16x16 tile alpha-blend of colour, depth, depth^2 and silhouette)
+// and (4) backward (reverse per-pixel traversal, vector no-return atomics): the "lane-per-quad" kernels of
+// DESIGN.md 3.1 / 3.1b, and the C entry points isogs_blend_fwd / isogs_blend_bwd / isogs_blend_bwd_geom.
 // Reference: gsplat RasterizeToPixels3DGSFwd.cu:17-188, RasterizeToPixels3DGSBwd.cu:15-278.
 //
-// Same warp-autonomous ring walk as blend.cu, but a LANE owns a whole 2x2 pixel quad (its four pixels
-// live in registers and are processed one after the other) and a warp owns a 16x8 half tile = 32 quads.
+// Warp-autonomous ring walk (no CTA barrier): a LANE owns a whole 2x2 pixel quad (its four pixels
+// live in registers and are processed one after the other) and a warp owns a 16x8 half tile = 32 quads; the warp
+// walks the tile's depth-sorted list through a private shared-memory ring of NW words x 32 staged Gaussians with
+// per-quad hit masks and independent per-quad cursors.
 // In one warp iteration every lane blends a different Gaussian (its quad's next hit) into its four
 // pixels.  Backward: the per-quad partial gradients are summed INSIDE the lane -- no shuffle reduction, no
 // select network -- and one quad's 11 gradient components leave as three 16-byte vector REDs
@@ -11,9 +14,10 @@
 // cursor / ring bookkeeping (about 45 instructions per warp iteration) is shared by up to 32 (quad, Gaussian)
 // pairs instead of 8.
 //
-// The sigma expression is the one of blend.cu / the oracle (explicit round-to-nearest intrinsics), so the
-// contribute / skip decision of every pixel, `last` and the images are the same as before.
-#include <cstdlib>
+// The file is compiled with FMA contraction ON; the sigma expression uses explicit round-to-nearest intrinsics and is the
+// one the oracle evaluates, so the contribute / skip decision of every pixel (and therefore `last`) is identical on CPU
+// and GPU.  Measured alternatives that did NOT pay off are recorded in DESIGN.md 3.1c (four lanes per quad, rings of
+// 4 words, scalar REDs, compacted rings, one 16-word ring per tile filled by cp.async.bulk / cp.async on mbarriers).
 
 #include "common.cuh"
 
@@ -21,13 +25,9 @@ namespace isogs {
 namespace lq {
 
 constexpr unsigned FULL = 0xffffffffu;
-constexpr int WARPS = 2;   // half tiles (16x8 pixels, one warp each) per tile
+constexpr int WARPS = 2;   // half tiles (16x8 pixels, one warp each) per tile = per CTA
 constexpr int THREADS = 32 * WARPS;
-// warps per CTA: 2 = one tile per CTA, 1 = one half tile per CTA (finer-grained CTA scheduling); ISOGS_LQ_WARPS
-inline int cta_warps() {
-    static const int w = [] { const char* e = getenv("ISOGS_LQ_WARPS"); const int v = e ? atoi(e) : 2; return v == 1 ? 1 : 2; }();
-    return w;
-}
+constexpr int NW_DEFAULT = 8; // ring words per warp (256 staged Gaussians, 14 KB): 7-8 CTAs per SM
 constexpr int FAR = 0x01000000;
 
 template <int NW, bool WITH_ID = true>
@@ -169,10 +169,8 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-// GEOM = true: tracking (only x, y, conic, z, z^2 gradients are produced; see blend.cu).
-// IDG = true: the ring keeps no Gaussian ids (13 KB per warp at NW = 8, so EIGHT CTAs fit an SM instead of seven);
-// the id of the entry a lane is about to blend is re-read from `vals` at the top of the iteration.
-template <int CH, int NW, bool GEOM, bool VEC, bool IDG>
+// GEOM = true: tracking -- only the gradient components the POSE depends on (x, y, conic, z, z^2) are produced.
+template <int CH, int NW, bool GEOM>
 __global__ void __launch_bounds__(THREADS, 8)
 blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
                     const int32_t* __restrict__ ranges, const float* __restrict__ alpha,
@@ -180,7 +178,7 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                     const float* __restrict__ v_alpha, float* __restrict__ v_rec) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    using R = Ring<NW, !IDG>;
+    using R = Ring<NW, true>;
     R& st = reinterpret_cast<R*>(s_raw)[wid];
     // half tile h = 2 * tile_y + half; a CTA holds blockDim.x / 32 consecutive halves of one tile column
     const int hidx = blockIdx.y * (blockDim.x >> 5) + wid, ty = hidx >> 1, half = hidx & 1;
@@ -223,7 +221,7 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
     for (int p = 0; p < 4; ++p) first[p] = warp_last - first[p];
 
     int staged = 0, base = 0; // warp-uniform: words [base, staged) are live in the ring
-    staged = initial_fill<NW, !IDG, -1>(st, warp_last, n_entries, n_words, rec, vals, bx0, by0, lane);
+    staged = initial_fill<NW, true, -1>(st, warp_last, n_entries, n_words, rec, vals, bx0, by0, lane);
     Pf pf;
     prefetch(pf, staged, warp_last, n_entries, rec, vals, lane);
     static_assert((NW & (NW - 1)) == 0, "NW must be a power of two");
@@ -252,8 +250,6 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
         const float4 g0s = st.g0[slot];
         const float4 g1s = st.g1[slot];
         const int e = act ? 32 * jq + s : -1;
-        int gid = 0;
-        if (IDG) gid = __ldg(vals + warp_last - max(e, 0));
         const float dxa = __fsub_rn(g0s.x, pxa), dxb = __fsub_rn(g0s.x, pxb);
         const float dya = __fsub_rn(g0s.y, pya), dyb = __fsub_rn(g0s.y, pyb);
         const float zxa = __fmul_rn(g0s.z, dxa), zxb = __fmul_rn(g0s.z, dxb);
@@ -312,37 +308,21 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
             if (anyv) {
                 const float ca = 2.0f * g0s.z, cb = g0s.w, cc = 2.0f * g1s.x;
                 const float v0 = fmaf(ca, Swx, cb * Swy), v1 = fmaf(cb, Swx, cc * Swy);
-                float* dst = v_rec + (int64_t)(IDG ? gid : st.id[slot]) * REC;
-                if (VEC) {
-                    red_add_v4(dst, v0, v1, 0.5f * Sxx, Sxy);
-                    if (GEOM) {
-                        atomicAdd(dst + 4, 0.5f * Syy);
-                        red_add_v4(dst + 8, 0.f, col[3], col[4], 0.f);
-                    } else {
-                        red_add_v4(dst + 4, 0.5f * Syy, Su, col[0], col[1]);
-                        red_add_v4(dst + 8, col[2], col[3], col[4], 0.f);
-                    }
-                } else {
-                    atomicAdd(dst + 0, v0);
-                    atomicAdd(dst + 1, v1);
-                    atomicAdd(dst + 2, 0.5f * Sxx);
-                    atomicAdd(dst + 3, Sxy);
+                float* dst = v_rec + (int64_t)st.id[slot] * REC;
+                red_add_v4(dst, v0, v1, 0.5f * Sxx, Sxy);
+                if (GEOM) {
                     atomicAdd(dst + 4, 0.5f * Syy);
-                    if (!GEOM) {
-                        atomicAdd(dst + 5, Su);
-                        atomicAdd(dst + 6, col[0]);
-                        atomicAdd(dst + 7, col[1]);
-                        atomicAdd(dst + 8, col[2]);
-                    }
-                    atomicAdd(dst + 9, col[3]);
-                    if (CH == 5) atomicAdd(dst + 10, col[4]);
+                    red_add_v4(dst + 8, 0.f, col[3], col[4], 0.f);
+                } else {
+                    red_add_v4(dst + 4, 0.5f * Syy, Su, col[0], col[1]);
+                    red_add_v4(dst + 8, col[2], col[3], col[4], 0.f);
                 }
             }
         }
         if (wmin > base) {
             ++base;
             if (staged < n_words) {
-                commit<NW, !IDG>(st, pf, staged, bx0, by0, lane);
+                commit<NW, true>(st, pf, staged, bx0, by0, lane);
                 ++staged;
                 prefetch(pf, staged, warp_last, n_entries, rec, vals, lane);
             }
@@ -482,58 +462,78 @@ int launch_fwd(const DevCam& dc, const float* rec, const int32_t* vals, const in
         ISOGS_CUDA(cudaFuncSetAttribute(blend_fwd_lq_kernel<CH, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_dev = dev;
     }
-    const int cw = cta_warps();
-    dim3 grid(dc.tw, dc.th * (WARPS / cw));
-    blend_fwd_lq_kernel<CH, NW><<<grid, 32 * cw, smem / WARPS * cw, stream>>>(dc, (const float4*)rec, vals, ranges, render, alpha, last);
+    dim3 grid(dc.tw, dc.th);
+    blend_fwd_lq_kernel<CH, NW><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, render, alpha, last);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
 }
 
-template <int CH, int NW, bool GEOM, bool VEC, bool IDG>
+template <int CH, int NW, bool GEOM>
 int launch(const DevCam& dc, const float* rec, const int32_t* vals, const int32_t* ranges, const float* alpha,
            const int32_t* last, const float* v_render, const float* v_alpha, float* v_rec, cudaStream_t stream) {
-    constexpr size_t smem = sizeof(Ring<NW, !IDG>) * WARPS;
+    constexpr size_t smem = sizeof(Ring<NW, true>) * WARPS;
     static thread_local int attr_dev = -1;
     int dev = 0;
     ISOGS_CUDA(cudaGetDevice(&dev));
     if (attr_dev != dev) {
-        ISOGS_CUDA(cudaFuncSetAttribute(blend_bwd_lq_kernel<CH, NW, GEOM, VEC, IDG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        ISOGS_CUDA(cudaFuncSetAttribute(blend_bwd_lq_kernel<CH, NW, GEOM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)smem));
         attr_dev = dev;
     }
-    const int cw = cta_warps();
-    dim3 grid(dc.tw, dc.th * (WARPS / cw));
-    blend_bwd_lq_kernel<CH, NW, GEOM, VEC, IDG><<<grid, 32 * cw, smem / WARPS * cw, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last,
-                                                                            v_render, v_alpha, v_rec);
+    dim3 grid(dc.tw, dc.th);
+    blend_bwd_lq_kernel<CH, NW, GEOM><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last,
+                                                                                 v_render, v_alpha, v_rec);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
 }
 
 } // namespace lq
 
-// called by isogs_blend_bwd / isogs_blend_bwd_geom (blend.cu); nw in {4, 8}
-int launch_blend_bwd_lq(const DevCam& dc, int ch, int nw, bool geom, bool vec, bool idg, const float* rec, const int32_t* vals,
-                        const int32_t* ranges, const float* alpha, const int32_t* last, const float* v_render,
-                        const float* v_alpha, float* v_rec, cudaStream_t stream) {
-#define LQ(CHN, NWN, G, V, I) lq::launch<CHN, NWN, G, V, I>(dc, rec, vals, ranges, alpha, last, v_render, v_alpha, v_rec, stream)
-#define LQ_NW(CHN, G, V, I) (nw == 8 ? LQ(CHN, 8, G, V, I) : LQ(CHN, 4, G, V, I))
-    if (!vec) return ch == 4 ? LQ_NW(4, false, false, false) : LQ_NW(5, false, false, false);
-    if (idg) {
-        if (geom) return ch == 4 ? LQ_NW(4, true, true, true) : LQ_NW(5, true, true, true);
-        return ch == 4 ? LQ_NW(4, false, true, true) : LQ_NW(5, false, true, true);
-    }
-    if (geom) return ch == 4 ? LQ_NW(4, true, true, false) : LQ_NW(5, true, true, false);
-    return ch == 4 ? LQ_NW(4, false, true, false) : LQ_NW(5, false, true, false);
-#undef LQ_NW
+} // namespace isogs
+
+using namespace isogs;
+
+extern "C" int isogs_blend_fwd(const isogs_camera* cam, int ch, const float* rec, const int32_t* vals_sorted,
+                               const int32_t* tile_ranges, float* render, float* alpha, int32_t* last,
+                               void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!cam || (ch != 4 && ch != 5)) { set_error("isogs_blend_fwd: ch must be 4 or 5"); return ISOGS_E_ARG; }
+    if ((uintptr_t)rec & 15) { set_error("isogs_blend_fwd: rec must be 16-byte aligned"); return ISOGS_E_ARG; }
+    DevCam dc = make_devcam(*cam);
+    if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
+    if (ch == 4) return lq::launch_fwd<4, lq::NW_DEFAULT>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, stream);
+    return lq::launch_fwd<5, lq::NW_DEFAULT>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, stream);
+}
+
+static int blend_bwd_entry(const char* who, bool geom, const isogs_camera* cam, int ch, const float* rec,
+                           const int32_t* vals_sorted, const int32_t* tile_ranges, const float* alpha, const int32_t* last,
+                           const float* v_render, const float* v_alpha, float* v_rec, cudaStream_t stream) {
+    if (!cam || (ch != 4 && ch != 5)) { set_error("%s: ch must be 4 or 5", who); return ISOGS_E_ARG; }
+    if (((uintptr_t)rec | (uintptr_t)v_rec) & 15) { set_error("%s: rec and v_rec must be 16-byte aligned", who); return ISOGS_E_ARG; }
+    DevCam dc = make_devcam(*cam);
+    if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
+#define LQ(CHN, G) lq::launch<CHN, lq::NW_DEFAULT, G>(dc, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream)
+    if (geom) return ch == 4 ? LQ(4, true) : LQ(5, true);
+    return ch == 4 ? LQ(4, false) : LQ(5, false);
 #undef LQ
 }
 
-int launch_blend_fwd_lq(const DevCam& dc, int ch, int nw, const float* rec, const int32_t* vals, const int32_t* ranges,
-                        float* render, float* alpha, int32_t* last, cudaStream_t stream) {
-#define LQF(CHN, NWN) lq::launch_fwd<CHN, NWN>(dc, rec, vals, ranges, render, alpha, last, stream)
-    if (ch == 4) return nw == 8 ? LQF(4, 8) : LQF(4, 4);
-    return nw == 8 ? LQF(5, 8) : LQF(5, 4);
-#undef LQF
+extern "C" int isogs_blend_bwd(const isogs_camera* cam, int ch, int64_t N, const float* rec,
+                               const int32_t* vals_sorted, const int32_t* tile_ranges, const float* alpha,
+                               const int32_t* last, const float* v_render, const float* v_alpha, float* v_rec,
+                               void* stream_) {
+    (void)N;
+    return blend_bwd_entry("isogs_blend_bwd", false, cam, ch, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha,
+                           v_rec, (cudaStream_t)stream_);
 }
 
-} // namespace isogs
+// Tracking variant: identical traversal, but only the gradient components the POSE depends on are reduced and
+// written: v_rec[0..4] (x, y, conic) and v_rec[9..10] (z, z^2); the colour / opacity slots are left untouched.
+extern "C" int isogs_blend_bwd_geom(const isogs_camera* cam, int ch, int64_t N, const float* rec,
+                                    const int32_t* vals_sorted, const int32_t* tile_ranges, const float* alpha,
+                                    const int32_t* last, const float* v_render, const float* v_alpha, float* v_rec,
+                                    void* stream_) {
+    (void)N;
+    return blend_bwd_entry("isogs_blend_bwd_geom", true, cam, ch, rec, vals_sorted, tile_ranges, alpha, last, v_render,
+                           v_alpha, v_rec, (cudaStream_t)stream_);
+}

@@ -4,8 +4,6 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
-#include <cstdlib>
-
 #include "common.cuh"
 
 namespace isogs {
@@ -494,12 +492,27 @@ extern "C" int isogs_tile_bin(const isogs_camera* cam, int64_t N, int64_t M, con
         ISOGS_CUDA(cudaMemsetAsync(tile_ranges, 0, sizeof(int32_t) * (n_tiles + 1), stream));
         return ISOGS_OK;
     }
+    return counting_bin(tw, th, N, (int32_t)M, /*clamp=*/false, rec, radii, keys_unsorted, keys_sorted, vals_sorted,
+                        tile_ranges, sort_temp, sort_temp_bytes, nullptr, stream);
+}
+
+// The LITERAL pipeline north_star (2) names -- duplicateWithKeys, a CUB radix sort of the (tile | depth) keys,
+// identifyTileRanges -- kept as an independently written cross-check of the counting-sort path (same outputs, bit
+// for bit; tests/test_gpu_parity.py) and for callers that want the reference's exact sequence of kernels.
+extern "C" int isogs_tile_bin_cub(const isogs_camera* cam, int64_t N, int64_t M, const float* rec, const int32_t* radii,
+                                  const int32_t* cum, uint64_t* keys_unsorted, int32_t* vals_unsorted,
+                                  uint64_t* keys_sorted, int32_t* vals_sorted, int32_t* tile_ranges, void* sort_temp,
+                                  size_t sort_temp_bytes, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!cam || N < 0 || M < 0 || M >= (1ll << 31) || !cum) { set_error("isogs_tile_bin_cub: bad argument"); return ISOGS_E_ARG; }
+    const int tw = (cam->width + TILE - 1) / TILE, th = (cam->height + TILE - 1) / TILE;
+    const int n_tiles = tw * th;
+    if (M == 0 || N == 0) {
+        ISOGS_CUDA(cudaMemsetAsync(tile_ranges, 0, sizeof(int32_t) * (n_tiles + 1), stream));
+        return ISOGS_OK;
+    }
     const int block = 256;
     const unsigned gN = (unsigned)((N + block - 1) / block);
-    static const bool use_cub = [] { const char* e = getenv("ISOGS_BIN"); return e && e[0] == 'c'; }();
-    if (!use_cub)
-        return counting_bin(tw, th, N, (int32_t)M, /*clamp=*/false, rec, radii, keys_unsorted, keys_sorted, vals_sorted,
-                            tile_ranges, sort_temp, sort_temp_bytes, nullptr, stream);
     emit_keys_kernel<<<gN, block, 0, stream>>>(
         tw, th, N, (const float4*)rec, (const int2*)radii, cum, keys_unsorted, vals_unsorted);
     ISOGS_CUDA(cudaGetLastError());

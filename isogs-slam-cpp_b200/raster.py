@@ -84,9 +84,10 @@ def preprocess(cam, means, scales, quats, opacities, colors, ch=4, flags=0, pose
     return rec, radii, tiles, cum, int(m.value)
 
 
-def tile_bin(cam, rec, radii, cum, M):
+def tile_bin(cam, rec, radii, cum, M, literal=False):
     """north_star (2).  Returns keys_sorted u64-as-int64 [M], vals_sorted i32 [M], ranges i32 [n_tiles+1],
-    plus the unsorted pair (for the bit-exact tests)."""
+    plus the unsorted pair (for the bit-exact tests).  literal=True runs the emit-keys + CUB radix sort + ranges
+    pipeline (isogs_tile_bin_cub) instead of the counting sort by tile."""
     N = rec.shape[0]
     dev = rec.device
     ku = torch.empty((M,), dtype=torch.int64, device=dev)
@@ -96,7 +97,8 @@ def tile_bin(cam, rec, radii, cum, M):
     ranges = torch.empty((cam.n_tiles + 1,), dtype=torch.int32, device=dev)
     _, sort_b = _lib.temp_bytes(0, M)
     tmp = torch.empty((sort_b,), dtype=torch.uint8, device=dev)
-    check(lib().isogs_tile_bin(C.byref(cam), N, M, _ptr(rec), _ptr(radii), _ptr(cum), _ptr(ku), _ptr(vu), _ptr(ks),
+    fn = lib().isogs_tile_bin_cub if literal else lib().isogs_tile_bin
+    check(fn(C.byref(cam), N, M, _ptr(rec), _ptr(radii), _ptr(cum), _ptr(ku), _ptr(vu), _ptr(ks),
                                _ptr(vs), _ptr(ranges), _ptr(tmp), sort_b, _stream()))
     return ks, vs, ranges, ku, vu
 

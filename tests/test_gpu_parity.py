@@ -175,3 +175,25 @@ def test_splatam_shaped_frame(pkg, orc, syn):
     _, _, o, render, alpha, ctx = run_both(pkg, orc, sc, 5, flags=flags, pose=(q, tr))
     assert_forward_parity(o, render, alpha, ctx)
     assert alpha.mean().item() > 0.8
+
+
+@pytest.mark.parametrize("n,W,H", [(6000, 200, 136), (60000, 48, 32)])
+def test_literal_cub_binning_equals_counting_sort(pkg, orc, n, W, H):
+    """isogs_tile_bin_cub -- the literal duplicateWithKeys + cub::DeviceRadixSort + identifyTileRanges pipeline that
+    north_star (2) names -- against the default counting-sort path AND the oracle: unsorted keys, sorted keys, values
+    and ranges all bit-identical (incl. tiles with > 8192 intersections)."""
+    sc = random_scene(n, W, H, 60.0 if W < 100 else 180.0, True, seed=3, big=W < 100)
+    cam = pkg.make_camera(sc["W"], sc["H"], sc["f"], sc["f"], sc["cx"], sc["cy"])
+    ocam = orc.make_camera(sc["W"], sc["H"], sc["f"], sc["f"], sc["cx"], sc["cy"])
+    rec, radii, tiles, cum, M = pkg.raster.preprocess(cam, t(sc["means"]), t(sc["scales"]), None, t(sc["opac"]),
+                                                      t(sc["cols"]), ch=4)
+    a = pkg.raster.tile_bin(cam, rec, radii, cum, M)
+    b = pkg.raster.tile_bin(cam, rec, radii, cum, M, literal=True)
+    torch.cuda.synchronize()
+    for x, y, name in zip(a[:3], b[:3], ("sorted keys", "sorted values", "ranges")):
+        assert torch.equal(x, y), name
+    orec, oradii, otiles = orc.preprocess_fwd(ocam, sc["means"], sc["scales"], None, sc["opac"], sc["cols"], ch=4)
+    ks, vs, rg, ku, vu = orc.tile_bin(ocam, orec, oradii, otiles, want_unsorted=True)
+    assert np.array_equal(b[3].cpu().numpy().view(np.uint64), ku), "unsorted keys (duplicateWithKeys emission order)"
+    assert np.array_equal(b[4].cpu().numpy(), vu)
+    assert np.array_equal(b[0].cpu().numpy().view(np.uint64), ks) and np.array_equal(b[2].cpu().numpy(), rg)
