@@ -119,6 +119,7 @@ int main(int argc, char** argv) {
     ws.totals = totals; ws.sort_temp = sort_tmp; ws.sort_temp_bytes = sort_b; ws.isect_cap = isect_cap;
     ws.render = render; ws.v_render = v_render; ws.alpha = alpha; ws.last = last; ws.small = small;
     ws.adam_state = adam_state; ws.dmaps = dmaps;
+    ws.tile_rects = dalloc<uint32_t>(4 * N);
     isogs_gaussians gs{};
     gs.N = N; gs.scale_dim = 1;
     gs.p[0] = means; gs.p[1] = cols; gs.p[2] = quats; gs.p[3] = logit; gs.p[4] = ls;

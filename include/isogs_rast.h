@@ -96,14 +96,20 @@ int isogs_temp_bytes(int64_t N, int64_t cap, size_t* scan_bytes, size_t* sort_by
  * tiles and cum may both be null (then n_isects_host must be null too): the sync-free pipeline
  * (isogs_tile_bin_async) counts intersections per tile itself and needs neither.
  * v_rec_zero (nullable, [N,12], 16-byte aligned): rows are cleared by the same kernel -- the gradient record
- * that isogs_blend_bwd accumulates into, so the step needs no separate memset launch. */
+ * that isogs_blend_bwd accumulates into, so the step needs no separate memset launch.
+ * tile_rects (nullable, [N,4] u32, 16-byte aligned): {x0 | x1 << 16, y0 | y1 << 16, depth bits, 0} -- the tile rect of
+ * intersect_tile (IntersectTile.cu:66-77; empty for a culled splat) and the key's depth bits, so that the binning
+ * kernels stream 16 bytes per Gaussian.  tile_counts (nullable, DEVICE int32[n_tiles], ZEROED by the caller): the
+ * per-tile intersection counts are accumulated by the same kernel (CTA-private shared-memory bins, one global
+ * atomic per touched tile) -- hand both to isogs_tile_bin_async with counts_ready = 1. */
 int isogs_preprocess_fwd(const isogs_camera* cam, const isogs_pose* pose, const float* pose_dev,
                          int64_t N, const float* means, const float* scales, int scale_dim,
                          const float* quats, const float* opacities, const float* colors,
                          int ch, int flags,
                          float* rec, int32_t* radii, int32_t* tiles, int32_t* cum,
                          void* scan_temp, size_t scan_temp_bytes,
-                         int64_t* n_isects_host, float* v_rec_zero, void* stream);
+                         int64_t* n_isects_host, float* v_rec_zero, uint32_t* tile_rects, int32_t* tile_counts,
+                         void* stream);
 
 /* duplicateWithKeys + radix sort + identifyTileRanges: replaces gsplat intersect_tile pass 2,
  * radix_sort_double_buffer and intersect_offset (Ops.h:186-204; IntersectTile.cu:87-113,
@@ -133,12 +139,15 @@ int isogs_tile_bin_cub(const isogs_camera* cam, int64_t N, int64_t M,
  * clears it (while it is set totals[0] keeps the largest count seen); hand `totals + 1` to isogs_adam_fused /
  * isogs_pose_keep_best as skip_flag so the affected steps update nothing, and clear it on the host after
  * growing the buffers.  bucket [capacity] u64 is scratch; keys_sorted may be null.  Output order is
- * bit-identical to isogs_tile_bin. */
+ * bit-identical to isogs_tile_bin.  tile_rects (nullable): the rows isogs_preprocess_fwd wrote (else the rects are
+ * re-derived from rec / radii); counts_ready = 1: the first n_tiles ints of sort_temp already hold the per-tile
+ * counts (isogs_preprocess_fwd's tile_counts pointed there), so the count pass is skipped. */
 int isogs_tile_bin_async(const isogs_camera* cam, int64_t N, int64_t capacity,
                          const float* rec, const int32_t* radii,
                          uint64_t* bucket, uint64_t* keys_sorted /*nullable*/, int32_t* vals_sorted,
                          int32_t* tile_ranges, int32_t* totals,
-                         void* sort_temp, size_t sort_temp_bytes, void* stream);
+                         void* sort_temp, size_t sort_temp_bytes,
+                         const uint32_t* tile_rects /*nullable*/, int counts_ready, void* stream);
 
 /* renderCUDA forward: replaces rasterize_to_pixels_3dgs_fwd (Ops.h:223-238;
  * RasterizeToPixels3DGSFwd.cu:17-188).  render [ch,H,W] planar (the Inria API's CHW),
@@ -381,6 +390,7 @@ typedef struct isogs_workspace {
     float* median_scratch; /* [2,H,W]  (nullable unless ISOGS_STEP_OUTLIER) */
     void* median_temp;
     size_t median_temp_bytes;
+    uint32_t* tile_rects;  /* [n_cap,4] u32 tile rect + depth bits per Gaussian (nullable: slower binning) */
 } isogs_workspace;
 
 #define ISOGS_STEP_SSIM 1     /* colour term 0.8*L1 + 0.2*(1-SSIM) (splatam.py:568) instead of pure L1 */

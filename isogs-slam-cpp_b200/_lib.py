@@ -63,7 +63,7 @@ class Workspace(C.Structure):
                 ("sort_temp_bytes", C.c_size_t), ("isect_cap", C.c_int64), ("render", C.c_void_p),
                 ("v_render", C.c_void_p), ("alpha", C.c_void_p), ("last", C.c_void_p), ("small", C.c_void_p),
                 ("adam_state", C.c_void_p), ("dmaps", C.c_void_p), ("median_scratch", C.c_void_p),
-                ("median_temp", C.c_void_p), ("median_temp_bytes", C.c_size_t)]
+                ("median_temp", C.c_void_p), ("median_temp_bytes", C.c_size_t), ("tile_rects", C.c_void_p)]
 
 
 class StepParams(C.Structure):
@@ -100,10 +100,11 @@ _SIGS = {
     "isogs_version": (C.c_int, []),
     "isogs_temp_bytes": (C.c_int, [_I64, _I64, C.POINTER(_SZ), C.POINTER(_SZ)]),
     "isogs_preprocess_fwd": (C.c_int, [C.POINTER(Camera), C.POINTER(Pose), _VP, _I64, _VP, _VP, _I32, _VP, _VP, _VP,
-                                       _I32, _I32, _VP, _VP, _VP, _VP, _VP, _SZ, C.POINTER(_I64), _VP, _VP]),
+                                       _I32, _I32, _VP, _VP, _VP, _VP, _VP, _SZ, C.POINTER(_I64), _VP, _VP, _VP, _VP]),
     "isogs_tile_bin": (C.c_int, [C.POINTER(Camera), _I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "isogs_tile_bin_cub": (C.c_int, [C.POINTER(Camera), _I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
-    "isogs_tile_bin_async": (C.c_int, [C.POINTER(Camera), _I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
+    "isogs_tile_bin_async": (C.c_int, [C.POINTER(Camera), _I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP,
+                                       _I32, _VP]),
     "isogs_blend_fwd": (C.c_int, [C.POINTER(Camera), _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "isogs_blend_bwd": (C.c_int, [C.POINTER(Camera), _I32, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "isogs_blend_bwd_geom": (C.c_int, [C.POINTER(Camera), _I32, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),

@@ -54,12 +54,21 @@ int check_common(const isogs_camera* cam, const isogs_frame* frame, const isogs_
 int forward(const isogs_camera* cam, const float* pose_dev, const isogs_workspace* ws, const isogs_gaussians* gs,
             void* const* ev, cudaStream_t st) {
     const float* quats = gs->scale_dim == 3 ? gs->p[2] : nullptr;
+    // with the rect rows available the per-tile counts are accumulated by the projection kernel itself: the counters
+    // (the head of sort_temp, where the binning keeps them) are cleared first
+    const bool fused_count = ws->tile_rects != nullptr && gs->N > 0;
+    const int n_tiles = ((cam->width + ISOGS_TILE - 1) / ISOGS_TILE) * ((cam->height + ISOGS_TILE - 1) / ISOGS_TILE);
+    if (fused_count) {
+        if (sizeof(int32_t) * (size_t)(n_tiles + 1) > ws->sort_temp_bytes) { set_error("sort temp too small for %d tiles", n_tiles); return ISOGS_E_ARG; }
+        ISOGS_CUDA(cudaMemsetAsync(ws->sort_temp, 0, sizeof(int32_t) * (size_t)(n_tiles + 1), st));
+    }
     ISOGS_TRY(isogs_preprocess_fwd(cam, nullptr, pose_dev, gs->N, gs->p[0], gs->p[4], gs->scale_dim, quats, gs->p[3],
                                    gs->p[1], 5, FLAGS_RAW, ws->rec, ws->radii, nullptr, nullptr, nullptr, 0, nullptr,
-                                   ws->v_rec, st));
+                                   ws->v_rec, ws->tile_rects, fused_count ? (int32_t*)ws->sort_temp : nullptr, st));
     ISOGS_TRY(mark(ev, 1, st));
     ISOGS_TRY(isogs_tile_bin_async(cam, gs->N, ws->isect_cap, ws->rec, ws->radii, ws->bucket, nullptr, ws->vals,
-                                   ws->ranges, ws->totals, ws->sort_temp, ws->sort_temp_bytes, st));
+                                   ws->ranges, ws->totals, ws->sort_temp, ws->sort_temp_bytes, ws->tile_rects,
+                                   fused_count ? 1 : 0, st));
     ISOGS_TRY(mark(ev, 2, st));
     ISOGS_TRY(isogs_blend_fwd(cam, 5, ws->rec, ws->vals, ws->ranges, ws->render, ws->alpha, ws->last, st));
     ISOGS_TRY(mark(ev, 3, st));

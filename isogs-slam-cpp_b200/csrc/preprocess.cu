@@ -13,9 +13,19 @@ preprocess_fwd_kernel(DevCam cam, DevPose pose, int64_t N, const float* __restri
                       const float* __restrict__ scales, const float* __restrict__ quats,
                       const float* __restrict__ opacities, const float* __restrict__ colors, int ch, int flags,
                       float4* __restrict__ rec, int2* __restrict__ radii, int32_t* __restrict__ tiles,
-                      float4* __restrict__ v_rec_zero) {
+                      float4* __restrict__ v_rec_zero, uint4* __restrict__ tile_rects, int32_t* __restrict__ tile_counts,
+                      int n_bins) {
+    // fused tile count (intersect_tile pass 1 + the histogram of the counting sort): CTA-private bins in shared
+    // memory, ONE global atomic per (CTA, touched tile); n_bins = 0: no shared bins (more tiles than fit)
+    extern __shared__ int32_t s_bins[];
+    if (tile_counts != nullptr && n_bins > 0) {
+        for (int b = threadIdx.x; b < n_bins; b += blockDim.x) s_bins[b] = 0;
+        __syncthreads();
+    }
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= N) return;
+    Rect tr = {0, 0, 0, 0};
+    uint32_t depth_bits = 0u;
+    if (i < N) {
     if (v_rec_zero != nullptr) { // the gradient record the blend backward accumulates into (saves a memset launch)
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         v_rec_zero[3 * i] = z; v_rec_zero[3 * i + 1] = z; v_rec_zero[3 * i + 2] = z;
@@ -42,17 +52,38 @@ preprocess_fwd_kernel(DevCam cam, DevPose pose, int64_t N, const float* __restri
         r[2] = make_float4(0.f, 0.f, 0.f, 0.f);
         radii[i] = make_int2(0, 0);
         if (tiles) tiles[i] = 0;
-        return;
+    } else {
+        float z = P.mc[2];
+        r[0] = make_float4(P.mx, P.my, 0.5f * P.a, P.b);
+        r[1] = make_float4(0.5f * P.c, P.L, P.opac, colors[3 * i]);
+        r[2] = make_float4(colors[3 * i + 1], colors[3 * i + 2], z, (ch == 5) ? z * z : 0.0f);
+        int rx = (int)P.rx, ry = (int)P.ry;
+        radii[i] = make_int2(rx, ry);
+        if (tiles || tile_rects || tile_counts) {
+            const Rect t = tile_rect(P.mx, P.my, rx, ry, cam.tw, cam.th);
+            if (tiles) tiles[i] = (t.y1 - t.y0) * (t.x1 - t.x0);
+            if (rx > 0 && ry > 0) tr = t;          // the binning kernels skip a splat unless both radii are positive
+            depth_bits = __float_as_uint(z);
+        }
     }
-    float z = P.mc[2];
-    r[0] = make_float4(P.mx, P.my, 0.5f * P.a, P.b);
-    r[1] = make_float4(0.5f * P.c, P.L, P.opac, colors[3 * i]);
-    r[2] = make_float4(colors[3 * i + 1], colors[3 * i + 2], z, (ch == 5) ? z * z : 0.0f);
-    int rx = (int)P.rx, ry = (int)P.ry;
-    radii[i] = make_int2(rx, ry);
-    if (tiles) {
-        Rect t = tile_rect(P.mx, P.my, rx, ry, cam.tw, cam.th);
-        tiles[i] = (t.y1 - t.y0) * (t.x1 - t.x0);
+    // the tile rect + depth bits, 16 bytes per Gaussian: what the binning kernels need, so they stream this array
+    // instead of gathering 28 bytes out of the 56-byte (rec, radii) rows
+    if (tile_rects) tile_rects[i] = make_uint4((uint32_t)tr.x0 | ((uint32_t)tr.x1 << 16), (uint32_t)tr.y0 | ((uint32_t)tr.y1 << 16),
+                                               depth_bits, 0u);
+    } // i < N
+    if (tile_counts != nullptr) {
+        if (n_bins > 0) {
+            for (int y = tr.y0; y < tr.y1; ++y)
+                for (int x = tr.x0; x < tr.x1; ++x) atomicAdd(s_bins + (y * cam.tw + x), 1);
+            __syncthreads();
+            for (int b = threadIdx.x; b < n_bins; b += blockDim.x) {
+                const int32_t c = s_bins[b];
+                if (c) atomicAdd(tile_counts + b, c);
+            }
+        } else {
+            for (int y = tr.y0; y < tr.y1; ++y)
+                for (int x = tr.x0; x < tr.x1; ++x) atomicAdd(tile_counts + (y * cam.tw + x), 1);
+        }
     }
 }
 
@@ -316,7 +347,7 @@ extern "C" int isogs_preprocess_fwd(const isogs_camera* cam, const isogs_pose* p
                                     const float* quats, const float* opacities, const float* colors, int ch,
                                     int flags, float* rec, int32_t* radii, int32_t* tiles, int32_t* cum,
                                     void* scan_temp, size_t scan_temp_bytes, int64_t* n_isects_host,
-                                    float* v_rec_zero, void* stream_) {
+                                    float* v_rec_zero, uint32_t* tile_rects, int32_t* tile_counts, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (!cam || N < 0 || (scale_dim != 1 && scale_dim != 3) || (ch != 4 && ch != 5) || (scale_dim == 3 && !quats)) {
         set_error("isogs_preprocess_fwd: bad argument (scale_dim=%d ch=%d)", scale_dim, ch);
@@ -327,21 +358,26 @@ extern "C" int isogs_preprocess_fwd(const isogs_camera* cam, const isogs_pose* p
         return ISOGS_OK;
     }
     if (N >= (1ll << 31)) { set_error("N too large"); return ISOGS_E_ARG; }
-    if ((((uintptr_t)rec | (uintptr_t)quats | (uintptr_t)v_rec_zero) & 15) || ((uintptr_t)radii & 7)) {
-        set_error("isogs_preprocess_fwd: rec / quats / v_rec_zero must be 16-byte aligned, radii 8-byte aligned");
+    if ((((uintptr_t)rec | (uintptr_t)quats | (uintptr_t)v_rec_zero | (uintptr_t)tile_rects) & 15) || ((uintptr_t)radii & 7)) {
+        set_error("isogs_preprocess_fwd: rec / quats / v_rec_zero / tile_rects must be 16-byte aligned, radii 8-byte aligned");
         return ISOGS_E_ARG;
     }
     DevCam dc = make_devcam(*cam);
     DevPose dp = make_devpose(pose, pose_dev);
     const int block = 256;
     const unsigned grid = (unsigned)((N + block - 1) / block);
+    const int n_tiles = dc.tw * dc.th;
+    const int n_bins = (tile_counts != nullptr && n_tiles <= 11264) ? n_tiles : 0; // 44 KB of bins: default 48 KB limit
+    const size_t smem = sizeof(int32_t) * (size_t)n_bins;
     if (scale_dim == 1)
-        preprocess_fwd_kernel<true><<<grid, block, 0, stream>>>(dc, dp, N, means, scales, quats, opacities, colors,
-                                                                 ch, flags, (float4*)rec, (int2*)radii, tiles, (float4*)v_rec_zero);
+        preprocess_fwd_kernel<true><<<grid, block, smem, stream>>>(dc, dp, N, means, scales, quats, opacities, colors,
+                                                                    ch, flags, (float4*)rec, (int2*)radii, tiles,
+                                                                    (float4*)v_rec_zero, (uint4*)tile_rects, tile_counts, n_bins);
     else
-        preprocess_fwd_kernel<false><<<grid, block, 0, stream>>>(dc, dp, N, means, scales, quats, opacities, colors,
-                                                                  ch, flags, (float4*)rec, (int2*)radii, tiles,
-                                                                  (float4*)v_rec_zero);
+        preprocess_fwd_kernel<false><<<grid, block, smem, stream>>>(dc, dp, N, means, scales, quats, opacities, colors,
+                                                                     ch, flags, (float4*)rec, (int2*)radii, tiles,
+                                                                     (float4*)v_rec_zero, (uint4*)tile_rects, tile_counts,
+                                                                     n_bins);
     ISOGS_CUDA(cudaGetLastError());
     if (!tiles || !cum) { // sync-free pipeline (isogs_tile_bin_async counts per tile itself)
         if (n_isects_host) { set_error("n_isects_host needs tiles and cum"); return ISOGS_E_ARG; }

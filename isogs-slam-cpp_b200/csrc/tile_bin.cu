@@ -1,8 +1,11 @@
 // tile_bin.cu -- north_star (2): duplicateWithKeys emits (tile | depth) 64-bit keys, a CUB onesweep
 // radix sort orders them, identifyTileRanges builds per-tile ranges.  Integer work, bit-exact
 // against the oracle.  Reference: gsplat IntersectTile.cu:87-113,296-339,209-257.
+#include <cub/block/block_merge_sort.cuh>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -218,6 +221,53 @@ tile_scatter_smem_kernel(int tw, int th, int n_tiles, int64_t N, const float4* _
     }
 }
 
+// the same scatter fed by the 16-byte (tile rect, depth bits) rows preprocess_fwd wrote: coalesced 16 B per Gaussian
+// instead of 28 B gathered out of the 56-byte (rec, radii) rows
+__global__ void __launch_bounds__(BIN_THREADS)
+tile_scatter_rect_kernel(int tw, int n_tiles, int64_t N, const uint4* __restrict__ rects,
+                         const int32_t* __restrict__ ranges, int32_t* __restrict__ cursors, uint64_t* __restrict__ bucket,
+                         int32_t capacity, int use_bins) {
+    extern __shared__ int32_t s_bins[];
+    if (use_bins) {
+        for (int b = threadIdx.x; b < n_tiles; b += BIN_THREADS) s_bins[b] = 0;
+        __syncthreads();
+    }
+    int64_t i = (int64_t)blockIdx.x * BIN_THREADS + threadIdx.x;
+    int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+    uint64_t v = 0;
+    if (i < N) {
+        const uint4 r = rects[i];
+        x0 = (int)(r.x & 0xffffu); x1 = (int)(r.x >> 16); y0 = (int)(r.y & 0xffffu); y1 = (int)(r.y >> 16);
+        v = ((uint64_t)r.z << 32) | (uint64_t)(uint32_t)i;
+    }
+    const int w = x1 - x0, ncell = w * (y1 - y0);
+    int rank[BIN_KEEP];
+    const int keep = use_bins ? BIN_KEEP : 0;
+#pragma unroll
+    for (int c = 0; c < BIN_KEEP; ++c)
+        if (c < keep && c < ncell) rank[c] = atomicAdd(s_bins + ((y0 + c / w) * tw + x0 + c % w), 1);
+    if (use_bins) {
+        __syncthreads();
+        for (int b = threadIdx.x; b < n_tiles; b += BIN_THREADS) {
+            const int32_t c = s_bins[b];
+            if (c) s_bins[b] = atomicAdd(cursors + b, c); // base of this CTA's block inside the tile bucket
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int c = 0; c < BIN_KEEP; ++c)
+        if (c < keep && c < ncell) {
+            const int t = (y0 + c / w) * tw + x0 + c % w;
+            const int slot = ranges[t] + s_bins[t] + rank[c];
+            if (slot < capacity) bucket[slot] = v;
+        }
+    for (int c = keep; c < ncell; ++c) {
+        const int t = (y0 + c / w) * tw + x0 + c % w;
+        const int slot = ranges[t] + atomicAdd(cursors + t, 1);
+        if (slot < capacity) bucket[slot] = v;
+    }
+}
+
 constexpr int SORT_SMEM_MAX = 8192; // entries per tile sorted in shared memory (64 KB)
 
 // Bitonic sorting network over n (ANY length) 64-bit values, in shared or global memory.  The
@@ -403,6 +453,47 @@ tile_sort_reg_kernel(const int32_t* __restrict__ ranges, const uint64_t* __restr
     else tile_sort_regs<8>(tile, start, n, seg, s_x, keys_sorted, vals_sorted, tid);
 }
 
+// ---- A/B candidate: the same per-tile sort by a block-wide merge sort (cub::BlockMergeSort: per-thread sort of E
+// keys, then log2(256) merge-path rounds through shared memory) instead of the 55-stage bitonic network ----------
+struct Less64 {
+    __device__ __forceinline__ bool operator()(const uint64_t& a, const uint64_t& b) const { return a < b; }
+};
+
+template <int E>
+__device__ __forceinline__ void tile_sort_merge(int tile, int start, int n, const uint64_t* __restrict__ seg, void* smem,
+                                                uint64_t* __restrict__ keys_sorted, int32_t* __restrict__ vals_sorted, int tid) {
+    using Sort = cub::BlockMergeSort<uint64_t, 256, E>;
+    uint64_t v[E];
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const int i = tid * E + r;
+        v[r] = i < n ? seg[i] : ~0ull;
+    }
+    Sort(*reinterpret_cast<typename Sort::TempStorage*>(smem)).Sort(v, Less64(), n, ~0ull);
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const int i = tid * E + r;
+        if (i < n) {
+            vals_sorted[start + i] = (int32_t)(uint32_t)v[r];
+            if (keys_sorted) keys_sorted[start + i] = ((uint64_t)tile << 32) | (v[r] >> 32);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+tile_sort_merge_kernel(const int32_t* __restrict__ ranges, const uint64_t* __restrict__ bucket,
+                       uint64_t* __restrict__ keys_sorted, int32_t* __restrict__ vals_sorted) {
+    __shared__ __align__(16) unsigned char s_tmp[sizeof(typename cub::BlockMergeSort<uint64_t, 256, 8>::TempStorage)];
+    const int tile = blockIdx.x, tid = threadIdx.x;
+    const int start = ranges[tile], n = ranges[tile + 1] - start;
+    if (n <= 0 || n > SORT_REG_MAX) return;
+    const uint64_t* seg = bucket + start;
+    if (n <= 256) tile_sort_merge<1>(tile, start, n, seg, s_tmp, keys_sorted, vals_sorted, tid);
+    else if (n <= 512) tile_sort_merge<2>(tile, start, n, seg, s_tmp, keys_sorted, vals_sorted, tid);
+    else if (n <= 1024) tile_sort_merge<4>(tile, start, n, seg, s_tmp, keys_sorted, vals_sorted, tid);
+    else tile_sort_merge<8>(tile, start, n, seg, s_tmp, keys_sorted, vals_sorted, tid);
+}
+
 inline int sort_end_bit(int n_tiles) {
     int bits = 0;
     while ((1ll << bits) <= (long long)n_tiles) ++bits; // floor(log2(n))+1, IntersectTile.cu:151
@@ -420,28 +511,33 @@ using namespace isogs;
 static int counting_bin(int tw, int th, int64_t N, int32_t capacity, bool clamp, const float* rec,
                         const int32_t* radii, uint64_t* bucket, uint64_t* keys_sorted, int32_t* vals_sorted,
                         int32_t* tile_ranges, void* sort_temp, size_t sort_temp_bytes, int32_t* totals,
-                        cudaStream_t stream) {
+                        cudaStream_t stream, const uint32_t* tile_rects = nullptr, bool counts_ready = false) {
     const int n_tiles = tw * th;
     const size_t need_scratch = sizeof(int32_t) * 3 * (size_t)(n_tiles + 1);
     if (need_scratch > sort_temp_bytes) { set_error("sort temp too small for %d tiles", n_tiles); return ISOGS_E_ARG; }
     int32_t* counts = (int32_t*)sort_temp;
     int32_t* cursors = counts + (n_tiles + 1);
     int32_t* true_ranges = cursors + (n_tiles + 1);
-    ISOGS_CUDA(cudaMemsetAsync(counts, 0, sizeof(int32_t) * (n_tiles + 1), stream));
     const int block = 256;
     const unsigned gN = (unsigned)((N + block - 1) / block);
     const bool smem_bins = n_tiles <= 11264; // 44 KB of bins fits the default 48 KB dynamic limit
     const unsigned gB = (unsigned)((N + BIN_THREADS - 1) / BIN_THREADS);
     const size_t bin_bytes = sizeof(int32_t) * (size_t)n_tiles;
-    if (smem_bins)
-        tile_count_smem_kernel<<<gB, BIN_THREADS, bin_bytes, stream>>>(tw, th, n_tiles, N, (const float4*)rec,
-                                                                       (const int2*)radii, counts);
-    else
-        tile_count_kernel<<<gN, block, 0, stream>>>(tw, th, N, (const float4*)rec, (const int2*)radii, counts);
+    if (!counts_ready) { // else: preprocess_fwd already accumulated the per-tile counts into sort_temp (fused step)
+        ISOGS_CUDA(cudaMemsetAsync(counts, 0, sizeof(int32_t) * (n_tiles + 1), stream));
+        if (smem_bins)
+            tile_count_smem_kernel<<<gB, BIN_THREADS, bin_bytes, stream>>>(tw, th, n_tiles, N, (const float4*)rec,
+                                                                           (const int2*)radii, counts);
+        else
+            tile_count_kernel<<<gN, block, 0, stream>>>(tw, th, N, (const float4*)rec, (const int2*)radii, counts);
+    }
     tile_scan_kernel<<<1, 1024, 0, stream>>>(n_tiles, counts, tile_ranges, cursors, clamp ? capacity : -1,
                                              clamp ? true_ranges : nullptr, totals);
     const int32_t* place = clamp ? true_ranges : tile_ranges;
-    if (smem_bins)
+    if (tile_rects != nullptr)
+        tile_scatter_rect_kernel<<<gB, BIN_THREADS, smem_bins ? bin_bytes : 0, stream>>>(
+            tw, n_tiles, N, (const uint4*)tile_rects, place, cursors, bucket, capacity, smem_bins ? 1 : 0);
+    else if (smem_bins)
         tile_scatter_smem_kernel<<<gB, BIN_THREADS, bin_bytes, stream>>>(tw, th, n_tiles, N, (const float4*)rec,
                                                                          (const int2*)radii, place, cursors, bucket,
                                                                          capacity);
@@ -455,7 +551,9 @@ static int counting_bin(int tw, int th, int64_t N, int32_t capacity, bool clamp,
         attr_set = true;
     }
     static_assert(SORT_REG_MAX == SORT_SMEM_SMALL, "the two sort kernels split the tiles at the same length");
-    tile_sort_reg_kernel<<<n_tiles, 256, 0, stream>>>(tile_ranges, bucket, keys_sorted, vals_sorted);
+    static const bool merge = [] { const char* e = getenv("ISOGS_SORT_MERGE"); return e && e[0] == '1'; }();   // A/B (dev)
+    if (merge) tile_sort_merge_kernel<<<n_tiles, 256, 0, stream>>>(tile_ranges, bucket, keys_sorted, vals_sorted);
+    else tile_sort_reg_kernel<<<n_tiles, 256, 0, stream>>>(tile_ranges, bucket, keys_sorted, vals_sorted);
     tile_sort_kernel<<<n_tiles, 256, SORT_SMEM_MAX * sizeof(uint64_t), stream>>>(
         SORT_SMEM_SMALL, 0x7fffffff, tile_ranges, bucket, keys_sorted, vals_sorted);
     ISOGS_CUDA(cudaGetLastError());
@@ -531,7 +629,7 @@ extern "C" int isogs_tile_bin_cub(const isogs_camera* cam, int64_t N, int64_t M,
 extern "C" int isogs_tile_bin_async(const isogs_camera* cam, int64_t N, int64_t capacity, const float* rec,
                                     const int32_t* radii, uint64_t* bucket, uint64_t* keys_sorted,
                                     int32_t* vals_sorted, int32_t* tile_ranges, int32_t* totals, void* sort_temp,
-                                    size_t sort_temp_bytes, void* stream_) {
+                                    size_t sort_temp_bytes, const uint32_t* tile_rects, int counts_ready, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (!cam || N < 0 || capacity < 0 || capacity >= (1ll << 31) || !totals) {
         set_error("isogs_tile_bin_async: bad argument");
@@ -543,6 +641,8 @@ extern "C" int isogs_tile_bin_async(const isogs_camera* cam, int64_t N, int64_t 
         ISOGS_CUDA(cudaMemsetAsync(totals, 0, sizeof(int32_t), stream)); // the sticky overflow word stays
         return ISOGS_OK;
     }
+    if (counts_ready && !tile_rects) { set_error("isogs_tile_bin_async: counts_ready needs tile_rects"); return ISOGS_E_ARG; }
+    if ((uintptr_t)tile_rects & 15) { set_error("isogs_tile_bin_async: tile_rects must be 16-byte aligned"); return ISOGS_E_ARG; }
     return counting_bin(tw, th, N, (int32_t)capacity, /*clamp=*/true, rec, radii, bucket, keys_sorted, vals_sorted,
-                        tile_ranges, sort_temp, sort_temp_bytes, totals, stream);
+                        tile_ranges, sort_temp, sort_temp_bytes, totals, stream, tile_rects, counts_ready != 0);
 }

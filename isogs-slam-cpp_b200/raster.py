@@ -80,7 +80,7 @@ def preprocess(cam, means, scales, quats, opacities, colors, ch=4, flags=0, pose
     check(lib().isogs_preprocess_fwd(C.byref(cam), C.byref(pose) if pose is not None else None, _ptr(pose_dev), N,
                                      _ptr(means), _ptr(scales), scale_dim, _ptr(quats), _ptr(opacities), _ptr(colors),
                                      ch, flags, _ptr(rec), _ptr(radii), _ptr(tiles), _ptr(cum), _ptr(scan_tmp),
-                                     scan_b, C.byref(m), None, _stream()))
+                                     scan_b, C.byref(m), None, None, None, _stream()))
     return rec, radii, tiles, cum, int(m.value)
 
 

@@ -150,6 +150,7 @@ class StepWorkspace:
         self.rec = torch.empty((n_cap, REC), dtype=f32, device=device)
         self.v_rec = torch.empty((n_cap, REC), dtype=f32, device=device)
         self.radii = torch.empty((n_cap, 2), dtype=i32, device=device)
+        self.tile_rects = torch.empty((n_cap, 4), dtype=i32, device=device)   # tile rect + depth bits per Gaussian
         self.tiles = torch.empty((n_cap,), dtype=i32, device=device)
         self.cum = torch.empty((n_cap,), dtype=i32, device=device)
         self.n_cap = n_cap
@@ -183,7 +184,8 @@ class StepWorkspace:
     def c_struct(self):
         """isogs_workspace over the current buffers (rebuilt when a buffer was re-allocated)."""
         bufs = (self.rec, self.v_rec, self.radii, self.ku, self.vs, self.ranges, self.totals, self.sort_tmp, self.render,
-                self.v_render, self.alpha, self.last, self.small, self.dmaps, self.outlier_scratch, self.median_tmp)
+                self.v_render, self.alpha, self.last, self.small, self.dmaps, self.outlier_scratch, self.median_tmp,
+                self.tile_rects)
         key = tuple(0 if b is None else b.data_ptr() for b in bufs) + (self.isect_cap,)
         if self._cws is not None and self._cws[0] == key:
             return self._cws[1]
@@ -199,6 +201,7 @@ class StepWorkspace:
         w.median_scratch = None if self.outlier_scratch is None else self.outlier_scratch.data_ptr()
         w.median_temp = None if self.median_tmp is None else self.median_tmp.data_ptr()
         w.median_temp_bytes = self.median_b
+        w.tile_rects = self.tile_rects.data_ptr()
         self._cws = (key, w)
         self.drop_graphs()                                    # captured launches hold the old pointers
         return w
@@ -286,6 +289,7 @@ class StepWorkspace:
         self.rec = torch.empty((n_cap, REC), dtype=f32, device=device)
         self.v_rec = torch.empty((n_cap, REC), dtype=f32, device=device)
         self.radii = torch.empty((n_cap, 2), dtype=i32, device=device)
+        self.tile_rects = torch.empty((n_cap, 4), dtype=i32, device=device)
         self.tiles = torch.empty((n_cap,), dtype=i32, device=device)
         self.cum = torch.empty((n_cap,), dtype=i32, device=device)
         self.n_cap = n_cap
@@ -316,10 +320,11 @@ def render_forward(ws, gmap, pose=None, pose_dev=None, ch=5, marks=None, zero_v_
                                  _ptr(gmap.p["means3D"]), _ptr(gmap.p["log_scales"]), gmap.sd, _ptr(quats),
                                  _ptr(gmap.p["logit_opacities"]), _ptr(gmap.p["rgb_colors"]), ch, flags,
                                  _ptr(ws.rec), _ptr(ws.radii), None, None, None, 0, None,
-                                 _ptr(ws.v_rec) if zero_v_rec else None, st))
+                                 _ptr(ws.v_rec) if zero_v_rec else None, _ptr(ws.tile_rects), None, st))
     _mark(marks, "preprocess_fwd")
     check(L.isogs_tile_bin_async(C.byref(cam), N, ws.isect_cap, _ptr(ws.rec), _ptr(ws.radii), _ptr(ws.ku), None,
-                                 _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.totals), _ptr(ws.sort_tmp), ws.sort_b, st))
+                                 _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.totals), _ptr(ws.sort_tmp), ws.sort_b,
+                                 _ptr(ws.tile_rects), 0, st))
     _mark(marks, "tile_bin")
     check(L.isogs_blend_fwd(C.byref(cam), ch, _ptr(ws.rec), _ptr(ws.vs), _ptr(ws.ranges), _ptr(ws.render),
                             _ptr(ws.alpha), _ptr(ws.last), st))

@@ -54,7 +54,7 @@ def test_fullsize_properties(pkg, syn, shape, n_target):
     tmp = torch.empty((sort_b,), dtype=torch.uint8, device="cuda")
     p = lambda x: C.c_void_p(x.data_ptr())
     pkg._lib.check(pkg.lib().isogs_tile_bin_async(C.byref(cam), N, M + 7, p(ctx.rec), p(ctx.radii), p(bucket), None,
-                                                  p(vs2), p(rg2), p(tot), p(tmp), sort_b,
+                                                  p(vs2), p(rg2), p(tot), p(tmp), sort_b, None, 0,
                                                   C.c_void_p(torch.cuda.current_stream().cuda_stream)))
     torch.cuda.synchronize()
     assert tot.tolist() == [M, 0] and torch.equal(rg2, ctx.ranges) and torch.equal(vs2[:M], ctx.vals)

@@ -228,3 +228,42 @@ def test_dropin_and_fused_paths_share_one_screen_gradient_convention(pkg, syn, s
     assert torch.allclose(fused, dropin, rtol=1e-6, atol=0)
     thr = float(fused[fused > 0].median())
     assert torch.equal(fused >= thr, dropin >= thr), "the two paths must select the same Gaussians"
+
+
+def test_fused_count_and_rect_binning_is_bit_identical(pkg, syn):
+    """The fused step's binning -- per-tile counts accumulated by the projection kernel, scatter fed by the 16-byte
+    (tile rect, depth bits) rows -- must produce exactly the lists of isogs_tile_bin (which are bit-exact against the
+    oracle and the reference's own intersect kernels)."""
+    params, (W, H, fx, fy, cx, cy) = _scene(syn)
+    cam = pkg.make_camera(W, H, fx, fy, cx, cy)
+    flags = pkg._lib.F_LOG_SCALES | pkg._lib.F_LOGIT_OPAC
+    means, ls = t(params["means3D"]), t(params["log_scales"])
+    lo, rgb = t(params["logit_opacities"].reshape(-1)), t(params["rgb_colors"])
+    q, tr = syn.w2c_to_pose(syn.trajectory(8, step=3.0)[4])
+    pose = pkg.make_pose(q, tr)
+    rec, radii, tiles, cum, M = pkg.raster.preprocess(cam, means, ls, None, lo, rgb, ch=5, flags=flags, pose=pose)
+    ks, vs, ranges, _, _ = pkg.raster.tile_bin(cam, rec, radii, cum, M)
+    N = means.shape[0]
+    L, st = pkg.lib(), C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    p = lambda x: None if x is None else C.c_void_p(x.data_ptr())
+    rec2 = torch.empty_like(rec); radii2 = torch.empty_like(radii)
+    rects = torch.empty((N, 4), dtype=torch.int32, device="cuda")
+    _, sort_b = pkg._lib.temp_bytes(0, M + 5)
+    tmp = torch.zeros((sort_b,), dtype=torch.uint8, device="cuda")          # counters (head of sort_temp) zeroed
+    pkg._lib.check(L.isogs_preprocess_fwd(C.byref(cam), C.byref(pose), None, N, p(means), p(ls), 1, None, p(lo), p(rgb), 5,
+                                          flags, p(rec2), p(radii2), None, None, None, 0, None, None, p(rects), p(tmp), st))
+    bucket = torch.empty((M + 5,), dtype=torch.int64, device="cuda")
+    ks2 = torch.empty((M + 5,), dtype=torch.int64, device="cuda")
+    vs2 = torch.empty((M + 5,), dtype=torch.int32, device="cuda")
+    rg2 = torch.empty_like(ranges)
+    tot = torch.zeros((2,), dtype=torch.int32, device="cuda")
+    pkg._lib.check(L.isogs_tile_bin_async(C.byref(cam), N, M + 5, p(rec2), p(radii2), p(bucket), p(ks2), p(vs2), p(rg2),
+                                          p(tot), p(tmp), sort_b, p(rects), 1, st))
+    torch.cuda.synchronize()
+    assert torch.equal(rec2, rec) and torch.equal(radii2, radii)
+    assert tot.tolist() == [M, 0]
+    assert torch.equal(rg2, ranges) and torch.equal(vs2[:M], vs) and torch.equal(ks2[:M], ks)
+    r = rects.cpu().numpy().view(np.uint32)
+    n_tiles_per = ((r[:, 0] >> 16) - (r[:, 0] & 0xffff)) * ((r[:, 1] >> 16) - (r[:, 1] & 0xffff))
+    assert np.array_equal(n_tiles_per.astype(np.int32), tiles.cpu().numpy())
+    assert np.array_equal(r[:, 2][n_tiles_per > 0], rec.cpu().numpy()[:, 10].view(np.uint32)[n_tiles_per > 0])

@@ -182,7 +182,7 @@ def test_tile_bin_async_matches_sync_and_reports_overflow(pkg, syn):
         rg2 = torch.empty((cam.n_tiles + 1,), dtype=torch.int32, device="cuda")
         tot = torch.zeros((2,), dtype=torch.int32, device="cuda")
         pkg._lib.check(L.isogs_tile_bin_async(C.byref(cam), N, cap, _ptr(rec), _ptr(radii), _ptr(bucket), _ptr(ks2),
-                                              _ptr(vs2), _ptr(rg2), _ptr(tot), _ptr(tmp), sort_b, _stream()))
+                                              _ptr(vs2), _ptr(rg2), _ptr(tot), _ptr(tmp), sort_b, None, 0, _stream()))
         torch.cuda.synchronize()
         return ks2, vs2, rg2, tot.cpu().numpy()
 
