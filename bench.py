@@ -193,7 +193,7 @@ def launches_per_step(world, ssim=False):
     tile_scan, tile_scatter, tile_sort_reg, tile_sort, blend_fwd, loss_l1, blend_bwd, preprocess_bwd, adam
     (+ ssim fwd / bwd; + the two-shot peer all-reduce and its wait at N > 1).  Checked against the ncu launch
     list under profiles/."""
-    return 12 + (2 if ssim else 0) + (2 if world > 1 else 0)
+    return 12 + (2 if ssim else 0) + (2 if world > 1 else 0)   # N > 1, fused exchange: +2 exchange kernels, -1 Adam
 
 
 _JSON_FD = 1
@@ -228,18 +228,26 @@ def run_ours(args):
     # NVLink peer memory (csrc/peer.cu); NCCL when asked for, or when CUDA IPC is unavailable on the box.
     dp = importlib.import_module("isogs_slam_cpp_b200.dp")
     ar, ar_kind, grad_alloc = None, "none", None
+    fused = False
     if world > 1:
         ar, ar_kind = dp.allreduce_mean_, "nccl all-reduce (ncclAvg)"
-        if args.allreduce == "p2p":
-            peer = dp.PeerAllReduce(dev)
+        if args.allreduce in ("p2p", "fused"):
+            fused = args.allreduce == "fused"
+            peer = dp.PeerReduceAdam(dev) if fused else dp.PeerAllReduce(dev)
             try:
                 peer.alloc(1024)                       # probe: cudaMalloc + IPC export + peer mapping on every rank
-                ar, ar_kind, grad_alloc = peer, "own two-shot kernel over NVLink peer memory (isogs_allreduce_avg_p2p)", peer.alloc
+                ar, grad_alloc = peer, peer.alloc
+                ar_kind = ("reduce + Adam + parameter broadcast fused in ONE kernel over NVLink peer memory "
+                           "(isogs_reduce_adam_p2p, optimizer state sharded)" if fused else
+                           "own two-shot kernel over NVLink peer memory (isogs_allreduce_avg_p2p)")
             except RuntimeError as e:
+                fused = False
                 ar_kind += f"; p2p unavailable: {e}"
                 if rank == 0:
                     print(f"[bench] peer all-reduce unavailable, using NCCL: {e}", file=sys.stderr)
     gmap = ss.GaussianMap(params, device=dev, grad_alloc=grad_alloc)
+    if fused:
+        ar.adopt(gmap)                             # parameter tensors into IPC-shared memory (peers store into them)
     ws = ss.StepWorkspace(cam, gmap.count, dev)
     P = W * H
     # keyframes resident in HBM (for `value`) and, as uint8 / uint16 source frames, in pinned host memory (for `e2e`)
@@ -359,6 +367,10 @@ def run_ours(args):
                 print("[bench] peer all-reduce timed out during warm-up, using NCCL", file=sys.stderr)
             ws.drop_graphs()
             gmap.grad_flat, gmap.g = None, {}
+            if fused:
+                gmap.p = {}
+                ar.drop_params()
+                fused = False
             ar.release()
             ar = dp.allreduce_mean_
             gmap = ss.GaussianMap(params, device=dev)
@@ -478,6 +490,10 @@ def run_ours(args):
         if hasattr(ar, "release"):
             ws.drop_graphs()
             gmap.grad_flat, gmap.g = None, {}
+            if fused:
+                init_p.clear()
+                gmap.p = {}
+                ar.drop_params()
             ar.release()
     if rank != 0:
         if world > 1:
@@ -746,8 +762,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
     ap.add_argument("--no-graph", action="store_true", help="enqueue every step eagerly instead of replaying the captured graph")
-    ap.add_argument("--allreduce", default="p2p", choices=["p2p", "nccl"],
-                    help="gradient average at N > 1: own NVLink peer kernel (default) or NCCL")
+    ap.add_argument("--allreduce", default="fused", choices=["fused", "p2p", "nccl"],
+                    help="exchange step at N > 1: reduce + Adam fused in one NVLink peer-memory kernel (default), the "
+                         "peer-memory all-reduce followed by the ordinary Adam launch, or NCCL")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line: anything a library prints there (NCCL's version banner under
     # NCCL_DEBUG=VERSION, torchrun notices) goes to stderr instead -- file descriptor 1 is pointed at stderr for

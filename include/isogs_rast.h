@@ -457,6 +457,28 @@ int isogs_allreduce_avg_p2p(int world, int rank, float* const* bufs /*HOST*/, ui
                             int64_t numel, uint32_t epoch, int n_ctas, int32_t* status, void* stream);
 int isogs_peer_wait(int world, const uint32_t* flags_local, uint32_t epoch, int32_t* status, void* stream);
 
+/* The exchange FUSED with the optimizer step: the owner of a slice averages it over the ranks (as above), applies Adam to
+ * it in registers -- its slice of the moments is the only up-to-date copy, i.e. the optimizer state is sharded over the
+ * ranks -- and stores the updated PARAMETERS into every rank's parameter tensors; isogs_adam_fused is not called at
+ * all.  Replaces, per rank, the all-reduce above + torch.optim.Adam.step over all N Gaussians (splatam.py:1475) by one
+ * kernel whose Adam work is N / world.  groups (HOST): position of each parameter group in the flat gradient buffer
+ * (`offset`, `numel` in floats; offset a multiple of 4), the group's parameter tensor on EVERY rank (peer-mapped, own
+ * entry = local, 16-byte aligned, at least 3 floats of slack behind numel), the LOCAL moments and the learning rate.
+ * state: DEVICE isogs_adam_state advanced by isogs_step_begin this iteration.  Flags / epoch / status / isogs_peer_wait
+ * as for isogs_allreduce_avg_p2p (wait before the next reader of the parameters). */
+#define ISOGS_PEER_MAX_WORLD 16
+typedef struct isogs_peer_adam_group {
+    int64_t offset, numel;
+    float* param[ISOGS_PEER_MAX_WORLD];
+    float* exp_avg;
+    float* exp_avg_sq;
+    float lr;
+} isogs_peer_adam_group;
+int isogs_reduce_adam_p2p(int world, int rank, float* const* grad_bufs /*HOST*/, uint32_t* const* flags /*HOST*/,
+                          int64_t numel, const isogs_peer_adam_group* groups /*HOST*/, int n_groups, float beta1,
+                          float beta2, float eps, const isogs_adam_state* state, uint32_t epoch, int n_ctas,
+                          int32_t* status, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -52,6 +52,11 @@ class Frame(C.Structure):
     _fields_ = [("gt_rgb", C.c_void_p), ("gt_depth", C.c_void_p), ("pose", C.c_float * 7), ("inv_n_depth", C.c_float)]
 
 
+class PeerAdamGroup(C.Structure):
+    _fields_ = [("offset", C.c_int64), ("numel", C.c_int64), ("param", C.c_void_p * 16), ("exp_avg", C.c_void_p),
+                ("exp_avg_sq", C.c_void_p), ("lr", C.c_float)]
+
+
 class Gaussians(C.Structure):
     _fields_ = [("N", C.c_int64), ("scale_dim", C.c_int32), ("reserved", C.c_int32),
                 ("p", C.c_void_p * 5), ("g", C.c_void_p * 5), ("m", C.c_void_p * 5), ("v", C.c_void_p * 5)]
@@ -142,6 +147,8 @@ _SIGS = {
     "isogs_peer_free": (C.c_int, [_VP]),
     "isogs_allreduce_avg_p2p": (C.c_int, [_I32, _I32, C.POINTER(_VP), C.POINTER(_VP), _I64, C.c_uint32, _I32, _VP, _VP]),
     "isogs_peer_wait": (C.c_int, [_I32, _VP, C.c_uint32, _VP, _VP]),
+    "isogs_reduce_adam_p2p": (C.c_int, [_I32, _I32, C.POINTER(_VP), C.POINTER(_VP), _I64, C.POINTER(PeerAdamGroup), _I32,
+                                        _F, _F, _F, _VP, C.c_uint32, _I32, _VP, _VP]),
     "isogs_prune_mask": (C.c_int, [_I64, _VP, _VP, _I32, _F, _F, _VP, _VP]),
     "isogs_compact": (C.c_int, [_I64, _VP, C.POINTER(Rows), _I32, _VP, _VP, _SZ, _VP, _VP]),
     "isogs_backproject_append": (C.c_int, [C.POINTER(Camera), C.POINTER(Pose), _VP, _VP, _VP, _VP, _F, _F, _VP, _VP,

@@ -122,6 +122,112 @@ peer_allreduce_kernel(PeerPtrs pp, int world, int rank, int64_t n4, uint32_t epo
     }
 }
 
+// ---- fused exchange + optimizer step ------------------------------------------------------------------------------
+// The slice owner does not hand the averaged GRADIENTS back: it applies Adam to its 1/world slice in registers (its
+// slice of the moments is the only copy that is kept up to date -- optimizer state sharded like ZeRO-1) and stores the
+// updated PARAMETERS into every rank's parameter tensors.  Same NVLink bytes as the all-reduce (slice loads from every
+// peer + slice stores to every peer), but Adam shrinks from all N Gaussians to N / world per rank, one launch and the
+// 32 MB re-read of averaged gradients disappear, and the replicas stay bit-identical by construction (one rank computes
+// each parameter, everybody receives the same bits).
+constexpr int PEER_MAX_GROUPS = 5;
+struct PeerAdamArgs {
+    int64_t off4[PEER_MAX_GROUPS], n4[PEER_MAX_GROUPS]; // group position in the flat gradient buffer (float4 units)
+    float4* param[PEER_MAX_GROUPS][PEER_MAX_WORLD];     // parameter tensor of the group on every rank
+    float4* m[PEER_MAX_GROUPS];
+    float4* v[PEER_MAX_GROUPS];                         // LOCAL moments
+    float lr[PEER_MAX_GROUPS];
+    int n_groups;
+    float b2, one_minus_b1, one_minus_b2, eps;
+    const isogs_adam_state* state;
+};
+
+// the arithmetic of adam_kernel (step.cu), operation for operation
+__device__ __forceinline__ void peer_adam_one(float& p, float g, float& m, float& v, const PeerAdamArgs& a, float step_size,
+                                              float inv_bc2_sqrt) {
+    const float mi = m + (g - m) * a.one_minus_b1;
+    const float vi = v * a.b2 + a.one_minus_b2 * g * g;
+    m = mi; v = vi;
+    const float denom = sqrtf(vi) * inv_bc2_sqrt + a.eps;
+    p = p - step_size * (mi / denom);
+}
+
+template <int WORLD>
+__device__ __forceinline__ void reduce_adam_slice(const PeerPtrs& pp, const PeerAdamArgs& a, int world, int rank,
+                                                  int64_t begin, int64_t end, float inv_world) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const float ib2 = (float)a.state->inv_bc2_sqrt;
+    const double ibc1 = a.state->inv_bc1;
+    for (int64_t i = begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < end; i += stride) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (WORLD > 0) {
+            float4 t[WORLD > 0 ? WORLD : 1];
+#pragma unroll
+            for (int p = 0; p < WORLD; ++p) t[p] = ld_relaxed_sys_f4(pp.buf[p] + i);     // all loads in flight first
+#pragma unroll
+            for (int p = 0; p < WORLD; ++p) { acc.x += t[p].x; acc.y += t[p].y; acc.z += t[p].z; acc.w += t[p].w; }
+        } else {
+            for (int p = 0; p < world; ++p) {
+                const float4 t = ld_relaxed_sys_f4(pp.buf[p] + i);
+                acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+            }
+        }
+        acc.x *= inv_world; acc.y *= inv_world; acc.z *= inv_world; acc.w *= inv_world;
+        int g = -1;
+#pragma unroll
+        for (int k = 0; k < PEER_MAX_GROUPS; ++k)
+            if (k < a.n_groups && i >= a.off4[k] && i < a.off4[k] + a.n4[k]) g = k;
+        if (g < 0) continue;                           // padding between groups
+        const int64_t j = i - a.off4[g];
+        const float ss = (float)((double)a.lr[g] * ibc1);
+        float4 P4 = a.param[g][rank][j], M4 = a.m[g][j], V4 = a.v[g][j];
+        peer_adam_one(P4.x, acc.x, M4.x, V4.x, a, ss, ib2);
+        peer_adam_one(P4.y, acc.y, M4.y, V4.y, a, ss, ib2);
+        peer_adam_one(P4.z, acc.z, M4.z, V4.z, a, ss, ib2);
+        peer_adam_one(P4.w, acc.w, M4.w, V4.w, a, ss, ib2);
+        a.m[g][j] = M4;
+        a.v[g][j] = V4;
+        const int n = WORLD > 0 ? WORLD : world;
+#pragma unroll
+        for (int p = 0; p < n; ++p) st_relaxed_sys_f4(a.param[g][p] + j, P4);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+peer_reduce_adam_kernel(PeerPtrs pp, PeerAdamArgs a, int world, int rank, int64_t n4, uint32_t epoch,
+                        int32_t* __restrict__ status) {
+    const int tid = threadIdx.x;
+    uint32_t* mine = pp.flags[rank];
+    // 1. "my gradients are complete AND I have finished reading my parameters for this iteration" (stream order put
+    //    this kernel after the backward pass), so peers may overwrite them
+    if (blockIdx.x == 0 && tid < world) st_release_sys(pp.flags[tid] + rank, epoch);
+    if (tid < world && !wait_epoch(mine + tid, epoch)) atomicExch(status, 1);
+    __syncthreads();
+    const int64_t per = (n4 + world - 1) / world;
+    const int64_t begin = min(n4, per * rank), end = min(n4, begin + per);
+    const float inv_world = 1.0f / (float)world;
+    switch (world) {
+        case 1: reduce_adam_slice<1>(pp, a, world, rank, begin, end, inv_world); break;
+        case 2: reduce_adam_slice<2>(pp, a, world, rank, begin, end, inv_world); break;
+        case 4: reduce_adam_slice<4>(pp, a, world, rank, begin, end, inv_world); break;
+        case 8: reduce_adam_slice<8>(pp, a, world, rank, begin, end, inv_world); break;
+        default: reduce_adam_slice<0>(pp, a, world, rank, begin, end, inv_world); break;
+    }
+    // 3. last CTA: "my slice of the parameters has landed"
+    __threadfence_system();
+    __syncthreads();
+    __shared__ bool s_last;
+    if (tid == 0) {
+        const uint32_t prev = atomicAdd(mine + 32, 1u);
+        s_last = prev == gridDim.x - 1;
+        if (s_last) mine[32] = 0;
+    }
+    __syncthreads();
+    if (s_last && tid < world) {
+        __threadfence_system();
+        st_release_sys(pp.flags[tid] + 16 + rank, epoch);
+    }
+}
+
 __global__ void peer_wait_kernel(const uint32_t* __restrict__ mine, int world, uint32_t epoch, int32_t* __restrict__ status) {
     if (threadIdx.x < world && !wait_epoch(mine + 16 + threadIdx.x, epoch)) atomicExch(status, 2);
 }
@@ -181,6 +287,51 @@ extern "C" int isogs_allreduce_avg_p2p(int world, int rank, float* const* bufs, 
     const int64_t want = (per + 255) / 256;
     if (want < grid) grid = (int)(want > 0 ? want : 1);
     peer_allreduce_kernel<<<grid, 256, 0, stream>>>(pp, world, rank, n4, epoch, status);
+    ISOGS_CUDA(cudaGetLastError());
+    return ISOGS_OK;
+}
+
+extern "C" int isogs_reduce_adam_p2p(int world, int rank, float* const* grad_bufs, uint32_t* const* flags, int64_t numel,
+                                     const isogs_peer_adam_group* groups, int n_groups, float beta1, float beta2, float eps,
+                                     const isogs_adam_state* state, uint32_t epoch, int n_ctas, int32_t* status,
+                                     void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world || !grad_bufs || !flags || numel < 0 || (numel & 3) ||
+        !status || !groups || n_groups < 1 || n_groups > PEER_MAX_GROUPS || !state) {
+        set_error("isogs_reduce_adam_p2p: bad argument (world <= 16, numel a multiple of 4, <= 5 groups, device Adam state)");
+        return ISOGS_E_ARG;
+    }
+    PeerPtrs pp{};
+    for (int p = 0; p < world; ++p) {
+        if (!grad_bufs[p] || !flags[p] || ((uintptr_t)grad_bufs[p] & 15)) { set_error("isogs_reduce_adam_p2p: null or misaligned peer buffer"); return ISOGS_E_ARG; }
+        pp.buf[p] = (float4*)grad_bufs[p];
+        pp.flags[p] = flags[p];
+    }
+    PeerAdamArgs a{};
+    a.n_groups = n_groups;
+    a.b2 = beta2; a.one_minus_b1 = 1.0f - beta1; a.one_minus_b2 = 1.0f - beta2; a.eps = eps;
+    a.state = state;
+    for (int g = 0; g < n_groups; ++g) {
+        const isogs_peer_adam_group& G = groups[g];
+        if ((G.offset & 3) || G.numel < 0 || !G.exp_avg || !G.exp_avg_sq || (((uintptr_t)G.exp_avg | (uintptr_t)G.exp_avg_sq) & 15)) {
+            set_error("isogs_reduce_adam_p2p: group %d: offset must be a multiple of 4 floats, moments 16-byte aligned", g);
+            return ISOGS_E_ARG;
+        }
+        a.off4[g] = G.offset / 4;
+        a.n4[g] = (G.numel + 3) / 4;                  // the tail float4 may carry up to 3 padding floats (kept zero / unused)
+        a.m[g] = (float4*)G.exp_avg;
+        a.v[g] = (float4*)G.exp_avg_sq;
+        a.lr[g] = G.lr;
+        for (int p = 0; p < world; ++p) {
+            if (!G.param[p] || ((uintptr_t)G.param[p] & 15)) { set_error("isogs_reduce_adam_p2p: group %d: null or misaligned parameter pointer of rank %d", g, p); return ISOGS_E_ARG; }
+            a.param[g][p] = (float4*)G.param[p];
+        }
+    }
+    const int64_t n4 = numel / 4, per = (n4 + world - 1) / world;
+    int grid = n_ctas > 0 ? n_ctas : 148 * 4;
+    const int64_t want = (per + 255) / 256;
+    if (want < grid) grid = (int)(want > 0 ? want : 1);
+    peer_reduce_adam_kernel<<<grid, 256, 0, stream>>>(pp, a, world, rank, n4, epoch, status);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
 }

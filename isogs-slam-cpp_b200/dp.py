@@ -106,38 +106,51 @@ class PeerAllReduce:
         dist.all_reduce(t, op=dist.ReduceOp.MIN, group=self.group)
         return bool(t.item())
 
-    def alloc(self, numel):
+    def _shared(self, nbytes):
+        """COLLECTIVE: cudaMalloc `nbytes` (zeroed) on every rank, exchange the IPC handles, map every peer.
+        Returns (own pointer, [pointer of every rank's allocation, own entry = own pointer])."""
         L = self._lib.lib()
-        self.release()
-        numel = (int(numel) + 3) & ~3
-        flag_off = (4 * numel + 255) & ~255
         ptr, handle = C.c_void_p(), (C.c_ubyte * 64)()
         with torch.cuda.device(self.device):
-            rc = L.isogs_peer_alloc(flag_off + self.FLAG_BYTES, C.byref(ptr), handle)
+            rc = L.isogs_peer_alloc(int(nbytes), C.byref(ptr), handle)
             err = None if rc == 0 else self._last_error()
             if not self._agree(rc == 0):
                 if rc == 0:
                     L.isogs_peer_free(ptr)
                 raise RuntimeError(f"isogs_peer_alloc failed on some rank ({err})")
-            self.own = int(ptr.value)
+            own = int(ptr.value)
             handles = [None] * self.world
             if self.world > 1:
                 dist.all_gather_object(handles, bytes(handle), group=self.group)
-            self.ptrs, ok, err = [], True, None
+            ptrs, ok, err = [], True, None
             for r in range(self.world):
                 if r == self.rank:
-                    self.ptrs.append(self.own)
+                    ptrs.append(own)
                     continue
                 q = C.c_void_p()
                 hb = (C.c_ubyte * 64).from_buffer_copy(handles[r])
                 if L.isogs_peer_open(hb, C.byref(q)) != 0:
                     ok, err = False, self._last_error()
-                    self.ptrs.append(0)
+                    ptrs.append(0)
                 else:
-                    self.ptrs.append(int(q.value))
+                    ptrs.append(int(q.value))
             if not self._agree(ok):
-                self.release()
+                self._unshare(own, ptrs)
                 raise RuntimeError(f"isogs_peer_open failed on some rank ({err})")
+        return own, ptrs
+
+    def _unshare(self, own, ptrs):
+        L = self._lib.lib()
+        for r, p in enumerate(ptrs):
+            if r != self.rank and p:
+                L.isogs_peer_close(C.c_void_p(p))
+        L.isogs_peer_free(C.c_void_p(own))
+
+    def alloc(self, numel):
+        self.release()
+        numel = (int(numel) + 3) & ~3
+        flag_off = (4 * numel + 255) & ~255
+        self.own, self.ptrs = self._shared(flag_off + self.FLAG_BYTES)
         self.bufs = (C.c_void_p * self.world)(*self.ptrs)
         self.flags = (C.c_void_p * self.world)(*[p + flag_off for p in self.ptrs])
         self.numel = numel
@@ -167,13 +180,96 @@ class PeerAllReduce:
     def release(self):
         if self.own is None:
             return
-        L = self._lib.lib()
         torch.cuda.synchronize(self.device)
         if self.world > 1:
             dist.barrier(group=self.group)           # nobody may still be reading this rank's buffer
-        for r, p in enumerate(self.ptrs):
-            if r != self.rank and p:
-                L.isogs_peer_close(C.c_void_p(p))
         self.tensor = None
-        L.isogs_peer_free(C.c_void_p(self.own))
+        self._unshare(self.own, self.ptrs)
         self.own, self.ptrs = None, []
+
+
+class PeerReduceAdam(PeerAllReduce):
+    """The exchange FUSED with the optimizer step (isogs_reduce_adam_p2p, csrc/peer.cu): the owner of a 1/world slice
+    averages it over the ranks, applies Adam to it in registers and stores the updated PARAMETERS into every rank's
+    parameter tensors.  The parameter tensors of the map therefore live in peer-mapped memory too:
+
+        ar = PeerReduceAdam(device)
+        gmap = GaussianMap(params, device, grad_alloc=ar.alloc)
+        ar.adopt(gmap)                                   # COLLECTIVE: moves gmap.p[...] into shared allocations
+        map_step(..., allreduce=ar)                      # backward, then this object: no isogs_adam_fused launch
+
+    Optimizer state is SHARDED: a rank keeps Adam moments only for the slice it owns.  reset_optimizer() (every mapping
+    call of the reference, splatam.py:1406) is slice-agnostic; anything that moves rows (prune / densify compaction) or
+    changes the Gaussian count in the middle of a mapping call must be preceded by sync_moments(gmap)."""
+
+    def __init__(self, device, group=None, n_ctas=0):
+        super().__init__(device, group, n_ctas)
+        self.pown, self.pptrs = {}, {}
+
+    def adopt(self, gmap):
+        """COLLECTIVE.  Re-homes every parameter tensor that has a gradient into IPC-shared memory (same values)."""
+        self.drop_params()
+        for k in gmap.grad_names:
+            old = gmap.p[k]
+            n = old.numel()
+            own, ptrs = self._shared(4 * n + 64)         # slack: the tail float4 of a group may run 3 floats over
+            t = torch.as_tensor(_RawCudaBuffer(own, n), device=self.device).view(old.shape)
+            t.copy_(old)
+            gmap.p[k] = t
+            self.pown[k], self.pptrs[k] = own, ptrs
+        gmap._cs = None
+        torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            dist.barrier(group=self.group)
+        return gmap
+
+    def fused_adam(self, gmap, lrs, eps=1e-15, beta1=0.9, beta2=0.999):
+        L = self._lib.lib()
+        n = gmap.grad_used
+        if gmap.grad_flat.data_ptr() != self.own or n > self.numel or n % 4:
+            raise ValueError("PeerReduceAdam: the map's gradient buffer must come from alloc()")
+        names = gmap.grad_names
+        arr = (self._lib.PeerAdamGroup * len(names))()
+        for i, k in enumerate(names):
+            if k not in self.pptrs or gmap.p[k].data_ptr() != self.pown[k]:
+                raise ValueError("PeerReduceAdam: call adopt(gmap) first (and again after the pool has grown)")
+            g = gmap.g[k]
+            arr[i].offset = (g.data_ptr() - gmap.grad_flat.data_ptr()) // 4
+            arr[i].numel = g.numel()
+            for r in range(self.world):
+                arr[i].param[r] = self.pptrs[k][r]
+            arr[i].exp_avg, arr[i].exp_avg_sq = gmap.m[k].data_ptr(), gmap.v[k].data_ptr()
+            arr[i].lr = lrs[k]
+        self.epoch += 1
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        self._lib.check(L.isogs_reduce_adam_p2p(self.world, self.rank, self.bufs, self.flags, n, arr, len(names), beta1, beta2,
+                                                eps, gmap.adam_state.data_ptr(), self.epoch, self.n_ctas,
+                                                self.status.data_ptr(), st))
+        self._lib.check(L.isogs_peer_wait(self.world, self.flags[self.rank], self.epoch, self.status.data_ptr(), st))
+
+    def sync_moments(self, gmap):
+        """COLLECTIVE.  Makes every rank's Adam moments complete again (each rank broadcasts the parts it owns):
+        needed before rows move (prune / densify) or the ownership boundaries shift (count change) mid-call."""
+        if self.world == 1:
+            return
+        n = gmap.grad_used
+        base = gmap.grad_flat.data_ptr()
+        for r in range(self.world):
+            b, e = slice_bounds(n, self.world, r)
+            for k in gmap.grad_names:
+                off = (gmap.g[k].data_ptr() - base) // 4
+                lo, hi = max(b, off) - off, min(e, off + gmap.g[k].numel()) - off
+                if hi <= lo:
+                    continue
+                for t in (gmap.m[k], gmap.v[k]):
+                    dist.broadcast(t.view(-1)[lo:hi], src=r, group=self.group)
+
+    def drop_params(self):
+        if not self.pown:
+            return
+        torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            dist.barrier(group=self.group)
+        for k in list(self.pown):
+            self._unshare(self.pown[k], self.pptrs[k])
+        self.pown, self.pptrs = {}, {}

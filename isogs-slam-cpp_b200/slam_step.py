@@ -525,6 +525,12 @@ def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, all
         if isoflat:
             iso_flat_loss(ws, gmap, seed=iso_seed)
             _mark(marks, "isoflat")
+        if allreduce is not None and hasattr(allreduce, "fused_adam"):
+            # exchange fused with the optimizer step (dp.PeerReduceAdam): no separate Adam launch
+            allreduce.fused_adam(gmap, lrs, eps)
+            _mark(marks, "allreduce")
+            ws.post_totals()
+            return ws.losses
         if allreduce is not None:
             allreduce(gmap.grad_flat[:gmap.grad_used])
             _mark(marks, "allreduce")
