@@ -396,8 +396,6 @@ typedef struct isogs_workspace {
 #define ISOGS_STEP_SSIM 1     /* colour term 0.8*L1 + 0.2*(1-SSIM) (splatam.py:568) instead of pure L1 */
 #define ISOGS_STEP_OUTLIER 2  /* tracking: ignore_outlier_depth_loss (splatam.py:551-554) */
 #define ISOGS_STEP_NO_SIL 4   /* tracking: use_sil_for_loss = False */
-#define ISOGS_STEP_KEEP_GRADS 8 /* mapping, both phases in one call: also write the gradients to gaussians->g (by default the
-                                 * projection backward applies Adam in place and the gradients never reach HBM) */
 #define ISOGS_PHASE_RENDER 1  /* begin + forward + loss + backward (gradients land in gaussians->g) */
 #define ISOGS_PHASE_ADAM 2    /* fused Adam on every group with a gradient */
 #define ISOGS_STEP_EVENTS 9   /* begin, preprocess_fwd, tile_bin, blend_fwd, loss, ssim, blend_bwd, preprocess_bwd, adam */

@@ -77,7 +77,7 @@ class StepParams(C.Structure):
                 ("eps", C.c_float)]
 
 
-STEP_SSIM, STEP_OUTLIER, STEP_NO_SIL, STEP_KEEP_GRADS = 1, 2, 4, 8
+STEP_SSIM, STEP_OUTLIER, STEP_NO_SIL = 1, 2, 4
 PHASE_RENDER, PHASE_ADAM = 1, 2
 STEP_EVENTS = 9
 STEP_EVENT_NAMES = ("begin", "preprocess_fwd", "tile_bin", "blend_fwd", "loss", "ssim", "blend_bwd", "preprocess_bwd",

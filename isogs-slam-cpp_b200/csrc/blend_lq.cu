@@ -333,25 +333,11 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
 // Forward, same organisation: a lane owns a 2x2 quad (T, 5 accumulators, last index per pixel in registers), a warp a
 // 16x8 half tile.  Reference: gsplat RasterizeToPixels3DGSFwd.cu:17-188.  The per-pixel body is predicated, not
 // branched; the contribute / saturate decisions are those of blend.cu::blend_fwd_kernel.
-// Optional epilogue (LOSS = true, 5 channels): the masked-L1 loss of get_loss (splatam.py:534-570,747-749; see
-// loss_l1_kernel in step.cu, whose arithmetic this restates per pixel) evaluated while the pixel's five channels and
-// alpha are still in registers: writes v_render [5,H,W] and adds the loss scalars, so the separate 59 MB pass over
-// render / ground truth / v_render (and its launch) disappears from the fused steps.
-struct FwdLoss {
-    const isogs_frame* frame;  // DEVICE slot: ground truth planes, 1 / n_valid_depth
-    float* v_render;           // [5,H,W]
-    float* losses;             // {total, colour, depth, n_valid}
-    float w_im, w_depth, sil_thres;
-    int mode, use_sil;         // mode 0 tracking (sums, silhouette mask), 1 mapping (means)
-};
-
-__device__ __forceinline__ float sgnf(float d) { return (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f); }
-
-template <int CH, int NW, bool LOSS>
+template <int CH, int NW>
 __global__ void __launch_bounds__(THREADS, 8)
 blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
                     const int32_t* __restrict__ ranges, float* __restrict__ render, float* __restrict__ alpha,
-                    int32_t* __restrict__ last, FwdLoss fl) {
+                    int32_t* __restrict__ last) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     using R = Ring<NW, false>;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -452,89 +438,32 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
         }
     }
     const int64_t P = (int64_t)cam.width * cam.height;
-    float sum_d = 0.f, sum_c = 0.f, cnt = 0.f;
-    const float* gt_rgb = nullptr;
-    const float* gt_depth = nullptr;
-    float inv_nd = 1.0f, inv_nc = 1.0f;
-    if (LOSS) {
-        gt_rgb = fl.frame->gt_rgb;
-        gt_depth = fl.frame->gt_depth;
-        if (fl.mode == 1) { inv_nd = fl.frame->inv_n_depth; inv_nc = 1.0f / (float)(3 * P); }
-    }
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
         const int xi = x0 + (p & 1), yi = y0 + (p >> 1);
         if (xi < cam.width && yi < cam.height) {
             const int64_t pix = (int64_t)yi * cam.width + xi;
-            float out[CH];
 #pragma unroll
-            for (int k = 0; k < CH; ++k) out[k] = (k < 3) ? fmaf(T[p], cam.bg[k], acc[p][k]) : acc[p][k];
-#pragma unroll
-            for (int k = 0; k < CH; ++k) render[k * P + pix] = out[k];
-            const float al = 1.0f - T[p];
-            alpha[pix] = al;
+            for (int k = 0; k < CH; ++k) render[k * P + pix] = (k < 3) ? fmaf(T[p], cam.bg[k], acc[p][k]) : acc[p][k];
+            alpha[pix] = 1.0f - T[p];
             last[pix] = last_idx[p];
-            if (LOSS && CH == 5) {
-                const float d = out[3], gd = gt_depth[pix];
-                const float unc = out[CH - 1] - d * d;
-                bool m = (gd > 0.f) && !(isnan(d) || isnan(unc));
-                bool mc = true;
-                if (fl.mode == 0) {
-                    if (fl.use_sil) m = m && (al > fl.sil_thres);
-                    mc = fl.use_sil ? m : true;
-                }
-                const float dd = d - gd;
-                if (gd > 0.f) cnt += 1.f;
-                if (m) sum_d += fabsf(dd);
-                fl.v_render[3 * P + pix] = m ? (fl.w_depth * inv_nd) * sgnf(dd) : 0.f;
-                fl.v_render[4 * P + pix] = 0.f;
-#pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    const float dc = out[k] - gt_rgb[k * P + pix];
-                    if (mc) sum_c += fabsf(dc);
-                    fl.v_render[k * P + pix] = mc ? (fl.w_im * inv_nc) * sgnf(dc) : 0.f;
-                }
-            }
-        }
-    }
-    if (LOSS) {
-        __shared__ float s_part[WARPS][3];
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            sum_d += __shfl_xor_sync(FULL, sum_d, off);
-            sum_c += __shfl_xor_sync(FULL, sum_c, off);
-            cnt += __shfl_xor_sync(FULL, cnt, off);
-        }
-        if (lane == 0) { s_part[wid][0] = sum_d; s_part[wid][1] = sum_c; s_part[wid][2] = cnt; }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            float sd = 0.f, sc = 0.f, n = 0.f;
-#pragma unroll
-            for (int w = 0; w < WARPS; ++w) { sd += s_part[w][0]; sc += s_part[w][1]; n += s_part[w][2]; }
-            if (sd != 0.f || sc != 0.f || n != 0.f) {
-                const float ld = sd * inv_nd, lc = sc * inv_nc;
-                atomicAdd(fl.losses + 0, fl.w_im * lc + fl.w_depth * ld);
-                atomicAdd(fl.losses + 1, lc);
-                atomicAdd(fl.losses + 2, ld);
-                atomicAdd(fl.losses + 3, n);
-            }
         }
     }
 }
 
-template <int CH, int NW, bool LOSS>
+template <int CH, int NW>
 int launch_fwd(const DevCam& dc, const float* rec, const int32_t* vals, const int32_t* ranges, float* render, float* alpha,
-               int32_t* last, const FwdLoss& fl, cudaStream_t stream) {
+               int32_t* last, cudaStream_t stream) {
     constexpr size_t smem = sizeof(Ring<NW, false>) * WARPS;
     static thread_local int attr_dev = -1;
     int dev = 0;
     ISOGS_CUDA(cudaGetDevice(&dev));
     if (attr_dev != dev) {
-        ISOGS_CUDA(cudaFuncSetAttribute(blend_fwd_lq_kernel<CH, NW, LOSS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ISOGS_CUDA(cudaFuncSetAttribute(blend_fwd_lq_kernel<CH, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_dev = dev;
     }
     dim3 grid(dc.tw, dc.th);
-    blend_fwd_lq_kernel<CH, NW, LOSS><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, render, alpha, last, fl);
+    blend_fwd_lq_kernel<CH, NW><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, render, alpha, last);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
 }
@@ -572,27 +501,9 @@ extern "C" int isogs_blend_fwd(const isogs_camera* cam, int ch, const float* rec
     if ((uintptr_t)rec & 15) { set_error("isogs_blend_fwd: rec must be 16-byte aligned"); return ISOGS_E_ARG; }
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
-    const lq::FwdLoss none{};
-    if (ch == 4) return lq::launch_fwd<4, lq::NW_DEFAULT, false>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, none, stream);
-    return lq::launch_fwd<5, lq::NW_DEFAULT, false>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, none, stream);
+    if (ch == 4) return lq::launch_fwd<4, lq::NW_DEFAULT>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, stream);
+    return lq::launch_fwd<5, lq::NW_DEFAULT>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, stream);
 }
-
-// isogs_blend_fwd (5 channels) with the masked-L1 loss evaluated in the epilogue: used by the fused steps
-// (fused_step.cu) when no depth-outlier mask is requested.  frame: DEVICE slot.
-namespace isogs {
-int launch_blend_fwd_loss(const isogs_camera* cam, const float* rec, const int32_t* vals_sorted, const int32_t* tile_ranges,
-                          float* render, float* alpha, int32_t* last, const isogs_frame* frame, int mode, float w_im,
-                          float w_depth, float sil_thres, int use_sil, float* v_render, float* losses, cudaStream_t stream) {
-    if (!cam || !frame || !v_render || !losses || (mode != 0 && mode != 1)) { set_error("blend_fwd_loss: bad argument"); return ISOGS_E_ARG; }
-    if ((uintptr_t)rec & 15) { set_error("blend_fwd_loss: rec must be 16-byte aligned"); return ISOGS_E_ARG; }
-    DevCam dc = make_devcam(*cam);
-    if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
-    lq::FwdLoss fl;
-    fl.frame = frame; fl.v_render = v_render; fl.losses = losses;
-    fl.w_im = w_im; fl.w_depth = w_depth; fl.sil_thres = sil_thres; fl.mode = mode; fl.use_sil = use_sil;
-    return lq::launch_fwd<5, lq::NW_DEFAULT, true>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, fl, stream);
-}
-} // namespace isogs
 
 static int blend_bwd_entry(const char* who, bool geom, const isogs_camera* cam, int ch, const float* rec,
                            const int32_t* vals_sorted, const int32_t* tile_ranges, const float* alpha, const int32_t* last,

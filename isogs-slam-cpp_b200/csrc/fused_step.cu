@@ -20,12 +20,6 @@ int launch_loss_l1(const isogs_camera* cam, int mode, const float* render, const
                    cudaStream_t stream);
 int launch_ssim_loss(const isogs_camera* cam, const float* render, const float* gt_rgb, const isogs_frame* frame_dev,
                      float weight, float* dmaps, float* v_render, float* losses, float* ssim_out, cudaStream_t stream);
-int launch_blend_fwd_loss(const isogs_camera* cam, const float* rec, const int32_t* vals_sorted, const int32_t* tile_ranges,
-                          float* render, float* alpha, int32_t* last, const isogs_frame* frame, int mode, float w_im,
-                          float w_depth, float sil_thres, int use_sil, float* v_render, float* losses, cudaStream_t stream);
-int launch_preprocess_bwd_adam(const isogs_camera* cam, const float* pose_dev, const isogs_gaussians* gs, int ch, int flags,
-                               const int32_t* radii, const float* v_rec, const float* lr5, float beta1, float beta2,
-                               float eps, const isogs_adam_state* state, const int32_t* skip, cudaStream_t stream);
 int launch_outlier_threshold(const isogs_camera* cam, const float* render_depth, const float* gt_depth,
                              const isogs_frame* frame_dev, float factor, float* scratch, void* sort_temp,
                              size_t sort_temp_bytes, float* thresh_out, cudaStream_t stream);
@@ -57,10 +51,8 @@ int check_common(const isogs_camera* cam, const isogs_frame* frame, const isogs_
 }
 
 // preprocess (raw parameters, frame transform fused) -> sync-free binning -> 5-channel blend
-// loss_mode >= 0: the masked-L1 loss rides in the blend forward's epilogue (v_render + loss scalars written there)
 int forward(const isogs_camera* cam, const float* pose_dev, const isogs_workspace* ws, const isogs_gaussians* gs,
-            void* const* ev, cudaStream_t st, const isogs_frame* frame = nullptr, int loss_mode = -1, float w_im = 0.f,
-            float w_depth = 0.f, float sil_thres = 0.f, int use_sil = 1) {
+            void* const* ev, cudaStream_t st) {
     const float* quats = gs->scale_dim == 3 ? gs->p[2] : nullptr;
     // with the rect rows available the per-tile counts are accumulated by the projection kernel itself: the counters
     // (the head of sort_temp, where the binning keeps them) are cleared first
@@ -78,11 +70,7 @@ int forward(const isogs_camera* cam, const float* pose_dev, const isogs_workspac
                                    ws->ranges, ws->totals, ws->sort_temp, ws->sort_temp_bytes, ws->tile_rects,
                                    fused_count ? 1 : 0, st));
     ISOGS_TRY(mark(ev, 2, st));
-    if (loss_mode >= 0)
-        ISOGS_TRY(launch_blend_fwd_loss(cam, ws->rec, ws->vals, ws->ranges, ws->render, ws->alpha, ws->last, frame, loss_mode,
-                                        w_im, w_depth, sil_thres, use_sil, ws->v_render, ws->small, st));
-    else
-        ISOGS_TRY(isogs_blend_fwd(cam, 5, ws->rec, ws->vals, ws->ranges, ws->render, ws->alpha, ws->last, st));
+    ISOGS_TRY(isogs_blend_fwd(cam, 5, ws->rec, ws->vals, ws->ranges, ws->render, ws->alpha, ws->last, st));
     ISOGS_TRY(mark(ev, 3, st));
     return ISOGS_OK;
 }
@@ -99,13 +87,12 @@ extern "C" int isogs_map_step(const isogs_camera* cam, const isogs_frame* frame,
     if (ssim && !ws->dmaps) { set_error("isogs_map_step: ISOGS_STEP_SSIM needs ws->dmaps"); return ISOGS_E_ARG; }
     const float* pose_dev = reinterpret_cast<const float*>(reinterpret_cast<const char*>(frame) + offsetof(isogs_frame, pose));
     float* losses = ws->small;
-    bool inline_adam = false;
     if (prm->phases & ISOGS_PHASE_RENDER) {
         ISOGS_TRY(mark(ev, 0, st));
         ISOGS_TRY(isogs_step_begin(ws->small, SMALL, ws->adam_state, prm->beta1, prm->beta2, st));
-        (void)losses;
-        ISOGS_TRY(forward(cam, pose_dev, ws, gs, ev, st, frame, 1, ssim ? 0.8f * prm->w_im : prm->w_im, prm->w_depth,
-                          prm->sil_thres, 1));
+        ISOGS_TRY(forward(cam, pose_dev, ws, gs, ev, st));
+        ISOGS_TRY(launch_loss_l1(cam, 1, ws->render, ws->alpha, nullptr, nullptr, frame, ssim ? 0.8f * prm->w_im : prm->w_im,
+                                 prm->w_depth, prm->sil_thres, 1, 1.0f, nullptr, ws->v_render, losses, st));
         ISOGS_TRY(mark(ev, 4, st));
         if (ssim)
             ISOGS_TRY(launch_ssim_loss(cam, ws->render, nullptr, frame, 0.2f * prm->w_im, ws->dmaps, ws->v_render, losses,
@@ -115,24 +102,13 @@ extern "C" int isogs_map_step(const isogs_camera* cam, const isogs_frame* frame,
             ISOGS_TRY(isogs_blend_bwd(cam, 5, gs->N, ws->rec, ws->vals, ws->ranges, ws->alpha, ws->last, ws->v_render,
                                       nullptr, ws->v_rec, st));
         ISOGS_TRY(mark(ev, 6, st));
-        // both phases in one call (no exchange / extra loss terms between backward and optimizer): the projection backward
-        // applies Adam in place and the gradients never travel through HBM
-        bool have_state = ws->adam_state != nullptr && gs->N > 0;
-        for (int k = 0; k < 5; ++k)
-            if (k != 2 || gs->scale_dim == 3) have_state = have_state && gs->m[k] && gs->v[k];
-        inline_adam = (prm->phases & ISOGS_PHASE_ADAM) && !(prm->flags & ISOGS_STEP_KEEP_GRADS) && have_state;
-        if (inline_adam) {
-            ISOGS_TRY(launch_preprocess_bwd_adam(cam, pose_dev, gs, 5, FLAGS_RAW, ws->radii, ws->v_rec, prm->lr, prm->beta1,
-                                                 prm->beta2, prm->eps, ws->adam_state, ws->totals + 1, st));
-        } else {
-            const float* quats = gs->scale_dim == 3 ? gs->p[2] : nullptr;
-            ISOGS_TRY(isogs_preprocess_bwd(cam, nullptr, pose_dev, gs->N, gs->p[0], gs->p[4], gs->scale_dim, quats, gs->p[3], 5,
-                                           FLAGS_RAW, ws->radii, ws->v_rec, gs->g[0], gs->g[4], gs->g[2], gs->g[3], gs->g[1],
-                                           nullptr, nullptr, nullptr, st));
-        }
+        const float* quats = gs->scale_dim == 3 ? gs->p[2] : nullptr;
+        ISOGS_TRY(isogs_preprocess_bwd(cam, nullptr, pose_dev, gs->N, gs->p[0], gs->p[4], gs->scale_dim, quats, gs->p[3], 5,
+                                       FLAGS_RAW, ws->radii, ws->v_rec, gs->g[0], gs->g[4], gs->g[2], gs->g[3], gs->g[1],
+                                       nullptr, nullptr, nullptr, st));
         ISOGS_TRY(mark(ev, 7, st));
     }
-    if ((prm->phases & ISOGS_PHASE_ADAM) && !inline_adam) {
+    if (prm->phases & ISOGS_PHASE_ADAM) {
         isogs_adam_group grp[5];
         int n = 0;
         for (int k = 0; k < 5; ++k) {
@@ -144,8 +120,8 @@ extern "C" int isogs_map_step(const isogs_camera* cam, const isogs_frame* frame,
             ++n;
         }
         ISOGS_TRY(isogs_adam_fused(grp, n, prm->beta1, prm->beta2, prm->eps, 1, ws->adam_state, ws->totals + 1, st));
+        ISOGS_TRY(mark(ev, 8, st));
     }
-    if (prm->phases & ISOGS_PHASE_ADAM) ISOGS_TRY(mark(ev, 8, st));
     return ISOGS_OK;
 }
 
@@ -166,17 +142,13 @@ extern "C" int isogs_track_step(const isogs_camera* cam, const isogs_frame* fram
     float* thr = ws->small + 28;
     ISOGS_TRY(mark(ev, 0, st));
     ISOGS_TRY(isogs_step_begin(ws->small, SMALL, pose_state, prm->beta1, prm->beta2, st));
-    const int use_sil = (prm->flags & ISOGS_STEP_NO_SIL) ? 0 : 1;
-    if (!outlier) {
-        ISOGS_TRY(forward(cam, pose, ws, gs, ev, st, frame, 0, prm->w_im, prm->w_depth, prm->sil_thres, use_sil));
-    } else {
-        // the mask needs 10 x the median depth error of the finished render (splatam.py:552-553): loss as its own pass
-        ISOGS_TRY(forward(cam, pose, ws, gs, ev, st));
+    ISOGS_TRY(forward(cam, pose, ws, gs, ev, st));
+    if (outlier)   // 10 x median depth error (splatam.py:552-553), device-side, ground truth through the frame slot
         ISOGS_TRY(launch_outlier_threshold(cam, ws->render + 3 * (size_t)cam->width * cam->height, nullptr, frame, 10.0f,
                                            ws->median_scratch, ws->median_temp, ws->median_temp_bytes, thr, st));
-        ISOGS_TRY(launch_loss_l1(cam, 0, ws->render, ws->alpha, nullptr, nullptr, frame, prm->w_im, prm->w_depth,
-                                 prm->sil_thres, use_sil, 1.0f, thr, ws->v_render, losses, st));
-    }
+    ISOGS_TRY(launch_loss_l1(cam, 0, ws->render, ws->alpha, nullptr, nullptr, frame, prm->w_im, prm->w_depth,
+                             prm->sil_thres, (prm->flags & ISOGS_STEP_NO_SIL) ? 0 : 1, 1.0f, outlier ? thr : nullptr,
+                             ws->v_render, losses, st));
     ISOGS_TRY(mark(ev, 4, st));
     ISOGS_TRY(mark(ev, 5, st));
     if (gs->N > 0)

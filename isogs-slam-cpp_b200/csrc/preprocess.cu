@@ -91,20 +91,6 @@ preprocess_fwd_kernel(DevCam cam, DevPose pose, int64_t N, const float* __restri
 // backward
 // ---------------------------------------------------------------------------------------------
 
-// Inline optimizer step (single-GPU mapping): the thread that holds Gaussian i's gradients applies Adam to its
-// parameters directly -- the 32 MB gradient write, its re-read and the adam_kernel launch disappear.  Parameter group
-// order as isogs_gaussians: 0 means3D, 1 rgb_colors, 2 unnorm_rotations, 3 logit_opacities, 4 log_scales.
-struct AdamInline {
-    int enabled;
-    float* colors;              // rgb_colors (the backward itself does not read them)
-    float* m[5];
-    float* v[5];
-    float lr[5];
-    float b2, one_minus_b1, one_minus_b2, eps;
-    const isogs_adam_state* state;
-    const int32_t* skip;
-};
-
 // pose_acc layout: [0..8] dL/dRp, [9..11] dL/dtp, [12..15] dL/dqn (through quat_mul, aniso only)
 template <bool ISO>
 __global__ void __launch_bounds__(256)
@@ -113,7 +99,7 @@ preprocess_bwd_kernel(DevCam cam, DevPose pose, int64_t N, const float* __restri
                       const float* __restrict__ opacities, int ch, int flags, const int2* __restrict__ radii,
                       const float4* __restrict__ v_rec, float* __restrict__ v_means, float* __restrict__ v_scales,
                       float* __restrict__ v_quats, float* __restrict__ v_opac, float* __restrict__ v_colors,
-                      float* __restrict__ v_means2d, float* __restrict__ pose_acc, AdamInline ad) {
+                      float* __restrict__ v_means2d, float* __restrict__ pose_acc) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     constexpr int SD = ISO ? 1 : 3;
     constexpr int NACC = ISO ? 12 : 16;
@@ -311,35 +297,6 @@ preprocess_bwd_kernel(DevCam cam, DevPose pose, int64_t N, const float* __restri
             v_means2d[3 * i + 1] = vxy[1] * (0.5f * (float)cam.height);
             v_means2d[3 * i + 2] = 0.f;
         }
-        if (ad.enabled && !(ad.skip != nullptr && *ad.skip != 0)) {
-            // torch.optim.Adam updates EVERY element that has a gradient tensor, also where the gradient is zero
-            // (culled splats: the moments decay and the momentum keeps moving the parameter)
-            const float ib2 = (float)ad.state->inv_bc2_sqrt;
-            const double ibc1 = ad.state->inv_bc1;
-            float* pm = const_cast<float*>(means);
-            float* ps = const_cast<float*>(scales);
-            float* po = const_cast<float*>(opacities);
-            auto upd = [&](float* p, float* mm, float* vv, int64_t idx, float g, float ss) {
-                float pv = p[idx], mv = mm[idx], vvv = vv[idx];
-                adam_update(pv, g, mv, vvv, ad.one_minus_b1, ad.b2, ad.one_minus_b2, ib2, ad.eps, ss);
-                p[idx] = pv; mm[idx] = mv; vv[idx] = vvv;
-            };
-            const float ss0 = (float)((double)ad.lr[0] * ibc1), ss1 = (float)((double)ad.lr[1] * ibc1);
-            const float ss3 = (float)((double)ad.lr[3] * ibc1), ss4 = (float)((double)ad.lr[4] * ibc1);
-#pragma unroll
-            for (int k = 0; k < 3; ++k) upd(pm, ad.m[0], ad.v[0], 3 * i + k, vm[k], ss0);
-#pragma unroll
-            for (int k = 0; k < 3; ++k) upd(ad.colors, ad.m[1], ad.v[1], 3 * i + k, vc[k], ss1);
-            if (!ISO) {
-                const float ss2 = (float)((double)ad.lr[2] * ibc1);
-                float* pq = const_cast<float*>(quats);
-#pragma unroll
-                for (int k = 0; k < 4; ++k) upd(pq, ad.m[2], ad.v[2], 4 * i + k, vq[k], ss2);
-            }
-            upd(po, ad.m[3], ad.v[3], i, vo, ss3);
-#pragma unroll
-            for (int k = 0; k < SD; ++k) upd(ps, ad.m[4], ad.v[4], SD * i + k, vs[k], ss4);
-        }
     }
     // N -> 7 pose reduction: warp shuffle, then shared, then one atomic per block per component
     if (pose_acc != nullptr && xf.has_pose) {
@@ -439,48 +396,13 @@ extern "C" int isogs_preprocess_fwd(const isogs_camera* cam, const isogs_pose* p
     return ISOGS_OK;
 }
 
-namespace isogs {
-static int preprocess_bwd_impl(const isogs_camera* cam, const isogs_pose* pose, const float* pose_dev, int64_t N,
-                               const float* means, const float* scales, int scale_dim, const float* quats,
-                               const float* opacities, int ch, int flags, const int32_t* radii, const float* v_rec,
-                               float* v_means, float* v_scales, float* v_quats, float* v_opac, float* v_colors,
-                               float* v_means2d, float* v_pose, float* pose_acc, const AdamInline& ad, cudaStream_t stream);
-
-// projection backward with the optimizer step applied in place (fused_step.cu, single-GPU mapping)
-int launch_preprocess_bwd_adam(const isogs_camera* cam, const float* pose_dev, const isogs_gaussians* gs, int ch, int flags,
-                               const int32_t* radii, const float* v_rec, const float* lr5, float beta1, float beta2,
-                               float eps, const isogs_adam_state* state, const int32_t* skip, cudaStream_t stream) {
-    AdamInline ad{};
-    ad.enabled = 1;
-    ad.colors = gs->p[1];
-    for (int k = 0; k < 5; ++k) { ad.m[k] = gs->m[k]; ad.v[k] = gs->v[k]; ad.lr[k] = lr5[k]; }
-    ad.b2 = beta2; ad.one_minus_b1 = 1.0f - beta1; ad.one_minus_b2 = 1.0f - beta2; ad.eps = eps;
-    ad.state = state; ad.skip = skip;
-    const float* quats = gs->scale_dim == 3 ? gs->p[2] : nullptr;
-    return preprocess_bwd_impl(cam, nullptr, pose_dev, gs->N, gs->p[0], gs->p[4], gs->scale_dim, quats, gs->p[3], ch, flags,
-                               radii, v_rec, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, ad,
-                               stream);
-}
-} // namespace isogs
-
 extern "C" int isogs_preprocess_bwd(const isogs_camera* cam, const isogs_pose* pose, const float* pose_dev,
                                     int64_t N, const float* means, const float* scales, int scale_dim,
                                     const float* quats, const float* opacities, int ch, int flags,
                                     const int32_t* radii, const float* v_rec, float* v_means, float* v_scales,
                                     float* v_quats, float* v_opac, float* v_colors, float* v_means2d,
                                     float* v_pose, float* pose_acc, void* stream_) {
-    AdamInline none{};
-    return preprocess_bwd_impl(cam, pose, pose_dev, N, means, scales, scale_dim, quats, opacities, ch, flags, radii, v_rec,
-                               v_means, v_scales, v_quats, v_opac, v_colors, v_means2d, v_pose, pose_acc, none,
-                               (cudaStream_t)stream_);
-}
-
-static int isogs::preprocess_bwd_impl(const isogs_camera* cam, const isogs_pose* pose, const float* pose_dev, int64_t N,
-                                      const float* means, const float* scales, int scale_dim, const float* quats,
-                                      const float* opacities, int ch, int flags, const int32_t* radii, const float* v_rec,
-                                      float* v_means, float* v_scales, float* v_quats, float* v_opac, float* v_colors,
-                                      float* v_means2d, float* v_pose, float* pose_acc, const AdamInline& ad,
-                                      cudaStream_t stream) {
+    cudaStream_t stream = (cudaStream_t)stream_;
     if (!cam || N < 0 || (scale_dim != 1 && scale_dim != 3) || (ch != 4 && ch != 5) || (scale_dim == 3 && !quats)) {
         set_error("isogs_preprocess_bwd: bad argument");
         return ISOGS_E_ARG;
@@ -500,12 +422,12 @@ static int isogs::preprocess_bwd_impl(const isogs_camera* cam, const isogs_pose*
         preprocess_bwd_kernel<true><<<grid, block, 0, stream>>>(dc, dp, N, means, scales, quats, opacities, ch, flags,
                                                                  (const int2*)radii, (const float4*)v_rec, v_means,
                                                                  v_scales, v_quats, v_opac, v_colors, v_means2d,
-                                                                 want_pose ? pose_acc : nullptr, ad);
+                                                                 want_pose ? pose_acc : nullptr);
     else
         preprocess_bwd_kernel<false><<<grid, block, 0, stream>>>(dc, dp, N, means, scales, quats, opacities, ch, flags,
                                                                   (const int2*)radii, (const float4*)v_rec, v_means,
                                                                   v_scales, v_quats, v_opac, v_colors, v_means2d,
-                                                                  want_pose ? pose_acc : nullptr, ad);
+                                                                  want_pose ? pose_acc : nullptr);
     ISOGS_CUDA(cudaGetLastError());
     if (want_pose) {
         pose_finish_kernel<<<1, 32, 0, stream>>>(dp, pose_acc, v_pose);

@@ -491,16 +491,14 @@ def _graph_launch(ws, key, enqueue):
 
 
 def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, allreduce=None, marks=None, w_im=0.5,
-             w_depth=1.0, ssim=False, isoflat=False, iso_seed=0, graph=False, eps=1e-15, keep_grads=False):
+             w_depth=1.0, ssim=False, isoflat=False, iso_seed=0, graph=False, eps=1e-15):
     """One mapping iteration on one keyframe (splatam.py:1412-1476): ONE host call (isogs_map_step) enqueues
     transform_to_frame + activations + projection, binning, the 5-channel blend, the masked-L1 (+ SSIM) loss, both
     backwards and the fused Adam; no host sync.  `pose` is the keyframe's HOST pose (camera_grad=False).
     `allreduce(flat_grad_tensor)` runs between backward and Adam, as do the iso / flat terms (`isoflat=True`, :572-675,
     three-axis scales) -- with ssim and isoflat the loss is the reference's complete mapping loss.  `marks` (a list)
     receives (stage, cuda event) pairs.  graph=True replays a captured CUDA graph of the step: one graph serves
-    every keyframe, because the frame is read through the device-side slot ws.cur_frame.  Without an exchange / extra
-    loss terms the projection backward applies Adam in place and the gradients never reach HBM: keep_grads=True
-    writes them to gmap.g as well (tests, densification statistics that want the parameter gradients)."""
+    every keyframe, because the frame is read through the device-side slot ws.cur_frame."""
     if ssim and ws.dmaps is None:
         ws.dmaps = torch.empty((9, ws.cam.height, ws.cam.width), dtype=torch.float32, device=ws.device)
     ws.check_overflow()
@@ -508,7 +506,7 @@ def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, all
     frame = ws.frame(gt_rgb, gt_depth, pose, inv_n_depth)
     cws, cgs = ws.c_struct(), gmap.c_struct()
     cws.adam_state = gmap.adam_state.data_ptr()
-    flags = (_lib.STEP_SSIM if ssim else 0) | (_lib.STEP_KEEP_GRADS if keep_grads else 0)
+    flags = _lib.STEP_SSIM if ssim else 0
     lr5 = [lrs.get(k, 0.0) for k in PARAM_ORDER]
     split = allreduce is not None or isoflat
     ev = _event_array(marks)
@@ -530,8 +528,6 @@ def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, all
         if allreduce is not None and hasattr(allreduce, "fused_adam"):
             # exchange fused with the optimizer step (dp.PeerReduceAdam): no separate Adam launch
             allreduce.fused_adam(gmap, lrs, eps)
-            if marks is not None:                  # this path has no separate Adam launch: drop its (unrecorded) mark
-                marks[:] = [m for m in marks if m[0] != "adam"]
             _mark(marks, "allreduce")
             ws.post_totals()
             return ws.losses

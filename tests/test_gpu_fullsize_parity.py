@@ -119,7 +119,7 @@ def test_map_and_track_step_match_oracle_at_full_size(pkg, orc, syn, ss, scene):
     before = {k: v.copy() for k, v in st["p"].items()}
     loss_m = osl.map_iteration(orc, ocam, st, q, tr, rgb_m, depth_m, grads_out=g_ref)
     inv_nd = 1.0 / max(1, int((depth_m > 0).sum()))
-    losses = ss.map_step(ws, gmap, pkg.make_pose(q, tr), grgb, gdepth, inv_nd, keep_grads=True)
+    losses = ss.map_step(ws, gmap, pkg.make_pose(q, tr), grgb, gdepth, inv_nd)
     torch.cuda.synchronize()
     assert not ws.check_overflow(wait=True)
     assert abs(float(losses[0]) - loss_m) <= 1e-4 * max(1.0, abs(loss_m))

@@ -350,7 +350,7 @@ def test_map_step_matches_oracle(pkg, orc, syn, ss):
         p_before = {kk: v.copy() for kk, v in st["p"].items()}
         lo = osl.map_iteration(orc, ocam, st, q, tr, rgb, depth, grads_out=g_ref)
         inv_nd = 1.0 / max(1, int((depth > 0).sum()))
-        losses = ss.map_step(ws, gmap, pkg.make_pose(q, tr), t(rgb), t(depth), inv_nd, keep_grads=True)
+        losses = ss.map_step(ws, gmap, pkg.make_pose(q, tr), t(rgb), t(depth), inv_nd)
         torch.cuda.synchronize()
         assert abs(float(losses[0]) - lo) <= 1e-4 * max(1.0, abs(lo))
         assert not ws.check_overflow(wait=True)
