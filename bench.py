@@ -190,10 +190,10 @@ def algorithmic_bytes(N, V, M, P, n_tiles):
 
 def launches_per_step(world, ssim=False):
     """Own kernels enqueued by one isogs_map_step (csrc/fused_step.cu): step_begin, preprocess_fwd, tile_count,
-    tile_scan, tile_scatter, tile_sort_reg, tile_sort, blend_fwd, loss_l1, blend_bwd, preprocess_bwd, adam
-    (+ ssim fwd / bwd; + the two-shot peer all-reduce and its wait at N > 1).  Checked against the ncu launch
-    list under profiles/."""
-    return 12 + (2 if ssim else 0) + (2 if world > 1 else 0)   # N > 1, fused exchange: +2 exchange kernels, -1 Adam
+    (tile counts fused), tile_scan, tile_scatter, tile_sort_merge, tile_sort (long tiles), blend_fwd, loss_l1, blend_bwd,
+    preprocess_bwd, adam = 11; + ssim fwd / bwd; at N > 1 the exchange kernel (reduce + Adam, replacing the Adam launch)
+    and its wait.  Checked against the ncu launch list under profiles/."""
+    return 11 + (2 if ssim else 0) + (1 if world > 1 else 0)
 
 
 _JSON_FD = 1

@@ -175,6 +175,18 @@ __device__ __forceinline__ void quat_mul(const float* a, const float* b, float* 
     o[3] = ((a[0] * b[3] + a[1] * b[2]) - a[2] * b[1]) + a[3] * b[0];
 }
 
+// One Adam element update with torch.optim.Adam semantics (bias corrections folded into step_size / inv_bc2_sqrt by the
+// caller); the ONE definition used by adam_kernel (step.cu), the projection backward's inline optimizer step
+// (preprocess.cu) and the fused exchange (peer.cu), so all three produce the same bits.
+__device__ __forceinline__ void adam_update(float& p, float g, float& m, float& v, float one_minus_b1, float b2,
+                                            float one_minus_b2, float inv_bc2_sqrt, float eps, float step_size) {
+    const float mi = m + (g - m) * one_minus_b1;
+    const float vi = v * b2 + one_minus_b2 * g * g;
+    m = mi; v = vi;
+    const float denom = sqrtf(vi) * inv_bc2_sqrt + eps;
+    p = p - step_size * (mi / denom);
+}
+
 struct Rect { int x0, y0, x1, y1; };
 // IntersectTile.cu:66-77; float->int conversion saturates on the GPU, written as the signed clamp
 __device__ __forceinline__ Rect tile_rect(float mx, float my, int rx, int ry, int tw, int th) {

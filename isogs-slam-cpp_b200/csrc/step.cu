@@ -125,11 +125,7 @@ constexpr int ADAM_BLOCK = 256, ADAM_VEC = 4;
 
 __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamArgs& a, float step_size,
                                          float inv_bc2_sqrt) {
-    const float mi = m + (g - m) * a.one_minus_b1;
-    const float vi = v * a.b2 + a.one_minus_b2 * g * g;
-    m = mi; v = vi;
-    const float denom = sqrtf(vi) * inv_bc2_sqrt + a.eps;
-    p = p - step_size * (mi / denom);
+    adam_update(p, g, m, v, a.one_minus_b1, a.b2, a.one_minus_b2, inv_bc2_sqrt, a.eps, step_size);
 }
 
 __global__ void __launch_bounds__(ADAM_BLOCK) adam_kernel(AdamArgs a) {

@@ -528,6 +528,8 @@ def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, all
         if allreduce is not None and hasattr(allreduce, "fused_adam"):
             # exchange fused with the optimizer step (dp.PeerReduceAdam): no separate Adam launch
             allreduce.fused_adam(gmap, lrs, eps)
+            if marks is not None:                  # this path has no separate Adam launch: drop its (unrecorded) mark
+                marks[:] = [m for m in marks if m[0] != "adam"]
             _mark(marks, "allreduce")
             ws.post_totals()
             return ws.losses

@@ -1,14 +1,16 @@
-# Multi-GPU check on an N-GPU box: mapping bench with the peer-memory gradient average and with NCCL, the
-# two-process IPC test.  Usage (on the GPU box): bash scripts/scale_check.sh <tag> <n_gpus>
-TAG=${1:-r1x}; N=${2:-8}
-run() { # $1 = ranks, $2 = out suffix, rest = extra bench flags
-  local n=$1 suf=$2; shift 2
-  timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29500 + n)) \
-    bench.py --gpus $n --steps 50 --warmup 5 "$@" > gpurun_out/${TAG}_bench_${suf}.json 2> gpurun_out/${TAG}_bench_${suf}.err
-  echo "rc=$? ${suf}: $(cut -c1-330 gpurun_out/${TAG}_bench_${suf}.json)"
-}
-run $N ${N}gpu
-run $N ${N}gpu_nccl --allreduce nccl
-if [ -n "$SCALE_PEER_TEST" ]; then timeout 200 python -m pytest tests/test_gpu_peer.py -q -m gpu 2>&1 | tail -3 > gpurun_out/${TAG}_pytest_peer.log; cat gpurun_out/${TAG}_pytest_peer.log; fi
-if [ $N -gt 4 ]; then run 4 4gpu; fi
-if [ $N -gt 2 ]; then run 2 2gpu; fi
+# Multi-GPU check on an N-GPU box: sharded parity test, then the bench with each exchange variant.
+# Usage: gpurun --gpus N -- bash scripts/scale_check.sh <tag> N
+TAG=$1; N=$2
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_multi.py -q -s > gpurun_out/${TAG}_multi_pytest.log 2>&1; grep -E "MULTI_GPU_PARITY|passed|failed|skipped" gpurun_out/${TAG}_multi_pytest.log | cut -c1-700
+for mode in fused p2p nccl; do
+  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29577 bench.py --gpus $N --steps 20 --warmup 5 --allreduce $mode > gpurun_out/${TAG}_bench_${N}gpu_$mode.json 2> gpurun_out/${TAG}_bench_${N}gpu_$mode.err || tail -5 gpurun_out/${TAG}_bench_${N}gpu_$mode.err
+  python - <<PY
+import json
+try:
+    d=json.load(open("gpurun_out/${TAG}_bench_${N}gpu_$mode.json"))
+    print("$mode", round(d["value"],1), round(d["ms_per_step"],4), "e2e", round(d["e2e"]["value"],1), d["stage_ms"], d.get("rank_stats"), d["config"]["replicas_identical_after_run"])
+except Exception as e:
+    print("$mode: no json", e)
+PY
+done
