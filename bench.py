@@ -189,8 +189,8 @@ def algorithmic_bytes(N, V, M, P, n_tiles):
 
 
 def launches_per_step(world, ssim=False):
-    """Own kernels enqueued by one isogs_map_step (csrc/fused_step.cu): step_begin, preprocess_fwd, tile_count,
-    (tile counts fused), tile_scan, tile_scatter, tile_sort_merge, tile_sort (long tiles), blend_fwd, loss_l1, blend_bwd,
+    """Own kernels enqueued by one isogs_map_step (csrc/fused_step.cu): step_begin, preprocess_fwd (tile counts fused),
+    tile_scan, tile_scatter, tile_sort_merge, tile_sort (long tiles), blend_fwd, loss_l1, blend_bwd,
     preprocess_bwd, adam = 11; + ssim fwd / bwd; at N > 1 the exchange kernel (reduce + Adam, replacing the Adam launch)
     and its wait.  Checked against the ncu launch list under profiles/."""
     return 11 + (2 if ssim else 0) + (1 if world > 1 else 0)

@@ -28,6 +28,10 @@ constexpr unsigned FULL = 0xffffffffu;
 constexpr int WARPS = 2;   // half tiles (16x8 pixels, one warp each) per tile = per CTA
 constexpr int THREADS = 32 * WARPS;
 constexpr int NW_DEFAULT = 8; // ring words per warp (256 staged Gaussians, 14 KB): 7-8 CTAs per SM
+// (quad, Gaussian) pairs a lane evaluates per warp iteration (both from its current ring word): two in the backward
+// amortise the cursor / retire bookkeeping and interleave two bodies (0.388 -> 0.379 ms, 124 registers); in the
+// lighter forward the second slot idles too often and costs more than it saves (0.267 -> 0.305 ms)
+constexpr int HITS_FWD = 1, HITS_BWD = 2;
 constexpr int FAR = 0x01000000;
 
 template <int NW, bool WITH_ID = true>
@@ -169,8 +173,18 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+// one (quad, Gaussian) pair being evaluated by a lane
+struct Hit {
+    float4 g0, g1;
+    float dx[2], dy[2], sigma[4];
+    unsigned slot;
+    int e;
+    bool valid[4], any;
+};
+
 // GEOM = true: tracking -- only the gradient components the POSE depends on (x, y, conic, z, z^2) are produced.
-template <int CH, int NW, bool GEOM>
+// HITS: (quad, Gaussian) pairs a lane evaluates per warp iteration.
+template <int CH, int NW, bool GEOM, int HITS>
 __global__ void __launch_bounds__(THREADS, 8)
 blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
                     const int32_t* __restrict__ ranges, const float* __restrict__ alpha,
@@ -244,78 +258,92 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
         const bool act = bits != 0u;
         const int wmin = __reduce_min_sync(FULL, act ? jq : jq + 1);
         if (wmin >= n_words) break;
-        const int s = act ? __ffs(bits) - 1 : 0;
-        bits &= bits - 1u;
-        const unsigned slot = wsl + s;
-        const float4 g0s = st.g0[slot];
-        const float4 g1s = st.g1[slot];
-        const int e = act ? 32 * jq + s : -1;
-        const float dxa = __fsub_rn(g0s.x, pxa), dxb = __fsub_rn(g0s.x, pxb);
-        const float dya = __fsub_rn(g0s.y, pya), dyb = __fsub_rn(g0s.y, pyb);
-        const float zxa = __fmul_rn(g0s.z, dxa), zxb = __fmul_rn(g0s.z, dxb);
-        const float cya = __fmul_rn(__fmul_rn(g1s.x, dya), dya), cyb = __fmul_rn(__fmul_rn(g1s.x, dyb), dyb);
-        float sigma[4];
-        sigma[0] = __fmaf_rn(__fmaf_rn(g0s.w, dya, zxa), dxa, cya);
-        sigma[1] = __fmaf_rn(__fmaf_rn(g0s.w, dya, zxb), dxb, cya);
-        sigma[2] = __fmaf_rn(__fmaf_rn(g0s.w, dyb, zxa), dxa, cyb);
-        sigma[3] = __fmaf_rn(__fmaf_rn(g0s.w, dyb, zxb), dxb, cyb);
-        bool valid[4];
-        bool anyv = false;
+        // up to HITS hits of this quad (from its current ring word) per warp iteration: the cursor / retire bookkeeping
+        // is amortised over them and their arithmetic interleaves (the per-pixel T / bdot recurrences chain hit b
+        // behind hit a, everything else is independent)
+        Hit h[HITS];
 #pragma unroll
-        for (int p = 0; p < 4; ++p) {
-            valid[p] = e >= first[p] && sigma[p] >= 0.f && sigma[p] <= g1s.y;
-            anyv |= valid[p];
-        }
-        if (__any_sync(FULL, anyv)) {
-            const float4 g2 = st.g2[slot];
-            const float opac = g1s.z;
-            float Swx = 0.f, Swy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f, Su = 0.f;
-            float col[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int k = 0; k < HITS; ++k) {
+            const bool on = bits != 0u;
+            const int sk = on ? __ffs(bits) - 1 : 0;
+            bits &= bits - 1u;
+            h[k].slot = wsl + sk;
+            h[k].e = on ? 32 * jq + sk : -1;
+            h[k].g0 = st.g0[h[k].slot];
+            h[k].g1 = st.g1[h[k].slot];
+            h[k].dx[0] = __fsub_rn(h[k].g0.x, pxa); h[k].dx[1] = __fsub_rn(h[k].g0.x, pxb);
+            h[k].dy[0] = __fsub_rn(h[k].g0.y, pya); h[k].dy[1] = __fsub_rn(h[k].g0.y, pyb);
+            const float zxa = __fmul_rn(h[k].g0.z, h[k].dx[0]), zxb = __fmul_rn(h[k].g0.z, h[k].dx[1]);
+            const float cya = __fmul_rn(__fmul_rn(h[k].g1.x, h[k].dy[0]), h[k].dy[0]);
+            const float cyb = __fmul_rn(__fmul_rn(h[k].g1.x, h[k].dy[1]), h[k].dy[1]);
+            h[k].sigma[0] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[0], zxa), h[k].dx[0], cya);
+            h[k].sigma[1] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[0], zxb), h[k].dx[1], cya);
+            h[k].sigma[2] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[1], zxa), h[k].dx[0], cyb);
+            h[k].sigma[3] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[1], zxb), h[k].dx[1], cyb);
+            h[k].any = false;
 #pragma unroll
             for (int p = 0; p < 4; ++p) {
-                const float dx = (p & 1) ? dxb : dxa, dy = (p >> 1) ? dyb : dya;
-                // branch-free: an invalid pixel runs with sigma = 0 and contributes exact zeros
-                const float vis = __expf(valid[p] ? -sigma[p] : 0.f);
-                const float ov = opac * vis;
-                const float a = fminf(MAX_ALPHA, ov);
-                const float ra = __fdividef(1.0f, 1.0f - a);
-                const float Tn = T[p] * ra; // transmittance in front of this Gaussian
-                T[p] = valid[p] ? Tn : T[p];
-                const float fac = valid[p] ? a * Tn : 0.f;
-                float cdot = g1s.w * vr[p][0];
-                cdot = fmaf(g2.x, vr[p][1], cdot);
-                cdot = fmaf(g2.y, vr[p][2], cdot);
-                cdot = fmaf(g2.z, vr[p][3], cdot);
-                if (CH == 5) cdot = fmaf(g2.w, vr[p][CH - 1], cdot);
-                const float v_a = fmaf(Tn, cdot, ra * (va_eff[p] - bdot[p]));
-                bdot[p] = fmaf(fac, cdot, bdot[p]);
-                const float u = (valid[p] && ov <= MAX_ALPHA) ? vis * v_a : 0.f;
-                const float v_sigma = -opac * u;
-                const float wx = v_sigma * dx, wy = v_sigma * dy;
-                Swx += wx;
-                Swy += wy;
-                Sxx = fmaf(wx, dx, Sxx);
-                Sxy = fmaf(wx, dy, Sxy);
-                Syy = fmaf(wy, dy, Syy);
-                if (!GEOM) {
-                    Su += u;
-#pragma unroll
-                    for (int k = 0; k < 3; ++k) col[k] = fmaf(fac, vr[p][k], col[k]);
-                }
-#pragma unroll
-                for (int k = 3; k < CH; ++k) col[k] = fmaf(fac, vr[p][k], col[k]);
+                h[k].valid[p] = h[k].e >= first[p] && h[k].sigma[p] >= 0.f && h[k].sigma[p] <= h[k].g1.y;
+                h[k].any |= h[k].valid[p];
             }
-            if (anyv) {
-                const float ca = 2.0f * g0s.z, cb = g0s.w, cc = 2.0f * g1s.x;
-                const float v0 = fmaf(ca, Swx, cb * Swy), v1 = fmaf(cb, Swx, cc * Swy);
-                float* dst = v_rec + (int64_t)st.id[slot] * REC;
-                red_add_v4(dst, v0, v1, 0.5f * Sxx, Sxy);
-                if (GEOM) {
-                    atomicAdd(dst + 4, 0.5f * Syy);
-                    red_add_v4(dst + 8, 0.f, col[3], col[4], 0.f);
-                } else {
-                    red_add_v4(dst + 4, 0.5f * Syy, Su, col[0], col[1]);
-                    red_add_v4(dst + 8, col[2], col[3], col[4], 0.f);
+        }
+        bool anyv = h[0].any;
+#pragma unroll
+        for (int k = 1; k < HITS; ++k) anyv |= h[k].any;
+        if (__any_sync(FULL, anyv)) {
+#pragma unroll
+            for (int k = 0; k < HITS; ++k) {
+                const Hit& hk = h[k];
+                const float4 g2 = st.g2[hk.slot];
+                const float opac = hk.g1.z;
+                float Swx = 0.f, Swy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f, Su = 0.f;
+                float col[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int p = 0; p < 4; ++p) {
+                    const float dx = hk.dx[p & 1], dy = hk.dy[p >> 1];
+                    // branch-free: an invalid pixel runs with sigma = 0 and contributes exact zeros
+                    const float vis = __expf(hk.valid[p] ? -hk.sigma[p] : 0.f);
+                    const float ov = opac * vis;
+                    const float a = fminf(MAX_ALPHA, ov);
+                    const float ra = __fdividef(1.0f, 1.0f - a);
+                    const float Tn = T[p] * ra; // transmittance in front of this Gaussian
+                    T[p] = hk.valid[p] ? Tn : T[p];
+                    const float fac = hk.valid[p] ? a * Tn : 0.f;
+                    float cdot = hk.g1.w * vr[p][0];
+                    cdot = fmaf(g2.x, vr[p][1], cdot);
+                    cdot = fmaf(g2.y, vr[p][2], cdot);
+                    cdot = fmaf(g2.z, vr[p][3], cdot);
+                    if (CH == 5) cdot = fmaf(g2.w, vr[p][CH - 1], cdot);
+                    const float v_a = fmaf(Tn, cdot, ra * (va_eff[p] - bdot[p]));
+                    bdot[p] = fmaf(fac, cdot, bdot[p]);
+                    const float u = (hk.valid[p] && ov <= MAX_ALPHA) ? vis * v_a : 0.f;
+                    const float v_sigma = -opac * u;
+                    const float wx = v_sigma * dx, wy = v_sigma * dy;
+                    Swx += wx;
+                    Swy += wy;
+                    Sxx = fmaf(wx, dx, Sxx);
+                    Sxy = fmaf(wx, dy, Sxy);
+                    Syy = fmaf(wy, dy, Syy);
+                    if (!GEOM) {
+                        Su += u;
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) col[c] = fmaf(fac, vr[p][c], col[c]);
+                    }
+#pragma unroll
+                    for (int c = 3; c < CH; ++c) col[c] = fmaf(fac, vr[p][c], col[c]);
+                }
+                if (hk.any) {
+                    const float ca = 2.0f * hk.g0.z, cb = hk.g0.w, cc = 2.0f * hk.g1.x;
+                    const float v0 = fmaf(ca, Swx, cb * Swy), v1 = fmaf(cb, Swx, cc * Swy);
+                    float* dst = v_rec + (int64_t)st.id[hk.slot] * REC;
+                    red_add_v4(dst, v0, v1, 0.5f * Sxx, Sxy);
+                    if (GEOM) {
+                        atomicAdd(dst + 4, 0.5f * Syy);
+                        red_add_v4(dst + 8, 0.f, col[3], col[4], 0.f);
+                    } else {
+                        red_add_v4(dst + 4, 0.5f * Syy, Su, col[0], col[1]);
+                        red_add_v4(dst + 8, col[2], col[3], col[4], 0.f);
+                    }
                 }
             }
         }
@@ -333,7 +361,7 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
 // Forward, same organisation: a lane owns a 2x2 quad (T, 5 accumulators, last index per pixel in registers), a warp a
 // 16x8 half tile.  Reference: gsplat RasterizeToPixels3DGSFwd.cu:17-188.  The per-pixel body is predicated, not
 // branched; the contribute / saturate decisions are those of blend.cu::blend_fwd_kernel.
-template <int CH, int NW>
+template <int CH, int NW, int HITS>
 __global__ void __launch_bounds__(THREADS, 8)
 blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
                     const int32_t* __restrict__ ranges, float* __restrict__ render, float* __restrict__ alpha,
@@ -385,45 +413,59 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
             const bool act = bits != 0u;
             const int wmin = __reduce_min_sync(FULL, act ? jq : jq + 1);
             if (wmin >= n_words) break;
-            const int s = act ? __ffs(bits) - 1 : 0;
-            bits &= bits - 1u;
-            const unsigned slot = wsl + s;
-            const float4 g0s = st.g0[slot];
-            const float4 g1s = st.g1[slot];
-            const float dxa = __fsub_rn(g0s.x, pxa), dxb = __fsub_rn(g0s.x, pxb);
-            const float dya = __fsub_rn(g0s.y, pya), dyb = __fsub_rn(g0s.y, pyb);
-            const float zxa = __fmul_rn(g0s.z, dxa), zxb = __fmul_rn(g0s.z, dxb);
-            const float cya = __fmul_rn(__fmul_rn(g1s.x, dya), dya), cyb = __fmul_rn(__fmul_rn(g1s.x, dyb), dyb);
-            float sigma[4];
-            sigma[0] = __fmaf_rn(__fmaf_rn(g0s.w, dya, zxa), dxa, cya);
-            sigma[1] = __fmaf_rn(__fmaf_rn(g0s.w, dya, zxb), dxb, cya);
-            sigma[2] = __fmaf_rn(__fmaf_rn(g0s.w, dyb, zxa), dxa, cyb);
-            sigma[3] = __fmaf_rn(__fmaf_rn(g0s.w, dyb, zxb), dxb, cyb);
-            bool hit[4];
-            bool anyh = false;
+            Hit h[HITS];
 #pragma unroll
-            for (int p = 0; p < 4; ++p) {
-                hit[p] = act && !done[p] && sigma[p] >= 0.f && sigma[p] <= g1s.y;
-                anyh |= hit[p];
-            }
-            if (__any_sync(FULL, anyh)) {
-                const float4 g2 = st.g2[slot];
-                const int idx = start + 32 * jq + s;
+            for (int k = 0; k < HITS; ++k) {
+                const bool on = bits != 0u;
+                const int sk = on ? __ffs(bits) - 1 : 0;
+                bits &= bits - 1u;
+                h[k].slot = wsl + sk;
+                h[k].e = 32 * jq + sk;
+                h[k].g0 = st.g0[h[k].slot];
+                h[k].g1 = st.g1[h[k].slot];
+                h[k].dx[0] = __fsub_rn(h[k].g0.x, pxa); h[k].dx[1] = __fsub_rn(h[k].g0.x, pxb);
+                h[k].dy[0] = __fsub_rn(h[k].g0.y, pya); h[k].dy[1] = __fsub_rn(h[k].g0.y, pyb);
+                const float zxa = __fmul_rn(h[k].g0.z, h[k].dx[0]), zxb = __fmul_rn(h[k].g0.z, h[k].dx[1]);
+                const float cya = __fmul_rn(__fmul_rn(h[k].g1.x, h[k].dy[0]), h[k].dy[0]);
+                const float cyb = __fmul_rn(__fmul_rn(h[k].g1.x, h[k].dy[1]), h[k].dy[1]);
+                h[k].sigma[0] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[0], zxa), h[k].dx[0], cya);
+                h[k].sigma[1] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[0], zxb), h[k].dx[1], cya);
+                h[k].sigma[2] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[1], zxa), h[k].dx[0], cyb);
+                h[k].sigma[3] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[1], zxb), h[k].dx[1], cyb);
+                h[k].any = false;
 #pragma unroll
                 for (int p = 0; p < 4; ++p) {
-                    const float a = fminf(MAX_ALPHA, g1s.z * __expf(hit[p] ? -sigma[p] : 0.f));
-                    const float nT = T[p] * (1.0f - a);
-                    const bool sat = hit[p] && nT <= T_CUTOFF;
-                    const bool contrib = hit[p] && !sat;
-                    done[p] = done[p] || sat;
-                    const float vis = contrib ? a * T[p] : 0.f;
-                    acc[p][0] = fmaf(g1s.w, vis, acc[p][0]);
-                    acc[p][1] = fmaf(g2.x, vis, acc[p][1]);
-                    acc[p][2] = fmaf(g2.y, vis, acc[p][2]);
-                    acc[p][3] = fmaf(g2.z, vis, acc[p][3]);
-                    if (CH == 5) acc[p][CH - 1] = fmaf(g2.w, vis, acc[p][CH - 1]);
-                    last_idx[p] = contrib ? idx : last_idx[p];
-                    T[p] = contrib ? nT : T[p];
+                    // (done[p] is re-checked when the hit is applied: an earlier hit of this iteration may saturate the pixel)
+                    h[k].valid[p] = on && h[k].sigma[p] >= 0.f && h[k].sigma[p] <= h[k].g1.y;
+                    h[k].any |= h[k].valid[p] && !done[p];
+                }
+            }
+            bool anyh = h[0].any;
+#pragma unroll
+            for (int k = 1; k < HITS; ++k) anyh |= h[k].any;
+            if (__any_sync(FULL, anyh)) {
+#pragma unroll
+                for (int k = 0; k < HITS; ++k) {
+                    const Hit& hk = h[k];
+                    const float4 g2 = st.g2[hk.slot];
+                    const int idx = start + hk.e;
+#pragma unroll
+                    for (int p = 0; p < 4; ++p) {
+                        const bool hit = hk.valid[p] && !done[p];
+                        const float a = fminf(MAX_ALPHA, hk.g1.z * __expf(hit ? -hk.sigma[p] : 0.f));
+                        const float nT = T[p] * (1.0f - a);
+                        const bool sat = hit && nT <= T_CUTOFF;
+                        const bool contrib = hit && !sat;
+                        done[p] = done[p] || sat;
+                        const float vis = contrib ? a * T[p] : 0.f;
+                        acc[p][0] = fmaf(hk.g1.w, vis, acc[p][0]);
+                        acc[p][1] = fmaf(g2.x, vis, acc[p][1]);
+                        acc[p][2] = fmaf(g2.y, vis, acc[p][2]);
+                        acc[p][3] = fmaf(g2.z, vis, acc[p][3]);
+                        if (CH == 5) acc[p][CH - 1] = fmaf(g2.w, vis, acc[p][CH - 1]);
+                        last_idx[p] = contrib ? idx : last_idx[p];
+                        T[p] = contrib ? nT : T[p];
+                    }
                 }
                 if (done[0] && done[1] && done[2] && done[3]) { jq = FAR; bits = 0u; } // quad saturated
             }
@@ -451,7 +493,7 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
     }
 }
 
-template <int CH, int NW>
+template <int CH, int NW, int HITS>
 int launch_fwd(const DevCam& dc, const float* rec, const int32_t* vals, const int32_t* ranges, float* render, float* alpha,
                int32_t* last, cudaStream_t stream) {
     constexpr size_t smem = sizeof(Ring<NW, false>) * WARPS;
@@ -459,16 +501,16 @@ int launch_fwd(const DevCam& dc, const float* rec, const int32_t* vals, const in
     int dev = 0;
     ISOGS_CUDA(cudaGetDevice(&dev));
     if (attr_dev != dev) {
-        ISOGS_CUDA(cudaFuncSetAttribute(blend_fwd_lq_kernel<CH, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ISOGS_CUDA(cudaFuncSetAttribute(blend_fwd_lq_kernel<CH, NW, HITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_dev = dev;
     }
     dim3 grid(dc.tw, dc.th);
-    blend_fwd_lq_kernel<CH, NW><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, render, alpha, last);
+    blend_fwd_lq_kernel<CH, NW, HITS><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, render, alpha, last);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
 }
 
-template <int CH, int NW, bool GEOM>
+template <int CH, int NW, bool GEOM, int HITS>
 int launch(const DevCam& dc, const float* rec, const int32_t* vals, const int32_t* ranges, const float* alpha,
            const int32_t* last, const float* v_render, const float* v_alpha, float* v_rec, cudaStream_t stream) {
     constexpr size_t smem = sizeof(Ring<NW, true>) * WARPS;
@@ -476,12 +518,12 @@ int launch(const DevCam& dc, const float* rec, const int32_t* vals, const int32_
     int dev = 0;
     ISOGS_CUDA(cudaGetDevice(&dev));
     if (attr_dev != dev) {
-        ISOGS_CUDA(cudaFuncSetAttribute(blend_bwd_lq_kernel<CH, NW, GEOM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        ISOGS_CUDA(cudaFuncSetAttribute(blend_bwd_lq_kernel<CH, NW, GEOM, HITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)smem));
         attr_dev = dev;
     }
     dim3 grid(dc.tw, dc.th);
-    blend_bwd_lq_kernel<CH, NW, GEOM><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last,
+    blend_bwd_lq_kernel<CH, NW, GEOM, HITS><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last,
                                                                                  v_render, v_alpha, v_rec);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
@@ -501,8 +543,9 @@ extern "C" int isogs_blend_fwd(const isogs_camera* cam, int ch, const float* rec
     if ((uintptr_t)rec & 15) { set_error("isogs_blend_fwd: rec must be 16-byte aligned"); return ISOGS_E_ARG; }
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
-    if (ch == 4) return lq::launch_fwd<4, lq::NW_DEFAULT>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, stream);
-    return lq::launch_fwd<5, lq::NW_DEFAULT>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, stream);
+    // one hit per lane per iteration in the forward (two measured 14 % slower: 0.305 vs 0.267 ms), two in the backward
+    if (ch == 4) return lq::launch_fwd<4, lq::NW_DEFAULT, lq::HITS_FWD>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, stream);
+    return lq::launch_fwd<5, lq::NW_DEFAULT, lq::HITS_FWD>(dc, rec, vals_sorted, tile_ranges, render, alpha, last, stream);
 }
 
 static int blend_bwd_entry(const char* who, bool geom, const isogs_camera* cam, int ch, const float* rec,
@@ -512,7 +555,7 @@ static int blend_bwd_entry(const char* who, bool geom, const isogs_camera* cam, 
     if (((uintptr_t)rec | (uintptr_t)v_rec) & 15) { set_error("%s: rec and v_rec must be 16-byte aligned", who); return ISOGS_E_ARG; }
     DevCam dc = make_devcam(*cam);
     if (dc.tw <= 0 || dc.th <= 0) return ISOGS_OK;
-#define LQ(CHN, G) lq::launch<CHN, lq::NW_DEFAULT, G>(dc, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream)
+#define LQ(CHN, G) lq::launch<CHN, lq::NW_DEFAULT, G, lq::HITS_BWD>(dc, rec, vals_sorted, tile_ranges, alpha, last, v_render, v_alpha, v_rec, stream)
     if (geom) return ch == 4 ? LQ(4, true) : LQ(5, true);
     return ch == 4 ? LQ(4, false) : LQ(5, false);
 #undef LQ
