@@ -381,18 +381,18 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
     const int n_entries = end - start;
     const int n_words = (n_entries + 31) >> 5;
 
+    // T[p] > 0: transmittance of a live pixel; T[p] < 0: the pixel is DONE (saturated, or outside the image) and -T[p]
+    // is its final transmittance -- the flag rides in the sign bit, so the loop carries no separate booleans
     float T[4], acc[4][CH];
     int last_idx[4];
-    bool done[4];
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
-        T[p] = 1.0f;
+        T[p] = (x0 + (p & 1) < cam.width && y0 + (p >> 1) < cam.height) ? 1.0f : -1.0f;
         last_idx[p] = start - 1;
-        done[p] = !(x0 + (p & 1) < cam.width && y0 + (p >> 1) < cam.height);
 #pragma unroll
         for (int k = 0; k < CH; ++k) acc[p][k] = 0.f;
     }
-    bool quad_done = done[0] && done[1] && done[2] && done[3];
+    const bool quad_done = T[0] < 0.f && T[1] < 0.f && T[2] < 0.f && T[3] < 0.f;
 
     if (n_words > 0 && !__all_sync(FULL, quad_done)) {
         int staged = 0, base = 0;
@@ -435,9 +435,9 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                 h[k].any = false;
 #pragma unroll
                 for (int p = 0; p < 4; ++p) {
-                    // (done[p] is re-checked when the hit is applied: an earlier hit of this iteration may saturate the pixel)
+                    // (liveness is re-checked when the hit is applied: an earlier hit of this iteration may saturate the pixel)
                     h[k].valid[p] = on && h[k].sigma[p] >= 0.f && h[k].sigma[p] <= h[k].g1.y;
-                    h[k].any |= h[k].valid[p] && !done[p];
+                    h[k].any |= h[k].valid[p] && T[p] > 0.f;
                 }
             }
             bool anyh = h[0].any;
@@ -451,12 +451,11 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                     const int idx = start + hk.e;
 #pragma unroll
                     for (int p = 0; p < 4; ++p) {
-                        const bool hit = hk.valid[p] && !done[p];
+                        const bool hit = hk.valid[p] && T[p] > 0.f;
                         const float a = fminf(MAX_ALPHA, hk.g1.z * __expf(hit ? -hk.sigma[p] : 0.f));
                         const float nT = T[p] * (1.0f - a);
                         const bool sat = hit && nT <= T_CUTOFF;
                         const bool contrib = hit && !sat;
-                        done[p] = done[p] || sat;
                         const float vis = contrib ? a * T[p] : 0.f;
                         acc[p][0] = fmaf(hk.g1.w, vis, acc[p][0]);
                         acc[p][1] = fmaf(g2.x, vis, acc[p][1]);
@@ -464,10 +463,10 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                         acc[p][3] = fmaf(g2.z, vis, acc[p][3]);
                         if (CH == 5) acc[p][CH - 1] = fmaf(g2.w, vis, acc[p][CH - 1]);
                         last_idx[p] = contrib ? idx : last_idx[p];
-                        T[p] = contrib ? nT : T[p];
+                        T[p] = contrib ? nT : (sat ? -T[p] : T[p]);
                     }
                 }
-                if (done[0] && done[1] && done[2] && done[3]) { jq = FAR; bits = 0u; } // quad saturated
+                if (T[0] < 0.f && T[1] < 0.f && T[2] < 0.f && T[3] < 0.f) { jq = FAR; bits = 0u; } // quad saturated
             }
             if (wmin > base) {
                 ++base;
@@ -486,8 +485,10 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
         if (xi < cam.width && yi < cam.height) {
             const int64_t pix = (int64_t)yi * cam.width + xi;
 #pragma unroll
-            for (int k = 0; k < CH; ++k) render[k * P + pix] = (k < 3) ? fmaf(T[p], cam.bg[k], acc[p][k]) : acc[p][k];
-            alpha[pix] = 1.0f - T[p];
+            const float Tf = fabsf(T[p]);
+#pragma unroll
+            for (int k = 0; k < CH; ++k) render[k * P + pix] = (k < 3) ? fmaf(Tf, cam.bg[k], acc[p][k]) : acc[p][k];
+            alpha[pix] = 1.0f - Tf;
             last[pix] = last_idx[p];
         }
     }
