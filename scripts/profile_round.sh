@@ -1,12 +1,25 @@
-# Round profile: GPU tests, bench line, ncu launch list, one --set full capture per kernel of interest.
-# Usage (on the GPU box): bash scripts/profile_round.sh <tag> "<kernel regexes>"
-TAG=${1:-r1x}
-KERNELS=${2:-"blend_bwd_kernel blend_fwd_kernel tile_sort_reg_kernel preprocess_bwd"}
-set -x
-timeout 900 python -m pytest tests -q -m gpu 2>&1 | tail -5 > gpurun_out/${TAG}_pytest.log
-timeout 600 python bench.py > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/${TAG}_ncu_launch.log 2>&1
-for k in $KERNELS; do
-  timeout 600 ncu --set full --clock-control none --import-source on -k regex:$k -s 4 -c 1 -f -o gpurun_out/${TAG}_$k python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/${TAG}_ncu_$k.log 2>&1
+# Round profile on the GPU box: GPU tests, the bench line + reference arm, the ncu launch list and ONE --set full
+# capture of every kernel of one mapping iteration.  Usage: bash scripts/profile_round.sh <tag>
+TAG=${1:-r2x}
+mkdir -p gpurun_out
+timeout 1200 python -m pytest tests -q -m gpu > gpurun_out/${TAG}_pytest_gpu.log 2>&1; tail -3 gpurun_out/${TAG}_pytest_gpu.log
+timeout 600 python bench.py --steps 20 --warmup 5 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; echo "bench rc $?"
+timeout 600 python bench.py --impl reference --steps 20 --warmup 1 > gpurun_out/${TAG}_bench_reference_arm.json 2> gpurun_out/${TAG}_bench_reference_arm.err
+for shape in tum scannetpp; do
+  ISOGS_BENCH_SHAPE=$shape timeout 600 python bench.py --steps 20 --warmup 5 --no-cpu > gpurun_out/${TAG}_bench_$shape.json 2> gpurun_out/${TAG}_bench_$shape.err
 done
-cat gpurun_out/${TAG}_pytest.log; cut -c1-400 gpurun_out/${TAG}_bench.json
+# launch list of 6 eager iterations (every launch with its device time; cold-cache, serialised: compare shares)
+python scripts/ncu_step.py replica 6 > gpurun_out/${TAG}_plain.log 2>&1 && \
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv python scripts/ncu_step.py replica 6 > gpurun_out/${TAG}_ncu_launch.log 2>&1
+# one full capture of each of the 11 kernels of the 5th iteration (4 x 11 launches skipped)
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"^(step_begin|preprocess_|tile_|blend_|loss_l1|adam_)" -s 44 -c 11 -f -o gpurun_out/${TAG}_step python scripts/ncu_step.py replica 6 > gpurun_out/${TAG}_ncu_full.log 2>&1
+ls -la gpurun_out/${TAG}_step.ncu-rep
+python - <<PY
+import json
+for n in ("bench", "bench_tum", "bench_scannetpp"):
+    try:
+        d = json.load(open("gpurun_out/${TAG}_%s.json" % n))
+        print(n, round(d["value"], 1), "it/s", round(d["ms_per_step"], 4), "ms  e2e", round(d["e2e"]["value"], 1), "track", d.get("tracking_iters_per_s"), d["stage_ms"], d.get("parity"))
+    except Exception as e:
+        print(n, "no json", e)
+PY
