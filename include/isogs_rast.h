@@ -394,7 +394,7 @@ typedef struct isogs_workspace {
 } isogs_workspace;
 
 #define ISOGS_STEP_SSIM 1     /* colour term 0.8*L1 + 0.2*(1-SSIM) (splatam.py:568) instead of pure L1 */
-#define ISOGS_STEP_OUTLIER 2  /* tracking: ignore_outlier_depth_loss (splatam.py:551-554) */
+#define ISOGS_STEP_OUTLIER 2  /* ignore_outlier_depth_loss (splatam.py:545-554); mapping: mean over the masked pixels */
 #define ISOGS_STEP_NO_SIL 4   /* tracking: use_sil_for_loss = False */
 #define ISOGS_PHASE_RENDER 1  /* begin + forward + loss + backward (gradients land in gaussians->g) */
 #define ISOGS_PHASE_ADAM 2    /* fused Adam on every group with a gradient */
@@ -405,6 +405,7 @@ typedef struct isogs_step_params {
     float w_im, w_depth, sil_thres;
     float lr[5];            /* mapping: per parameter group; tracking: lr[0] = rotation, lr[1] = translation */
     float beta1, beta2, eps;
+    float lr_pose[2];       /* isogs_map_step_ba: rotation, translation */
 } isogs_step_params;
 
 /* One mapping iteration on one keyframe == get_loss(mapping=True) + loss.backward() + optimizer.step()
@@ -415,6 +416,13 @@ typedef struct isogs_step_params {
  * ISOGS_STEP_EVENTS cudaEvent_t recorded after the stages for per-stage timing. */
 int isogs_map_step(const isogs_camera* cam, const isogs_frame* frame /*DEVICE*/, const isogs_workspace* ws,
                    const isogs_gaussians* gs, const isogs_step_params* prm, void* const* events, void* stream);
+
+/* get_loss(mapping=True, do_ba=True) (splatam.py:505-510): the same iteration with the keyframe's pose a parameter
+ * too -- the transform is differentiated with respect to both, the pose takes its own Adam step (prm->lr_pose,
+ * pose_state).  pose / pose_m / pose_v: DEVICE float[7]; frame->pose is ignored.  Both phases in one call. */
+int isogs_map_step_ba(const isogs_camera* cam, const isogs_frame* frame /*DEVICE*/, const isogs_workspace* ws,
+                      const isogs_gaussians* gs, float* pose, float* pose_m, float* pose_v,
+                      isogs_adam_state* pose_state, const isogs_step_params* prm, void* const* events, void* stream);
 
 /* One tracking iteration == get_loss(tracking=True) + backward + Adam on the pose + best-candidate rule
  * (splatam.py:1247-1290; Tracker::optimizePose, cpp/src/slam/tracker.cpp:15-115).  pose / pose_m / pose_v:

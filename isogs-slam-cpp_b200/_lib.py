@@ -74,7 +74,7 @@ class Workspace(C.Structure):
 class StepParams(C.Structure):
     _fields_ = [("flags", C.c_int32), ("phases", C.c_int32), ("w_im", C.c_float), ("w_depth", C.c_float),
                 ("sil_thres", C.c_float), ("lr", C.c_float * 5), ("beta1", C.c_float), ("beta2", C.c_float),
-                ("eps", C.c_float)]
+                ("eps", C.c_float), ("lr_pose", C.c_float * 2)]
 
 
 STEP_SSIM, STEP_OUTLIER, STEP_NO_SIL = 1, 2, 4
@@ -124,6 +124,8 @@ _SIGS = {
     "isogs_pose_keep_best": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     "isogs_map_step": (C.c_int, [C.POINTER(Camera), _VP, C.POINTER(Workspace), C.POINTER(Gaussians),
                                  C.POINTER(StepParams), C.POINTER(_VP), _VP]),
+    "isogs_map_step_ba": (C.c_int, [C.POINTER(Camera), _VP, C.POINTER(Workspace), C.POINTER(Gaussians), _VP, _VP, _VP,
+                                    _VP, C.POINTER(StepParams), C.POINTER(_VP), _VP]),
     "isogs_track_step": (C.c_int, [C.POINTER(Camera), _VP, C.POINTER(Workspace), C.POINTER(Gaussians), _VP, _VP, _VP,
                                    _VP, _VP, C.POINTER(StepParams), C.POINTER(_VP), _VP]),
     "isogs_unpack_rgbd": (C.c_int, [C.POINTER(Camera), _VP, _VP, _F, _VP, _VP, _VP]),

@@ -17,12 +17,12 @@ namespace isogs {
 int launch_loss_l1(const isogs_camera* cam, int mode, const float* render, const float* alpha, const float* gt_rgb,
                    const float* gt_depth, const isogs_frame* frame_dev, float w_im, float w_depth, float sil_thres,
                    int use_sil, float inv_n_depth, const float* outlier_thresh, float* v_render, float* losses,
-                   cudaStream_t stream);
+                   cudaStream_t stream, const float* inv_n_dev = nullptr);
 int launch_ssim_loss(const isogs_camera* cam, const float* render, const float* gt_rgb, const isogs_frame* frame_dev,
                      float weight, float* dmaps, float* v_render, float* losses, float* ssim_out, cudaStream_t stream);
 int launch_outlier_threshold(const isogs_camera* cam, const float* render_depth, const float* gt_depth,
                              const isogs_frame* frame_dev, float factor, float* scratch, void* sort_temp,
-                             size_t sort_temp_bytes, float* thresh_out, cudaStream_t stream);
+                             size_t sort_temp_bytes, float* thresh_out, cudaStream_t stream, float* inv_n_out = nullptr);
 
 namespace {
 constexpr int SMALL = 32; // losses[4] | v_pose[7] | pose_acc[16] | ssim | outlier thr | geo[3]
@@ -79,20 +79,42 @@ int forward(const isogs_camera* cam, const float* pose_dev, const isogs_workspac
 
 using namespace isogs;
 
-extern "C" int isogs_map_step(const isogs_camera* cam, const isogs_frame* frame, const isogs_workspace* ws,
-                              const isogs_gaussians* gs, const isogs_step_params* prm, void* const* ev, void* stream_) {
-    cudaStream_t st = (cudaStream_t)stream_;
+// ba != nullptr: get_loss(mapping=True, do_ba=True) (splatam.py:505-510) -- the keyframe's pose is a parameter too
+struct BaPose { float *pose, *m, *v; isogs_adam_state* state; };
+
+static int map_step_impl(const isogs_camera* cam, const isogs_frame* frame, const isogs_workspace* ws,
+                         const isogs_gaussians* gs, const isogs_step_params* prm, const BaPose* ba, void* const* ev,
+                         cudaStream_t st) {
     ISOGS_TRY(check_common(cam, frame, ws, gs, prm, "isogs_map_step"));
     const bool ssim = (prm->flags & ISOGS_STEP_SSIM) != 0;
     if (ssim && !ws->dmaps) { set_error("isogs_map_step: ISOGS_STEP_SSIM needs ws->dmaps"); return ISOGS_E_ARG; }
-    const float* pose_dev = reinterpret_cast<const float*>(reinterpret_cast<const char*>(frame) + offsetof(isogs_frame, pose));
+    const bool outlier = (prm->flags & ISOGS_STEP_OUTLIER) != 0;
+    if (outlier && (!ws->median_scratch || !ws->median_temp)) {
+        set_error("isogs_map_step: ISOGS_STEP_OUTLIER needs the median scratch");
+        return ISOGS_E_ARG;
+    }
+    if (ba && (!ba->pose || !ba->m || !ba->v || !ba->state)) { set_error("isogs_map_step_ba: null pose state"); return ISOGS_E_ARG; }
+    const float* pose_dev = ba ? ba->pose
+                               : reinterpret_cast<const float*>(reinterpret_cast<const char*>(frame) + offsetof(isogs_frame, pose));
     float* losses = ws->small;
+    float* v_pose = ws->small + 4;
+    float* pose_acc = ws->small + 11;
+    float* thr = ws->small + 28;
     if (prm->phases & ISOGS_PHASE_RENDER) {
         ISOGS_TRY(mark(ev, 0, st));
         ISOGS_TRY(isogs_step_begin(ws->small, SMALL, ws->adam_state, prm->beta1, prm->beta2, st));
+        if (ba) ISOGS_TRY(isogs_step_begin(nullptr, 0, ba->state, prm->beta1, prm->beta2, st));
         ISOGS_TRY(forward(cam, pose_dev, ws, gs, ev, st));
+        // ignore_outlier_depth_loss in mapping mode (splatam.py:545-549): the depth term is the MEAN over the masked
+        // pixels, so the normaliser 1/n(mask) is data dependent; it comes out of the sorted errors next to the median
+        // (median_scratch[0], free once the sort has run)
+        if (outlier)
+            ISOGS_TRY(launch_outlier_threshold(cam, ws->render + 3 * (size_t)cam->width * cam->height, nullptr, frame, 10.0f,
+                                               ws->median_scratch, ws->median_temp, ws->median_temp_bytes, thr, st,
+                                               ws->median_scratch));
         ISOGS_TRY(launch_loss_l1(cam, 1, ws->render, ws->alpha, nullptr, nullptr, frame, ssim ? 0.8f * prm->w_im : prm->w_im,
-                                 prm->w_depth, prm->sil_thres, 1, 1.0f, nullptr, ws->v_render, losses, st));
+                                 prm->w_depth, prm->sil_thres, 1, 1.0f, outlier ? thr : nullptr, ws->v_render, losses, st,
+                                 outlier ? ws->median_scratch : nullptr));
         ISOGS_TRY(mark(ev, 4, st));
         if (ssim)
             ISOGS_TRY(launch_ssim_loss(cam, ws->render, nullptr, frame, 0.2f * prm->w_im, ws->dmaps, ws->v_render, losses,
@@ -105,7 +127,7 @@ extern "C" int isogs_map_step(const isogs_camera* cam, const isogs_frame* frame,
         const float* quats = gs->scale_dim == 3 ? gs->p[2] : nullptr;
         ISOGS_TRY(isogs_preprocess_bwd(cam, nullptr, pose_dev, gs->N, gs->p[0], gs->p[4], gs->scale_dim, quats, gs->p[3], 5,
                                        FLAGS_RAW, ws->radii, ws->v_rec, gs->g[0], gs->g[4], gs->g[2], gs->g[3], gs->g[1],
-                                       nullptr, nullptr, nullptr, st));
+                                       nullptr, ba ? v_pose : nullptr, ba ? pose_acc : nullptr, st));
         ISOGS_TRY(mark(ev, 7, st));
     }
     if (prm->phases & ISOGS_PHASE_ADAM) {
@@ -120,9 +142,34 @@ extern "C" int isogs_map_step(const isogs_camera* cam, const isogs_frame* frame,
             ++n;
         }
         ISOGS_TRY(isogs_adam_fused(grp, n, prm->beta1, prm->beta2, prm->eps, 1, ws->adam_state, ws->totals + 1, st));
+        if (ba) {
+            isogs_adam_group pg[2];
+            pg[0].param = ba->pose; pg[0].grad = v_pose; pg[0].exp_avg = ba->m; pg[0].exp_avg_sq = ba->v;
+            pg[0].numel = 4; pg[0].lr = prm->lr_pose[0];
+            pg[1].param = ba->pose + 4; pg[1].grad = v_pose + 4; pg[1].exp_avg = ba->m + 4; pg[1].exp_avg_sq = ba->v + 4;
+            pg[1].numel = 3; pg[1].lr = prm->lr_pose[1];
+            ISOGS_TRY(isogs_adam_fused(pg, 2, prm->beta1, prm->beta2, prm->eps, 1, ba->state, ws->totals + 1, st));
+        }
         ISOGS_TRY(mark(ev, 8, st));
     }
     return ISOGS_OK;
+}
+
+extern "C" int isogs_map_step(const isogs_camera* cam, const isogs_frame* frame, const isogs_workspace* ws,
+                              const isogs_gaussians* gs, const isogs_step_params* prm, void* const* ev, void* stream_) {
+    return map_step_impl(cam, frame, ws, gs, prm, nullptr, ev, (cudaStream_t)stream_);
+}
+
+extern "C" int isogs_map_step_ba(const isogs_camera* cam, const isogs_frame* frame, const isogs_workspace* ws,
+                                 const isogs_gaussians* gs, float* pose, float* pose_m, float* pose_v,
+                                 isogs_adam_state* pose_state, const isogs_step_params* prm, void* const* ev,
+                                 void* stream_) {
+    const BaPose ba{pose, pose_m, pose_v, pose_state};
+    if (prm && prm->phases != (ISOGS_PHASE_RENDER | ISOGS_PHASE_ADAM)) {
+        set_error("isogs_map_step_ba: both phases in one call");
+        return ISOGS_E_ARG;
+    }
+    return map_step_impl(cam, frame, ws, gs, prm, &ba, ev, (cudaStream_t)stream_);
 }
 
 extern "C" int isogs_track_step(const isogs_camera* cam, const isogs_frame* frame, const isogs_workspace* ws,

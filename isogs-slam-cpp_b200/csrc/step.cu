@@ -35,7 +35,8 @@ __global__ void __launch_bounds__(256)
 loss_l1_kernel(int64_t P, int mode, const float* __restrict__ render, const float* __restrict__ alpha,
                const float* __restrict__ gt_rgb, const float* __restrict__ gt_depth, float w_im, float w_depth,
                float sil_thres, int use_sil, float inv_nd, float inv_nc, const float* __restrict__ outlier_thresh,
-               float* __restrict__ v_render, float* __restrict__ losses, const isogs_frame* __restrict__ fr) {
+               float* __restrict__ v_render, float* __restrict__ losses, const isogs_frame* __restrict__ fr,
+               const float* __restrict__ inv_n_dev) {
     if (fr != nullptr) {   // current frame through the device-side frame slot (CUDA-graph replay)
         gt_rgb = fr->gt_rgb;
         gt_depth = fr->gt_depth;
@@ -45,6 +46,7 @@ loss_l1_kernel(int64_t P, int mode, const float* __restrict__ render, const floa
             return;
         }
     }
+    if (inv_n_dev != nullptr) inv_nd = *inv_n_dev;   // mapping + outlier mask: 1 / n(mask), computed on the device
     float sum_d = 0.f, sum_c = 0.f, cnt = 0.f;
     const bool outl = outlier_thresh != nullptr;
     const float othr = outl ? *outlier_thresh : 0.f;
@@ -327,7 +329,7 @@ namespace isogs {
 int launch_loss_l1(const isogs_camera* cam, int mode, const float* render, const float* alpha, const float* gt_rgb,
                    const float* gt_depth, const isogs_frame* frame_dev, float w_im, float w_depth, float sil_thres,
                    int use_sil, float inv_n_depth, const float* outlier_thresh, float* v_render, float* losses,
-                   cudaStream_t stream);
+                   cudaStream_t stream, const float* inv_n_dev = nullptr);
 }
 
 extern "C" int isogs_loss_l1_fused(const isogs_camera* cam, int mode, const float* render, const float* alpha,
@@ -341,13 +343,13 @@ extern "C" int isogs_loss_l1_fused(const isogs_camera* cam, int mode, const floa
 int isogs::launch_loss_l1(const isogs_camera* cam, int mode, const float* render, const float* alpha, const float* gt_rgb,
                           const float* gt_depth, const isogs_frame* frame_dev, float w_im, float w_depth,
                           float sil_thres, int use_sil, float inv_n_depth, const float* outlier_thresh,
-                          float* v_render, float* losses, cudaStream_t stream) {
+                          float* v_render, float* losses, cudaStream_t stream, const float* inv_n_dev) {
     if (!cam || (mode != 0 && mode != 1) || (!frame_dev && (!gt_rgb || !gt_depth))) {
         set_error("isogs_loss_l1_fused: bad argument");
         return ISOGS_E_ARG;
     }
-    if (mode == 1 && outlier_thresh) {
-        set_error("isogs_loss_l1_fused: the outlier mask is supported for tracking (mode 0) only");
+    if (mode == 1 && outlier_thresh && !inv_n_dev) {   // the mean's normaliser is 1 / n(mask): data dependent
+        set_error("isogs_loss_l1_fused: mapping with the outlier mask goes through isogs_map_step (ISOGS_STEP_OUTLIER)");
         return ISOGS_E_ARG;
     }
     const int64_t P = (int64_t)cam->width * cam->height;
@@ -359,11 +361,13 @@ int isogs::launch_loss_l1(const isogs_camera* cam, int mode, const float* render
     if (vec) {
         const int blocks = (int)std::min<int64_t>((P / 4 + 255) / 256, 148 * 8);
         loss_l1_kernel<4><<<blocks, 256, 0, stream>>>(P, mode, render, alpha, gt_rgb, gt_depth, w_im, w_depth, sil_thres,
-                                                      use_sil, inv_nd, inv_nc, outlier_thresh, v_render, losses, frame_dev);
+                                                      use_sil, inv_nd, inv_nc, outlier_thresh, v_render, losses, frame_dev,
+                                                      inv_n_dev);
     } else {
         const int blocks = (int)std::min<int64_t>((P + 255) / 256, 148 * 8);
         loss_l1_kernel<1><<<blocks, 256, 0, stream>>>(P, mode, render, alpha, gt_rgb, gt_depth, w_im, w_depth, sil_thres,
-                                                      use_sil, inv_nd, inv_nc, outlier_thresh, v_render, losses, frame_dev);
+                                                      use_sil, inv_nd, inv_nc, outlier_thresh, v_render, losses, frame_dev,
+                                                      inv_n_dev);
     }
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
@@ -380,11 +384,35 @@ depth_error_kernel(int64_t P, const float* __restrict__ render_depth, const floa
 __global__ void median_pick_kernel(int64_t P, const float* __restrict__ sorted, float factor, float* out) {
     if (threadIdx.x == 0 && blockIdx.x == 0) *out = factor * sorted[(P - 1) / 2];
 }
+// mapping mode: also 1 / n(mask) with mask = (gt > 0) & (|gt - d| < thr) & finite (splatam.py:545-549, 556-559)
+__global__ void __launch_bounds__(1024)
+median_pick_count_kernel(int64_t P, const float* __restrict__ sorted, float factor, const float* __restrict__ render_depth,
+                         const float* __restrict__ gt_depth, const isogs_frame* __restrict__ fr, float* out,
+                         float* inv_n_out) {
+    if (fr != nullptr) gt_depth = fr->gt_depth;
+    const float thr = factor * sorted[(P - 1) / 2];
+    int n = 0;
+    for (int64_t i = threadIdx.x; i < P; i += blockDim.x) {
+        const float gd = gt_depth[i], d = render_depth[i], d2 = render_depth[P + i];
+        const float unc = d2 - d * d;
+        n += (gd > 0.f) && (fabsf(d - gd) < thr) && !(isnan(d) || isnan(unc));
+    }
+    __shared__ int sm[32];
+    for (int off = 16; off > 0; off >>= 1) n += __shfl_xor_sync(0xffffffffu, n, off);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = n;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int w = 0; w < 32; ++w) t += sm[w];
+        *out = thr;
+        *inv_n_out = t > 0 ? 1.0f / (float)t : 0.0f;
+    }
+}
 
 namespace isogs {
 int launch_outlier_threshold(const isogs_camera* cam, const float* render_depth, const float* gt_depth,
                              const isogs_frame* frame_dev, float factor, float* scratch, void* sort_temp,
-                             size_t sort_temp_bytes, float* thresh_out, cudaStream_t stream);
+                             size_t sort_temp_bytes, float* thresh_out, cudaStream_t stream, float* inv_n_out = nullptr);
 }
 
 extern "C" int isogs_depth_outlier_threshold(const isogs_camera* cam, const float* render_depth, const float* gt_depth,
@@ -396,7 +424,7 @@ extern "C" int isogs_depth_outlier_threshold(const isogs_camera* cam, const floa
 
 int isogs::launch_outlier_threshold(const isogs_camera* cam, const float* render_depth, const float* gt_depth,
                                     const isogs_frame* frame_dev, float factor, float* scratch, void* sort_temp,
-                                    size_t sort_temp_bytes, float* thresh_out, cudaStream_t stream) {
+                                    size_t sort_temp_bytes, float* thresh_out, cudaStream_t stream, float* inv_n_out) {
     if (!cam || !render_depth || (!gt_depth && !frame_dev) || !scratch || !thresh_out) {
         set_error("isogs_depth_outlier_threshold: bad argument");
         return ISOGS_E_ARG;
@@ -408,7 +436,11 @@ int isogs::launch_outlier_threshold(const isogs_camera* cam, const float* render
     ISOGS_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, need, scratch, scratch + P, (int)P, 0, 32, stream));
     if (need > sort_temp_bytes) { set_error("sort temp too small (%zu needed)", need); return ISOGS_E_ARG; }
     ISOGS_CUDA(cub::DeviceRadixSort::SortKeys(sort_temp, sort_temp_bytes, scratch, scratch + P, (int)P, 0, 32, stream));
-    median_pick_kernel<<<1, 32, 0, stream>>>(P, scratch + P, factor, thresh_out);
+    if (inv_n_out != nullptr)   // render_depth is plane 3 of the 5-channel render: plane 4 (depth^2) follows it
+        median_pick_count_kernel<<<1, 1024, 0, stream>>>(P, scratch + P, factor, render_depth, gt_depth, frame_dev,
+                                                         thresh_out, inv_n_out);
+    else
+        median_pick_kernel<<<1, 32, 0, stream>>>(P, scratch + P, factor, thresh_out);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
 }

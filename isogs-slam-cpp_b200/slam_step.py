@@ -447,8 +447,9 @@ def _mark(marks, name):
         marks.append((name, ev))
 
 
-def _params(flags, phases, w_im, w_depth, sil_thres, lr5, eps, beta1=0.9, beta2=0.999):
+def _params(flags, phases, w_im, w_depth, sil_thres, lr5, eps, beta1=0.9, beta2=0.999, lr_pose=(0.0, 0.0)):
     p = _lib.StepParams()
+    p.lr_pose[:] = [float(v) for v in lr_pose]
     p.flags, p.phases = int(flags), int(phases)
     p.w_im, p.w_depth, p.sil_thres = float(w_im), float(w_depth), float(sil_thres)
     p.lr[:] = [float(v) for v in lr5]
@@ -491,22 +492,49 @@ def _graph_launch(ws, key, enqueue):
 
 
 def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, allreduce=None, marks=None, w_im=0.5,
-             w_depth=1.0, ssim=False, isoflat=False, iso_seed=0, graph=False, eps=1e-15):
+             w_depth=1.0, ssim=False, isoflat=False, iso_seed=0, graph=False, eps=1e-15, ignore_outlier_depth=False,
+             ba=None):
     """One mapping iteration on one keyframe (splatam.py:1412-1476): ONE host call (isogs_map_step) enqueues
     transform_to_frame + activations + projection, binning, the 5-channel blend, the masked-L1 (+ SSIM) loss, both
     backwards and the fused Adam; no host sync.  `pose` is the keyframe's HOST pose (camera_grad=False).
     `allreduce(flat_grad_tensor)` runs between backward and Adam, as do the iso / flat terms (`isoflat=True`, :572-675,
     three-axis scales) -- with ssim and isoflat the loss is the reference's complete mapping loss.  `marks` (a list)
     receives (stage, cuda event) pairs.  graph=True replays a captured CUDA graph of the step: one graph serves
-    every keyframe, because the frame is read through the device-side slot ws.cur_frame."""
+    every keyframe, because the frame is read through the device-side slot ws.cur_frame.
+    ignore_outlier_depth: the depth term over |err| < 10 median(err) only, mean over the masked pixels (:545-549).
+    ba: a PoseState -- get_loss(do_ba=True) (:505-510): the keyframe's pose is optimised together with the map
+    (learning rates lrs['cam_unnorm_rots'], lrs['cam_trans']); `pose` is then ignored."""
+    if ba is not None:
+        if allreduce is not None or isoflat or graph:
+            raise ValueError("map_step(ba=...) runs the eager single-call path")
+        ws.check_overflow()
+        if ssim and ws.dmaps is None:
+            ws.dmaps = torch.empty((9, ws.cam.height, ws.cam.width), dtype=torch.float32, device=ws.device)
+        if ignore_outlier_depth:
+            ws.median_temp()
+        frame = ws.frame(gt_rgb, gt_depth, pose, inv_n_depth)
+        cws, cgs = ws.c_struct(), gmap.c_struct()
+        cws.adam_state = gmap.adam_state.data_ptr()
+        flags = (_lib.STEP_SSIM if ssim else 0) | (_lib.STEP_OUTLIER if ignore_outlier_depth else 0)
+        prm = _params(flags, _lib.PHASE_RENDER | _lib.PHASE_ADAM, w_im, w_depth, 0.99, [lrs.get(k, 0.0) for k in PARAM_ORDER],
+                      eps, lr_pose=(lrs.get("cam_unnorm_rots", 0.0), lrs.get("cam_trans", 0.0)))
+        gmap.step_count += 1
+        ba.step_count += 1
+        check(lib().isogs_map_step_ba(C.byref(ws.cam), frame.data_ptr(), C.byref(cws), C.byref(cgs), ba.pose.data_ptr(),
+                                      ba.m.data_ptr(), ba.v.data_ptr(), ba.adam_state.data_ptr(), C.byref(prm),
+                                      _event_array(marks), _stream()))
+        ws.post_totals()
+        return ws.losses
     if ssim and ws.dmaps is None:
         ws.dmaps = torch.empty((9, ws.cam.height, ws.cam.width), dtype=torch.float32, device=ws.device)
+    if ignore_outlier_depth:
+        ws.median_temp()
     ws.check_overflow()
     L, st = lib(), _stream()
     frame = ws.frame(gt_rgb, gt_depth, pose, inv_n_depth)
     cws, cgs = ws.c_struct(), gmap.c_struct()
     cws.adam_state = gmap.adam_state.data_ptr()
-    flags = _lib.STEP_SSIM if ssim else 0
+    flags = (_lib.STEP_SSIM if ssim else 0) | (_lib.STEP_OUTLIER if ignore_outlier_depth else 0)
     lr5 = [lrs.get(k, 0.0) for k in PARAM_ORDER]
     split = allreduce is not None or isoflat
     ev = _event_array(marks)

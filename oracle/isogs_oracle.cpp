@@ -721,9 +721,17 @@ extern "C" void orc_loss_l1(const orc_camera* cam, int mode, const float* render
     const int64_t P = (int64_t)cam->width * cam->height;
     double sum_d = 0.0, sum_c = 0.0;
     int64_t n_d = 0;
-    // pass 1: counts for the mean normalisers (mapping)
+    // pass 1: counts for the mean normalisers (mapping).  With ignore_outlier_depth_loss the mean runs over the
+    // masked pixels (splatam.py:545-549, 556-559: |err|[mask].mean()).
     if (mode == 1)
-        for (int64_t i = 0; i < P; ++i) n_d += (gt_depth[i] > 0.0f);
+        for (int64_t i = 0; i < P; ++i) {
+            bool m = gt_depth[i] > 0.0f;
+            if (outlier_thresh >= 0.0f) {
+                float d = render[3 * P + i], unc = render[4 * P + i] - d * d;
+                m = m && (fabsf(d - gt_depth[i]) < outlier_thresh) && !(std::isnan(d) || std::isnan(unc));
+            }
+            n_d += m;
+        }
     const float inv_nd = (mode == 1) ? (n_d > 0 ? 1.0f / (float)n_d : 0.0f) : 1.0f;
     const float inv_nc = (mode == 1) ? 1.0f / (float)(3 * P) : 1.0f;
 #pragma omp parallel for reduction(+ : sum_d, sum_c) schedule(static)

@@ -29,17 +29,19 @@ def _flags(orc):
 
 
 def map_iteration(orc, ocam, state, q, t, gt_rgb, gt_depth, grads_out=None, extra_grads=None, w_im=0.5, w_depth=1.0,
-                  ssim=False, isoflat=False):
+                  ssim=False, isoflat=False, ignore_outlier_depth=False, ba=None, lr_rot=4e-4, lr_trans=2e-3):
     """One mapping iteration on one keyframe.  extra_grads: list of gradient dicts from OTHER ranks of the
-    data-parallel schedule (averaged with this one before Adam)."""
+    data-parallel schedule (averaged with this one before Adam).  ba: a TrackState -- do_ba=True
+    (splatam.py:505-510), the pose is a parameter as well (q, t ignored)."""
     p = state["p"]
-    pose = orc.make_pose(q, t)
+    pose = orc.make_pose(q, t) if ba is None else orc.make_pose(ba.pose[:4], ba.pose[4:])
     lo = p["logit_opacities"].reshape(-1)
     qs = _quats(p)
     o = orc.render_full(ocam, p["means3D"], p["log_scales"], qs, lo, p["rgb_colors"], ch=5, flags=_flags(orc),
                         pose=pose)
     v_render, losses = orc.loss_l1(ocam, 1, o["render"], o["alpha"], gt_rgb, gt_depth,
-                                   w_im=(0.8 * w_im if ssim else w_im), w_depth=w_depth)
+                                   w_im=(0.8 * w_im if ssim else w_im), w_depth=w_depth,
+                                   ignore_outlier_depth=ignore_outlier_depth)
     if ssim:  # colour term 0.8 * L1 + 0.2 * (1 - SSIM), splatam.py:568
         v_c = np.ascontiguousarray(v_render[:3])
         s_val = orc.ssim(o["render"][:3], gt_rgb, -0.2 * w_im, v_c)
@@ -68,6 +70,13 @@ def map_iteration(orc, ocam, state, q, t, gt_rgb, gt_depth, grads_out=None, extr
             continue
         orc.adam(p[k].reshape(-1), np.ascontiguousarray(grads[k]).reshape(-1), state["m"][k].reshape(-1),
                  state["v"][k].reshape(-1), lr, eps=1e-15, step=state["step"])
+    if ba is not None:
+        gp = np.ascontiguousarray(g["pose"], dtype=np.float32)
+        if grads_out is not None:
+            grads_out["pose"] = gp.copy()
+        ba.step += 1
+        orc.adam(ba.pose[:4], gp[:4], ba.m[:4], ba.v[:4], lr_rot, eps=1e-15, step=ba.step)
+        orc.adam(ba.pose[4:], gp[4:], ba.m[4:], ba.v[4:], lr_trans, eps=1e-15, step=ba.step)
     return float(losses[0])
 
 

@@ -267,3 +267,49 @@ def test_fused_count_and_rect_binning_is_bit_identical(pkg, syn):
     n_tiles_per = ((r[:, 0] >> 16) - (r[:, 0] & 0xffff)) * ((r[:, 1] >> 16) - (r[:, 1] & 0xffff))
     assert np.array_equal(n_tiles_per.astype(np.int32), tiles.cpu().numpy())
     assert np.array_equal(r[:, 2][n_tiles_per > 0], rec.cpu().numpy()[:, 10].view(np.uint32)[n_tiles_per > 0])
+
+
+def test_map_step_outlier_mask_and_bundle_adjust_modes_match_the_oracle(pkg, orc, syn, ss):
+    """The two get_loss modes the shipped configs leave off (VERDICT r1 missing 8): ignore_outlier_depth_loss in
+    mapping mode -- the depth term is the MEAN over the masked pixels, so its normaliser is computed on the device
+    (splatam.py:545-549, 556-559) -- and do_ba=True, where the keyframe's pose gets a gradient and an Adam step next
+    to the Gaussians (:505-510).  One iteration of each (and both together) against the oracle's iteration."""
+    import oracle_slam as osl
+    params, (W, H, fx, fy, cx, cy) = _scene(syn)
+    cam, ocam = pkg.make_camera(W, H, fx, fy, cx, cy), orc.make_camera(W, H, fx, fy, cx, cy)
+    traj = syn.trajectory(8, step=3.0)
+    c, d, _ = syn.render_frame("tiny", traj[3], seed=3)
+    c, d = np.ascontiguousarray(c), np.ascontiguousarray(d[0])
+    d[40:60, 50:90] *= 0.5                               # a foreground object the map does not hold: depth outliers
+    q, tr = syn.w2c_to_pose(traj[2])                     # the neighbouring frame's pose: a pose gradient exists
+    inv_nd = 1.0 / max(1, int((d > 0).sum()))
+    lrs = dict(ss.MAPPING_LRS, cam_unnorm_rots=4e-4, cam_trans=2e-3)
+    grgb, gdepth = t(c), t(d)
+    for outlier, ba in ((True, False), (False, True), (True, True)):
+        gmap = ss.GaussianMap(params, device="cuda")
+        ws = ss.StepWorkspace(cam, gmap.count, torch.device("cuda"))
+        state = osl.new_state(params)
+        ts = osl.TrackState(q, tr) if ba else None
+        ps = ss.PoseState(q, tr, "cuda") if ba else None
+        og = {}
+        lo = osl.map_iteration(orc, ocam, state, q, tr, c, d, grads_out=og, ignore_outlier_depth=outlier, ba=ts)
+        losses = ss.map_step(ws, gmap, pkg.make_pose(q, tr), grgb, gdepth, inv_nd, lrs=lrs, ignore_outlier_depth=outlier,
+                             ba=ps)
+        torch.cuda.synchronize()
+        assert not ws.check_overflow(wait=True)
+        assert abs(float(losses[0]) - lo) <= 2e-4 * abs(lo), (outlier, ba, float(losses[0]), lo)
+        for k in ("means3D", "rgb_colors", "logit_opacities", "log_scales"):
+            got, want = gmap.g[k].cpu().numpy().reshape(-1), np.asarray(og[k]).reshape(-1)
+            assert np.abs(got - want).max() <= 2e-3 * np.abs(want).max() + 1e-9, (outlier, ba, k)
+        if ba:
+            v = ws.v_pose.cpu().numpy()
+            assert np.abs(v - og["pose"]).max() <= 1e-3 * np.abs(og["pose"]).max(), (v, og["pose"])
+            got = ps.pose.cpu().numpy()
+            assert np.abs(got - ts.pose).max() <= 0.02 * 4e-4, (got, ts.pose)      # one Adam step = lr * sign(g)
+            assert np.abs(got - np.concatenate([q, tr])).max() > 1e-4, "the pose must have stepped"
+        if outlier:   # the mask bites: the normaliser differs from 1 / n(valid depth)
+            thr = orc.depth_outlier_threshold(orc.render_full(ocam, params["means3D"], params["log_scales"], None,
+                                              params["logit_opacities"].reshape(-1), params["rgb_colors"], ch=5,
+                                              flags=orc.F_LOG_SCALES | orc.F_LOGIT_OPAC, pose=orc.make_pose(q, tr))["render"][3], d)
+            assert abs(float(ws.small[28]) - thr) <= 1e-5 * thr
+            assert float(ws.outlier_scratch[0]) > inv_nd * 1.01
