@@ -215,6 +215,18 @@ int isogs_depth_outlier_threshold(const isogs_camera* cam, const float* render_d
                                   float factor, float* scratch, void* sort_temp, size_t sort_temp_bytes,
                                   float* thresh_out, void* stream);
 
+/* Allocation-free variant of isogs_depth_outlier_threshold.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses
+ * that forbid it).  The scratch (two H*W float planes + the sort temp) is a file-scope device array inside the
+ * library -- ISOGS_NOALLOC_BYTES on every GPU that loads it, until exit -- so the caller passes inputs and the
+ * output only.  Images of more than ISOGS_NOALLOC_MAX_PIXELS pixels are rejected with ISOGS_E_ARG.  The call
+ * allocates nothing and does not synchronise.  All calls share the one array: calls that overlap on the GPU
+ * (different streams or threads) race; serialise them.  Same result, bit for bit, as the entry above. */
+#define ISOGS_NOALLOC_MAX_PIXELS (1 << 21)                                   /* >= 1752 x 1168 */
+#define ISOGS_NOALLOC_BYTES (8ull * ISOGS_NOALLOC_MAX_PIXELS + (4ull << 20)) /* 20 MiB */
+int isogs_depth_outlier_threshold_noalloc(const isogs_camera* cam, const float* render_depth, const float* gt_depth,
+                                          float factor, float* thresh_out, void* stream);
+
 /* fused SSIM term of the mapping colour loss 0.8*L1 + 0.2*(1 - SSIM): replaces calc_ssim / _ssim
  * (python_ordinary/utils/slam_external.py:54-97; call site splatam.py:568) and its autograd backward
  * (5 depthwise 11x11 conv2d, zero padding, sigma 1.5, c1 = 1e-4, c2 = 9e-4, mean over [3,H,W]).

@@ -122,6 +122,7 @@ _SIGS = {
     "isogs_adam_fused": (C.c_int, [C.POINTER(AdamGroup), _I32, _F, _F, _F, _I32, _VP, _VP, _VP]),
     "isogs_step_begin": (C.c_int, [_VP, _I32, _VP, _F, _F, _VP]),
     "isogs_pose_keep_best": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
+    "isogs_depth_outlier_threshold_noalloc": (C.c_int, [C.POINTER(Camera), _VP, _VP, _F, _VP, _VP]),
     "isogs_map_step": (C.c_int, [C.POINTER(Camera), _VP, C.POINTER(Workspace), C.POINTER(Gaussians),
                                  C.POINTER(StepParams), C.POINTER(_VP), _VP]),
     "isogs_map_step_ba": (C.c_int, [C.POINTER(Camera), _VP, C.POINTER(Workspace), C.POINTER(Gaussians), _VP, _VP, _VP,

@@ -7,6 +7,7 @@
 #include <cub/device/device_scan.cuh>
 
 #include <cmath>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -443,6 +444,57 @@ int isogs::launch_outlier_threshold(const isogs_camera* cam, const float* render
         median_pick_kernel<<<1, 32, 0, stream>>>(P, scratch + P, factor, thresh_out);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
+}
+
+// ---- allocation-free variant of the outlier threshold ------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  The depth-error
+// planes and the radix-sort temp of isogs_depth_outlier_threshold live in ONE file-scope device array that every
+// GPU loading the library holds until exit (ISOGS_NOALLOC_BYTES = 20 MiB).  Nothing in it has to start at zero:
+// depth_error_kernel writes all H*W errors, the sort writes all H*W outputs and CUB initialises its own temp.
+// Every call shares the array, so calls that overlap on the GPU (two streams, two threads) race.
+constexpr int64_t NOALLOC_MAX_PIXELS = ISOGS_NOALLOC_MAX_PIXELS;
+constexpr size_t NOALLOC_SORT_TEMP = (size_t)4 << 20;
+constexpr size_t NOALLOC_BYTES = sizeof(float) * 2 * (size_t)NOALLOC_MAX_PIXELS + NOALLOC_SORT_TEMP;
+static_assert(NOALLOC_BYTES == ISOGS_NOALLOC_BYTES, "header and kernel file disagree on the scratch size");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+// In host code g_noalloc_scratch is a host-side stand-in, not a device address: the address a kernel may use comes
+// from cudaGetSymbolAddress, taken once per device with that device current.
+static int noalloc_scratch_ptr(unsigned char** out) {
+    constexpr int MAX_DEV = 64;
+    static unsigned char* ptrs[MAX_DEV] = {};
+    static std::mutex mu;
+    int dev = 0;
+    ISOGS_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEV) { set_error("isogs_depth_outlier_threshold_noalloc: device %d out of range", dev); return ISOGS_E_ARG; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (ptrs[dev] == nullptr) {
+        void* p = nullptr;
+        ISOGS_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        ptrs[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = ptrs[dev];
+    return ISOGS_OK;
+}
+
+extern "C" int isogs_depth_outlier_threshold_noalloc(const isogs_camera* cam, const float* render_depth,
+                                                     const float* gt_depth, float factor, float* thresh_out,
+                                                     void* stream_) {
+    if (!cam) { set_error("isogs_depth_outlier_threshold_noalloc: null camera"); return ISOGS_E_ARG; }
+    const int64_t P = (int64_t)cam->width * cam->height;
+    if (P > NOALLOC_MAX_PIXELS) {
+        set_error("isogs_depth_outlier_threshold_noalloc: %lld pixels exceed the built-in scratch (max %lld); use "
+                  "isogs_depth_outlier_threshold with caller scratch", (long long)P, (long long)NOALLOC_MAX_PIXELS);
+        return ISOGS_E_ARG;
+    }
+    unsigned char* base = nullptr;
+    const int rc = noalloc_scratch_ptr(&base);
+    if (rc != ISOGS_OK) return rc;
+    float* scratch = reinterpret_cast<float*>(base);
+    void* sort_temp = base + sizeof(float) * 2 * (size_t)NOALLOC_MAX_PIXELS;   // 256-byte aligned: 8 * 2^21 bytes in
+    return launch_outlier_threshold(cam, render_depth, gt_depth, nullptr, factor, scratch, sort_temp, NOALLOC_SORT_TEMP,
+                                    thresh_out, (cudaStream_t)stream_);
 }
 
 // uint8 HWC colour + uint16 depth -> fp32 planes (basedataset.py:299-340: color / 255, depth / png_depth_scale)
