@@ -342,18 +342,21 @@ tile_sort_kernel(int lo, int hi, int n_tiles, const int32_t* __restrict__ n_big,
 constexpr int SORT_REG_MAX = 2048;
 
 // ---- per-tile sort for tiles with <= 2048 intersections (the common case): a block-wide merge sort
-// (cub::BlockMergeSort: thread t sorts its E consecutive keys, then log2(256) merge-path rounds through shared
+// (cub::BlockMergeSort: thread t sorts its E consecutive keys, then log2(128) merge-path rounds through shared
 // memory).  Measured against a hand-written 55-stage register / shuffle bitonic network on the same buckets (round
 // 2, replica shape): 65 us against 76 us -- the network was bound by the ALU / shuffle pipes (46 M warp
-// instructions), the merge sort executes about half as many. -------------------------------------------------
+// instructions), the merge sort executes about half as many.  Block size (same shape, whole binning stage): 256
+// threads 0.096 ms, 128 threads 0.074 ms, 64 threads 0.085 ms -- the merge rounds are barrier / shared-memory latency
+// bound, 128 threads x E <= 8 keys halves the threads waiting at each of one round fewer.  A finer ladder of E, or
+// separate launches per shared-memory size, changed nothing. -------------------------------------------------
 struct Less64 {
     __device__ __forceinline__ bool operator()(const uint64_t& a, const uint64_t& b) const { return a < b; }
 };
 
-template <int E>
+template <int T, int E>
 __device__ __forceinline__ void tile_sort_merge(int tile, int start, int n, const uint64_t* __restrict__ seg, void* smem,
                                                 uint64_t* __restrict__ keys_sorted, int32_t* __restrict__ vals_sorted, int tid) {
-    using Sort = cub::BlockMergeSort<uint64_t, 256, E>;
+    using Sort = cub::BlockMergeSort<uint64_t, T, E>;
     uint64_t v[E];
 #pragma unroll
     for (int r = 0; r < E; ++r) {
@@ -371,18 +374,27 @@ __device__ __forceinline__ void tile_sort_merge(int tile, int start, int n, cons
     }
 }
 
-__global__ void __launch_bounds__(256)
+constexpr int SORT_THREADS = 128;
+
+__global__ void __launch_bounds__(SORT_THREADS)
 tile_sort_merge_kernel(const int32_t* __restrict__ ranges, const uint64_t* __restrict__ bucket,
                        uint64_t* __restrict__ keys_sorted, int32_t* __restrict__ vals_sorted) {
-    __shared__ __align__(16) unsigned char s_tmp[sizeof(typename cub::BlockMergeSort<uint64_t, 256, 8>::TempStorage)];
+    constexpr int T = SORT_THREADS;
+    __shared__ __align__(16) unsigned char s_tmp[sizeof(typename cub::BlockMergeSort<uint64_t, T, SORT_REG_MAX / T>::TempStorage)];
     const int tile = blockIdx.x, tid = threadIdx.x;
     const int start = ranges[tile], n = ranges[tile + 1] - start;
     if (n <= 0 || n > SORT_REG_MAX) return;
     const uint64_t* seg = bucket + start;
-    if (n <= 256) tile_sort_merge<1>(tile, start, n, seg, s_tmp, keys_sorted, vals_sorted, tid);
-    else if (n <= 512) tile_sort_merge<2>(tile, start, n, seg, s_tmp, keys_sorted, vals_sorted, tid);
-    else if (n <= 1024) tile_sort_merge<4>(tile, start, n, seg, s_tmp, keys_sorted, vals_sorted, tid);
-    else tile_sort_merge<8>(tile, start, n, seg, s_tmp, keys_sorted, vals_sorted, tid);
+#define TSM(E) tile_sort_merge<T, E>(tile, start, n, seg, s_tmp, keys_sorted, vals_sorted, tid)
+    if (n <= 2 * T) TSM(2);
+    else if (n <= 4 * T) TSM(4);
+    else if (n <= 5 * T) TSM(5);
+    else if (n <= 6 * T) TSM(6);
+    else if (n <= 7 * T) TSM(7);
+    else if (n <= 8 * T) TSM(8);
+    else if (n <= 12 * T) TSM(12);
+    else TSM(16);
+#undef TSM
 }
 
 inline int sort_end_bit(int n_tiles) {
@@ -443,7 +455,7 @@ static int counting_bin(int tw, int th, int64_t N, int32_t capacity, bool clamp,
         attr_set = true;
     }
     static_assert(SORT_REG_MAX == SORT_SMEM_SMALL, "the two sort kernels split the tiles at the same length");
-    tile_sort_merge_kernel<<<n_tiles, 256, 0, stream>>>(tile_ranges, bucket, keys_sorted, vals_sorted);
+    tile_sort_merge_kernel<<<n_tiles, SORT_THREADS, 0, stream>>>(tile_ranges, bucket, keys_sorted, vals_sorted);
     // the rare long tiles: a small persistent grid that exits at once when tile_scan_kernel counted none
     tile_sort_kernel<<<std::min(n_tiles, 148), 256, SORT_SMEM_MAX * sizeof(uint64_t), stream>>>(
         SORT_SMEM_SMALL, 0x7fffffff, n_tiles, n_big, tile_ranges, bucket, keys_sorted, vals_sorted);
