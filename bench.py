@@ -231,8 +231,20 @@ def run_ours(args):
     fused = False
     if world > 1:
         ar, ar_kind = dp.allreduce_mean_, "nccl all-reduce (ncclAvg)"
-        if args.allreduce in ("p2p", "fused"):
-            fused = args.allreduce == "fused"
+        kind = args.allreduce
+        if kind == "nvls":                             # in-switch reduction; falls back to the peer-memory kernel
+            peer = dp.NvlsReduceAdam(dev)
+            try:
+                peer.alloc(1024)
+                ar, grad_alloc, fused = peer, peer.alloc, True
+                ar_kind = ("reduce (multimem.ld_reduce inside the NVSwitch) + Adam + parameter broadcast (multimem.st) "
+                           "fused in ONE kernel (isogs_reduce_adam_nvls, optimizer state sharded)")
+            except RuntimeError as e:
+                kind = "fused"
+                if rank == 0:
+                    print(f"[bench] NVLS unavailable, using the peer-memory kernel: {e}", file=sys.stderr)
+        if kind in ("p2p", "fused"):
+            fused = kind == "fused"
             peer = dp.PeerReduceAdam(dev) if fused else dp.PeerAllReduce(dev)
             try:
                 peer.alloc(1024)                       # probe: cudaMalloc + IPC export + peer mapping on every rank
@@ -762,7 +774,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
     ap.add_argument("--no-graph", action="store_true", help="enqueue every step eagerly instead of replaying the captured graph")
-    ap.add_argument("--allreduce", default="fused", choices=["fused", "p2p", "nccl"],
+    ap.add_argument("--allreduce", default="fused", choices=["nvls", "fused", "p2p", "nccl"],
                     help="exchange step at N > 1: reduce + Adam fused in one NVLink peer-memory kernel (default), the "
                          "peer-memory all-reduce followed by the ordinary Adam launch, or NCCL")
     args = ap.parse_args()

@@ -499,6 +499,18 @@ int isogs_reduce_adam_p2p(int world, int rank, float* const* grad_bufs /*HOST*/,
                           float beta2, float eps, const isogs_adam_state* state, uint32_t epoch, int n_ctas,
                           int32_t* status, void* stream);
 
+/* The same fused exchange through the NVSwitch's in-fabric reduction (NVLS): mc_grad is the MULTICAST address of the
+ * flat gradient buffer (every rank's buffer bound to one multicast object), mc_params[g] the multicast address of
+ * parameter group g.  The slice owner reads its slice with ONE multimem.ld_reduce.add.v4.f32 per 16 bytes (the switch
+ * sums the ranks' copies: 1/world of the buffer crosses the owner's link instead of (world-1)/world) and broadcasts
+ * the updated parameters with ONE multimem.st (instead of world peer stores).  The summation order inside the switch
+ * is the hardware's, so the result agrees with isogs_reduce_adam_p2p to rounding, not bit for bit; replicas stay
+ * bit-identical by construction.  No reference counterpart (the reference has no distributed code). */
+int isogs_reduce_adam_nvls(int world, int rank, float* const* grad_bufs /*HOST*/, uint32_t* const* flags /*HOST*/,
+                           int64_t numel, const isogs_peer_adam_group* groups /*HOST*/, int n_groups, float beta1,
+                           float beta2, float eps, const isogs_adam_state* state, uint32_t epoch, int n_ctas,
+                           int32_t* status, const float* mc_grad, float* const* mc_params /*HOST*/, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -152,6 +152,8 @@ _SIGS = {
     "isogs_peer_wait": (C.c_int, [_I32, _VP, C.c_uint32, _VP, _VP]),
     "isogs_reduce_adam_p2p": (C.c_int, [_I32, _I32, C.POINTER(_VP), C.POINTER(_VP), _I64, C.POINTER(PeerAdamGroup), _I32,
                                         _F, _F, _F, _VP, C.c_uint32, _I32, _VP, _VP]),
+    "isogs_reduce_adam_nvls": (C.c_int, [_I32, _I32, C.POINTER(_VP), C.POINTER(_VP), _I64, C.POINTER(PeerAdamGroup), _I32,
+                                         _F, _F, _F, _VP, C.c_uint32, _I32, _VP, _VP, C.POINTER(_VP), _VP]),
     "isogs_prune_mask": (C.c_int, [_I64, _VP, _VP, _I32, _F, _F, _VP, _VP]),
     "isogs_compact": (C.c_int, [_I64, _VP, C.POINTER(Rows), _I32, _VP, _VP, _SZ, _VP, _VP]),
     "isogs_backproject_append": (C.c_int, [C.POINTER(Camera), C.POINTER(Pose), _VP, _VP, _VP, _VP, _F, _F, _VP, _VP,

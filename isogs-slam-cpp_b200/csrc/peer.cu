@@ -139,7 +139,22 @@ struct PeerAdamArgs {
     int n_groups;
     float b2, one_minus_b1, one_minus_b2, eps;
     const isogs_adam_state* state;
+    // NVLS (multicast) addresses of the same allocations, or null: the gradient slice is then reduced INSIDE the
+    // NVSwitch by one multimem.ld_reduce and the parameters are broadcast by one multimem.st
+    const float4* mc_grad;
+    float4* mc_param[PEER_MAX_GROUPS];
 };
+
+__device__ __forceinline__ float4 multimem_ld_reduce_add_f4(const float4* mc) {
+    float4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(mc) : "memory");
+    return r;
+}
+__device__ __forceinline__ void multimem_st_f4(float4* mc, const float4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 :: "l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 
 // the arithmetic of adam_kernel (step.cu), operation for operation
 __device__ __forceinline__ void peer_adam_one(float& p, float g, float& m, float& v, const PeerAdamArgs& a, float step_size,
@@ -147,7 +162,7 @@ __device__ __forceinline__ void peer_adam_one(float& p, float g, float& m, float
     adam_update(p, g, m, v, a.one_minus_b1, a.b2, a.one_minus_b2, inv_bc2_sqrt, a.eps, step_size);
 }
 
-template <int WORLD>
+template <int WORLD, bool MC = false>
 __device__ __forceinline__ void reduce_adam_slice(const PeerPtrs& pp, const PeerAdamArgs& a, int world, int rank,
                                                   int64_t begin, int64_t end, float inv_world) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -155,7 +170,9 @@ __device__ __forceinline__ void reduce_adam_slice(const PeerPtrs& pp, const Peer
     const double ibc1 = a.state->inv_bc1;
     for (int64_t i = begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < end; i += stride) {
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (WORLD > 0) {
+        if (MC) {
+            acc = multimem_ld_reduce_add_f4(a.mc_grad + i);
+        } else if (WORLD > 0) {
             float4 t[WORLD > 0 ? WORLD : 1];
 #pragma unroll
             for (int p = 0; p < WORLD; ++p) t[p] = ld_relaxed_sys_f4(pp.buf[p] + i);     // all loads in flight first
@@ -182,9 +199,13 @@ __device__ __forceinline__ void reduce_adam_slice(const PeerPtrs& pp, const Peer
         peer_adam_one(P4.w, acc.w, M4.w, V4.w, a, ss, ib2);
         a.m[g][j] = M4;
         a.v[g][j] = V4;
-        const int n = WORLD > 0 ? WORLD : world;
+        if (MC) {
+            multimem_st_f4(a.mc_param[g] + j, P4);
+        } else {
+            const int n = WORLD > 0 ? WORLD : world;
 #pragma unroll
-        for (int p = 0; p < n; ++p) st_relaxed_sys_f4(a.param[g][p] + j, P4);
+            for (int p = 0; p < n; ++p) st_relaxed_sys_f4(a.param[g][p] + j, P4);
+        }
     }
 }
 
@@ -201,12 +222,16 @@ peer_reduce_adam_kernel(PeerPtrs pp, PeerAdamArgs a, int world, int rank, int64_
     const int64_t per = (n4 + world - 1) / world;
     const int64_t begin = min(n4, per * rank), end = min(n4, begin + per);
     const float inv_world = 1.0f / (float)world;
-    switch (world) {
-        case 1: reduce_adam_slice<1>(pp, a, world, rank, begin, end, inv_world); break;
-        case 2: reduce_adam_slice<2>(pp, a, world, rank, begin, end, inv_world); break;
-        case 4: reduce_adam_slice<4>(pp, a, world, rank, begin, end, inv_world); break;
-        case 8: reduce_adam_slice<8>(pp, a, world, rank, begin, end, inv_world); break;
-        default: reduce_adam_slice<0>(pp, a, world, rank, begin, end, inv_world); break;
+    if (a.mc_grad != nullptr) {
+        reduce_adam_slice<0, true>(pp, a, world, rank, begin, end, inv_world);
+    } else {
+        switch (world) {
+            case 1: reduce_adam_slice<1>(pp, a, world, rank, begin, end, inv_world); break;
+            case 2: reduce_adam_slice<2>(pp, a, world, rank, begin, end, inv_world); break;
+            case 4: reduce_adam_slice<4>(pp, a, world, rank, begin, end, inv_world); break;
+            case 8: reduce_adam_slice<8>(pp, a, world, rank, begin, end, inv_world); break;
+            default: reduce_adam_slice<0>(pp, a, world, rank, begin, end, inv_world); break;
+        }
     }
     // 3. last CTA: "my slice of the parameters has landed"
     __threadfence_system();
@@ -287,11 +312,10 @@ extern "C" int isogs_allreduce_avg_p2p(int world, int rank, float* const* bufs, 
     return ISOGS_OK;
 }
 
-extern "C" int isogs_reduce_adam_p2p(int world, int rank, float* const* grad_bufs, uint32_t* const* flags, int64_t numel,
-                                     const isogs_peer_adam_group* groups, int n_groups, float beta1, float beta2, float eps,
-                                     const isogs_adam_state* state, uint32_t epoch, int n_ctas, int32_t* status,
-                                     void* stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
+static int reduce_adam_launch(int world, int rank, float* const* grad_bufs, uint32_t* const* flags, int64_t numel,
+                              const isogs_peer_adam_group* groups, int n_groups, float beta1, float beta2, float eps,
+                              const isogs_adam_state* state, uint32_t epoch, int n_ctas, int32_t* status,
+                              const float* mc_grad, float* const* mc_params, cudaStream_t stream) {
     if (world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world || !grad_bufs || !flags || numel < 0 || (numel & 3) ||
         !status || !groups || n_groups < 1 || n_groups > PEER_MAX_GROUPS || !state) {
         set_error("isogs_reduce_adam_p2p: bad argument (world <= 16, numel a multiple of 4, <= 5 groups, device Adam state)");
@@ -304,6 +328,14 @@ extern "C" int isogs_reduce_adam_p2p(int world, int rank, float* const* grad_buf
         pp.flags[p] = flags[p];
     }
     PeerAdamArgs a{};
+    a.mc_grad = (const float4*)mc_grad;
+    if (mc_grad != nullptr) {
+        if (((uintptr_t)mc_grad & 15) || !mc_params) { set_error("isogs_reduce_adam_nvls: null or misaligned multicast pointer"); return ISOGS_E_ARG; }
+        for (int g = 0; g < n_groups; ++g) {
+            if (!mc_params[g] || ((uintptr_t)mc_params[g] & 15)) { set_error("isogs_reduce_adam_nvls: group %d: null or misaligned multicast parameter pointer", g); return ISOGS_E_ARG; }
+            a.mc_param[g] = (float4*)mc_params[g];
+        }
+    }
     a.n_groups = n_groups;
     a.b2 = beta2; a.one_minus_b1 = 1.0f - beta1; a.one_minus_b2 = 1.0f - beta2; a.eps = eps;
     a.state = state;
@@ -330,6 +362,23 @@ extern "C" int isogs_reduce_adam_p2p(int world, int rank, float* const* grad_buf
     peer_reduce_adam_kernel<<<grid, 256, 0, stream>>>(pp, a, world, rank, n4, epoch, status);
     ISOGS_CUDA(cudaGetLastError());
     return ISOGS_OK;
+}
+
+extern "C" int isogs_reduce_adam_p2p(int world, int rank, float* const* grad_bufs, uint32_t* const* flags, int64_t numel,
+                                     const isogs_peer_adam_group* groups, int n_groups, float beta1, float beta2, float eps,
+                                     const isogs_adam_state* state, uint32_t epoch, int n_ctas, int32_t* status,
+                                     void* stream_) {
+    return reduce_adam_launch(world, rank, grad_bufs, flags, numel, groups, n_groups, beta1, beta2, eps, state, epoch,
+                              n_ctas, status, nullptr, nullptr, (cudaStream_t)stream_);
+}
+
+extern "C" int isogs_reduce_adam_nvls(int world, int rank, float* const* grad_bufs, uint32_t* const* flags, int64_t numel,
+                                      const isogs_peer_adam_group* groups, int n_groups, float beta1, float beta2, float eps,
+                                      const isogs_adam_state* state, uint32_t epoch, int n_ctas, int32_t* status,
+                                      const float* mc_grad, float* const* mc_params, void* stream_) {
+    if (!mc_grad || !mc_params) { set_error("isogs_reduce_adam_nvls: multicast pointers required"); return ISOGS_E_ARG; }
+    return reduce_adam_launch(world, rank, grad_bufs, flags, numel, groups, n_groups, beta1, beta2, eps, state, epoch,
+                              n_ctas, status, mc_grad, mc_params, (cudaStream_t)stream_);
 }
 
 extern "C" int isogs_peer_wait(int world, const uint32_t* flags_local, uint32_t epoch, int32_t* status, void* stream_) {

@@ -242,10 +242,13 @@ class PeerReduceAdam(PeerAllReduce):
             arr[i].lr = lrs[k]
         self.epoch += 1
         st = torch.cuda.current_stream(self.device).cuda_stream
+        self._launch(L, n, arr, names, beta1, beta2, eps, gmap, st)
+        self._lib.check(L.isogs_peer_wait(self.world, self.flags[self.rank], self.epoch, self.status.data_ptr(), st))
+
+    def _launch(self, L, n, arr, names, beta1, beta2, eps, gmap, st):
         self._lib.check(L.isogs_reduce_adam_p2p(self.world, self.rank, self.bufs, self.flags, n, arr, len(names), beta1, beta2,
                                                 eps, gmap.adam_state.data_ptr(), self.epoch, self.n_ctas,
                                                 self.status.data_ptr(), st))
-        self._lib.check(L.isogs_peer_wait(self.world, self.flags[self.rank], self.epoch, self.status.data_ptr(), st))
 
     def sync_moments(self, gmap):
         """COLLECTIVE.  Makes every rank's Adam moments complete again (each rank broadcasts the parts it owns):
@@ -273,3 +276,55 @@ class PeerReduceAdam(PeerAllReduce):
         for k in list(self.pown):
             self._unshare(self.pown[k], self.pptrs[k])
         self.pown, self.pptrs = {}, {}
+
+
+class NvlsReduceAdam(PeerReduceAdam):
+    """PeerReduceAdam through the NVSwitch's in-fabric reduction (isogs_reduce_adam_nvls): the gradient buffer and the
+    parameter tensors are SYMMETRIC allocations bound to a multicast object, so the owner of a slice reads it with one
+    multimem.ld_reduce (the switch adds the ranks' copies) and broadcasts the updated parameters with one multimem.st.
+    The allocation / multicast binding / handle exchange is torch.distributed._symmetric_memory (plumbing: device memory
+    and rendezvous); the kernel is ours.  Raises at alloc() -- on every rank together -- when the box has no multicast
+    support, so the caller can fall back to PeerReduceAdam."""
+
+    def __init__(self, device, group=None, n_ctas=0):
+        super().__init__(device, group, n_ctas)
+        self._symm = {}          # own pointer -> (tensor, handle, multicast pointer)
+
+    def _shared(self, nbytes):
+        import torch.distributed._symmetric_memory as symm_mem
+        grp = self.group if self.group is not None else dist.group.WORLD
+        ok, err, t, hdl, mc = True, None, None, None, 0
+        try:
+            try:
+                symm_mem.set_backend("CUDA")
+            except Exception:
+                pass
+            with torch.cuda.device(self.device):
+                t = symm_mem.empty((int(nbytes) + 3) // 4, dtype=torch.float32, device=self.device)
+                t.zero_()
+                hdl = symm_mem.rendezvous(t, grp)
+            mc = int(hdl.multicast_ptr)
+            off = int(getattr(hdl, "offset", 0))
+            ptrs = [int(p) + off for p in hdl.buffer_ptrs]
+            if not mc:
+                ok, err = False, "no multicast support (multicast_ptr == 0)"
+            elif ptrs[self.rank] != t.data_ptr():
+                ok, err = False, f"symmetric buffer pointer mismatch ({ptrs[self.rank]:#x} vs {t.data_ptr():#x}, offset {off})"
+            mc += off
+        except Exception as e:                               # noqa: BLE001 -- any failure means "no NVLS here"
+            ok, err = False, f"{type(e).__name__}: {e}"
+        if not self._agree(ok):
+            raise RuntimeError(f"NVLS symmetric allocation unavailable on some rank ({err})")
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)                       # every rank's zero fill has landed before anybody's flags are used
+        self._symm[t.data_ptr()] = (t, hdl, mc)
+        return t.data_ptr(), ptrs
+
+    def _unshare(self, own, ptrs):
+        self._symm.pop(own, None)                            # the symmetric allocation is freed with its tensor
+
+    def _launch(self, L, n, arr, names, beta1, beta2, eps, gmap, st):
+        mcp = (C.c_void_p * len(names))(*[self._symm[self.pown[k]][2] for k in names])
+        self._lib.check(L.isogs_reduce_adam_nvls(self.world, self.rank, self.bufs, self.flags, n, arr, len(names), beta1,
+                                                 beta2, eps, gmap.adam_state.data_ptr(), self.epoch, self.n_ctas,
+                                                 self.status.data_ptr(), self._symm[self.own][2], mcp, st))

@@ -43,14 +43,22 @@ def main():
         k["rgb_d"], k["depth_d"], k["pose"] = tt(k["rgb"]), tt(k["depth"]), pkg.make_pose(k["q"], k["t"])
     names = ("means3D", "rgb_colors", "logit_opacities", "log_scales")
     results = {}
-    for mode in ("nccl", "p2p", "fused"):
+    nvls_note = None
+    for mode in ("nccl", "p2p", "fused", "nvls"):
         ar, alloc = dp.allreduce_mean_, None
         if mode == "p2p":
             ar = dp.PeerAllReduce(dev); alloc = ar.alloc
         elif mode == "fused":
             ar = dp.PeerReduceAdam(dev); alloc = ar.alloc
+        elif mode == "nvls":
+            ar = dp.NvlsReduceAdam(dev); alloc = ar.alloc
+            try:
+                ar.alloc(1024)                     # COLLECTIVE probe: raises on every rank when there is no multicast
+            except RuntimeError as e:
+                nvls_note = str(e)
+                continue
         gmap = ss.GaussianMap(params, device=dev, grad_alloc=alloc)
-        if mode == "fused":
+        if mode in ("fused", "nvls"):
             ar.adopt(gmap)
         ws = ss.StepWorkspace(cam, gmap.count, dev)
         losses = []
@@ -63,7 +71,7 @@ def main():
             ar.check_status()
         same = dp.replicas_identical([gmap.view(n) for n in names])
         results[mode] = dict(p={n: gmap.view(n).cpu().numpy().copy() for n in names}, losses=losses, same=bool(same))
-        if mode == "fused":
+        if mode in ("fused", "nvls"):
             # a re-sliced count (prune) needs complete moments everywhere: after sync_moments the moments of every
             # rank equal those of a full (unsharded) Adam
             ar.sync_moments(gmap)
@@ -103,6 +111,13 @@ def main():
             d = float(np.abs(results["fused"]["p"][n] - results["p2p"]["p"][n]).max() / lrs[n])
             report.setdefault("fused_vs_p2p_in_steps", {})[n] = d
             ok = ok and d <= 0.02 * iters
+        report["nvls"] = report.get("nvls", dict(unavailable=nvls_note))
+        if "nvls" in results:
+            ok = ok and results["nvls"]["moments_identical_after_sync"]
+            for n in names:
+                d = float(np.abs(results["nvls"]["p"][n] - results["fused"]["p"][n]).max() / lrs[n])
+                report.setdefault("nvls_vs_fused_in_steps", {})[n] = d
+                ok = ok and d <= 0.02 * iters
         report["moments_identical_after_sync"] = results["fused"]["moments_identical_after_sync"]
         ok = ok and results["fused"]["moments_identical_after_sync"]
         m_ref = st["m"]["rgb_colors"].reshape(results["fused"]["m"]["rgb_colors"].shape)
