@@ -359,7 +359,8 @@ def run_ours(args):
         """Blocks of exactly `steps` steps until min_s of device time is covered; every rank derives the same block
         count from the max-over-ranks time of the first block.  Every block starts from the initial map."""
         first = timed(fn, steps, reset=reset)
-        n_more = int(min(max_blocks, max(0, np.ceil(min_s * 1e3 / max(first, 1e-3)) - 1)))
+        # 5 % head-room: the first block (cold clocks / caches) is the slowest, so later blocks are shorter than it
+        n_more = int(min(max_blocks, max(0, np.ceil(1.05 * min_s * 1e3 / max(first, 1e-3)) - 1)))
         blocks = [first] + [timed(fn, steps, first=(b + 1) * steps, reset=reset) for b in range(n_more)]
         return blocks
 

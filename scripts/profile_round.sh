@@ -14,6 +14,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
 # one full capture of each of the 11 kernels of the 5th iteration (4 x 11 launches skipped)
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"^(step_begin|preprocess_|tile_|blend_|loss_l1|adam_)" -s 44 -c 11 -f -o gpurun_out/${TAG}_step python scripts/ncu_step.py replica 6 > gpurun_out/${TAG}_ncu_full.log 2>&1
 ls -la gpurun_out/${TAG}_step.ncu-rep
+timeout 600 python scripts/time_to_loss.py --ms "${STEP_MS:-1:0.813,2:0.864,8:0.918}" > gpurun_out/${TAG}_time_to_loss.log 2>&1; grep TIME_TO_LOSS gpurun_out/${TAG}_time_to_loss.log | cut -c1-1500 || tail -5 gpurun_out/${TAG}_time_to_loss.log
 python - <<PY
 import json
 for n in ("bench", "bench_tum", "bench_scannetpp"):
