@@ -456,6 +456,8 @@ int isogs_graph_begin(void* stream);
 int isogs_graph_end(void* stream, void** graph_exec);
 int isogs_graph_launch(void* graph_exec, void* stream);
 int isogs_graph_destroy(void* graph_exec);
+/* Kernel nodes / other nodes (memsets, copies) of a captured graph, counted from the graph at isogs_graph_end. */
+int isogs_graph_info(void* graph_exec, int32_t* n_kernel_nodes, int32_t* n_other_nodes);
 
 /* keyframe-sharded mapping, SURVEY 8(e): the average of the flat gradient buffer over the ranks as ONE kernel over
  * NVLink peer memory (two-shot: every rank reduces the 1/world slice it owns from all ranks in rank order and stores the

@@ -134,6 +134,7 @@ _SIGS = {
     "isogs_graph_end": (C.c_int, [_VP, C.POINTER(_VP)]),
     "isogs_graph_launch": (C.c_int, [_VP, _VP]),
     "isogs_graph_destroy": (C.c_int, [_VP]),
+    "isogs_graph_info": (C.c_int, [_VP, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "isogs_densify_stats": (C.c_int, [_I64, _VP, _VP, _I32, _F, _F, _VP, _VP, _VP, _VP]),
     "isogs_densify_select": (C.c_int, [_I64, _VP, _VP, _VP, _I32, _F, _F, _I32, _VP, _VP, _SZ, _VP, _VP]),
     "isogs_densify_emit": (C.c_int, [_I64, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _I32, _I32, _VP, C.c_uint64, _VP, _VP]),

@@ -10,6 +10,9 @@
 // (isogs_frame), and Adam's step count / bias corrections live on the device (isogs_adam_state, advanced by the
 // step's first kernel).
 #include <cstddef>
+#include <mutex>
+#include <unordered_map>
+#include <vector>
 
 #include "common.cuh"
 
@@ -219,6 +222,8 @@ extern "C" int isogs_track_step(const isogs_camera* cam, const isogs_frame* fram
 }
 
 // ---- CUDA-graph capture / replay ------------------------------------------------------------------------------
+static std::mutex g_graph_mu;
+static std::unordered_map<void*, std::pair<int32_t, int32_t>> g_graph_info;
 extern "C" int isogs_graph_begin(void* stream_) {
     ISOGS_CUDA(cudaStreamBeginCapture((cudaStream_t)stream_, cudaStreamCaptureModeThreadLocal));
     return ISOGS_OK;
@@ -228,11 +233,36 @@ extern "C" int isogs_graph_end(void* stream_, void** graph_exec) {
     if (!graph_exec) { set_error("isogs_graph_end: null output"); return ISOGS_E_ARG; }
     cudaGraph_t g = nullptr;
     ISOGS_CUDA(cudaStreamEndCapture((cudaStream_t)stream_, &g));
+    // what was captured, counted from the graph itself (bench.py reports it as gpu_launches)
+    int32_t n_kernel = 0, n_other = 0;
+    size_t n_nodes = 0;
+    if (cudaGraphGetNodes(g, nullptr, &n_nodes) == cudaSuccess && n_nodes > 0) {
+        std::vector<cudaGraphNode_t> nodes(n_nodes);
+        if (cudaGraphGetNodes(g, nodes.data(), &n_nodes) == cudaSuccess)
+            for (size_t i = 0; i < n_nodes; ++i) {
+                cudaGraphNodeType t;
+                if (cudaGraphNodeGetType(nodes[i], &t) != cudaSuccess) continue;
+                if (t == cudaGraphNodeTypeKernel) ++n_kernel; else ++n_other;
+            }
+    }
     cudaGraphExec_t ge = nullptr;
     const int rc = check_cuda(cudaGraphInstantiate(&ge, g, 0), "cudaGraphInstantiate");
     cudaGraphDestroy(g);
     if (rc != ISOGS_OK) return rc;
+    {
+        std::lock_guard<std::mutex> lock(g_graph_mu);
+        g_graph_info[(void*)ge] = {n_kernel, n_other};
+    }
     *graph_exec = (void*)ge;
+    return ISOGS_OK;
+}
+
+extern "C" int isogs_graph_info(void* graph_exec, int32_t* n_kernel_nodes, int32_t* n_other_nodes) {
+    std::lock_guard<std::mutex> lock(g_graph_mu);
+    const auto it = g_graph_info.find(graph_exec);
+    if (it == g_graph_info.end()) { set_error("isogs_graph_info: unknown graph"); return ISOGS_E_ARG; }
+    if (n_kernel_nodes) *n_kernel_nodes = it->second.first;
+    if (n_other_nodes) *n_other_nodes = it->second.second;
     return ISOGS_OK;
 }
 
@@ -243,6 +273,12 @@ extern "C" int isogs_graph_launch(void* graph_exec, void* stream_) {
 }
 
 extern "C" int isogs_graph_destroy(void* graph_exec) {
-    if (graph_exec) ISOGS_CUDA(cudaGraphExecDestroy((cudaGraphExec_t)graph_exec));
+    if (graph_exec) {
+        {
+            std::lock_guard<std::mutex> lock(g_graph_mu);
+            g_graph_info.erase(graph_exec);
+        }
+        ISOGS_CUDA(cudaGraphExecDestroy((cudaGraphExec_t)graph_exec));
+    }
     return ISOGS_OK;
 }

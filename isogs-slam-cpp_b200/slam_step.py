@@ -491,6 +491,16 @@ def _graph_launch(ws, key, enqueue):
     check(L.isogs_graph_launch(ge, _stream()))
 
 
+def graph_node_counts(ws):
+    """{key: (kernel nodes, other nodes)} of every graph this workspace has captured (counted from the graphs)."""
+    out = {}
+    for key, h in ws._graphs.items():
+        k, o = C.c_int32(0), C.c_int32(0)
+        check(lib().isogs_graph_info(h, C.byref(k), C.byref(o)))
+        out[key] = (int(k.value), int(o.value))
+    return out
+
+
 def map_step(ws, gmap, pose, gt_rgb, gt_depth, inv_n_depth, lrs=MAPPING_LRS, allreduce=None, marks=None, w_im=0.5,
              w_depth=1.0, ssim=False, isoflat=False, iso_seed=0, graph=False, eps=1e-15, ignore_outlier_depth=False,
              ba=None):
