@@ -155,7 +155,7 @@ def main():
     tw, th = (W + 15) // 16, (H + 15) // 16
     rng = np.random.RandomState(0)
     tiles = rng.choice(tw * th, min(a.tiles, tw * th), replace=False)
-    variants = [("nw8", 8, False, False), ("nw16", 16, False, False)]
+    variants = [("nw8", 8, False, False), ("nw16", 16, False, False), ("nw32", 32, False, False), ("nw64", 64, False, False), ("nw64skip", 64, False, True)]
     tot = {v[0]: [0, 0, 0] for v in variants}   # iterations, live, staged words
     pairs = 0
     for t in tiles:
