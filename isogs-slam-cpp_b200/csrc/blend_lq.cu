@@ -19,7 +19,6 @@
 // and GPU.  Measured alternatives that did NOT pay off are recorded in DESIGN.md 3.1c (four lanes per quad, rings of
 // 4 words, scalar REDs, compacted rings, one 16-word ring per tile filled by cp.async.bulk / cp.async on mbarriers).
 
-#include <cstdlib>
 #include "common.cuh"
 
 namespace isogs {
@@ -72,8 +71,8 @@ __device__ __forceinline__ void prefetch(Pf& pf, int word, int first, int n_entr
 // Hit masks of the 32 Gaussians of one ring word (lane L holds Gaussian L's g0 / g1) against the warp's 32 quads,
 // written to st.hits[wsl + q].  Footprint test as in blend.cu::quad_hits (squared half extents + Gershgorin circle,
 // padded, conservative).
-template <class RingT>
-__device__ __forceinline__ void publish_hits(RingT& st, bool have, const float4& g0, const float4& g1,
+template <int NW, bool WITH_ID>
+__device__ __forceinline__ void publish_hits(Ring<NW, WITH_ID>& st, bool have, const float4& g0, const float4& g1,
                                              unsigned wsl, float bx0, float by0, int lane) {
     float hx2 = -1.f, hy2 = -1.f, R2 = -1.f;
     if (have) {
@@ -119,7 +118,7 @@ __device__ __forceinline__ void commit(Ring<NW, WITH_ID>& st, const Pf& pf, int 
         st.g2[slot] = pf.g2;
         if (WITH_ID) st.id[slot] = pf.id;
     }
-    publish_hits(st, pf.have, pf.g0, pf.g1, wsl, bx0, by0, lane);
+    publish_hits<NW, WITH_ID>(st, pf.have, pf.g0, pf.g1, wsl, bx0, by0, lane);
     __syncwarp();
 }
 
@@ -164,7 +163,7 @@ __device__ __forceinline__ int initial_fill(Ring<NW, WITH_ID>& st, int first, in
             g0 = st.g0[slot];
             g1 = st.g1[slot];
         }
-        publish_hits(st, have, g0, g1, 32u * w, bx0, by0, lane);
+        publish_hits<NW, WITH_ID>(st, have, g0, g1, 32u * w, bx0, by0, lane);
     }
     __syncwarp();
     return nfill;
@@ -177,7 +176,6 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
 // one (quad, Gaussian) pair being evaluated by a lane
 struct Hit {
     float4 g0, g1;
-    int id;
     float dx[2], dy[2], sigma[4];
     unsigned slot;
     int e;
@@ -186,7 +184,7 @@ struct Hit {
 
 // GEOM = true: tracking -- only the gradient components the POSE depends on (x, y, conic, z, z^2) are produced.
 // HITS: (quad, Gaussian) pairs a lane evaluates per warp iteration.
-template <int CH, int NW, bool GEOM, int HITS, bool GATHER = false>
+template <int CH, int NW, bool GEOM, int HITS>
 __global__ void __launch_bounds__(THREADS, 8)
 blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
                     const int32_t* __restrict__ ranges, const float* __restrict__ alpha,
@@ -271,14 +269,8 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
             bits &= bits - 1u;
             h[k].slot = wsl + sk;
             h[k].e = on ? 32 * jq + sk : -1;
-            if (GATHER) {
-                const float4* r = rec + 3 * (int64_t)st.id[h[k].slot];
-                h[k].g0 = __ldg(r);
-                h[k].g1 = __ldg(r + 1);
-            } else {
-                h[k].g0 = st.g0[h[k].slot];
-                h[k].g1 = st.g1[h[k].slot];
-            }
+            h[k].g0 = st.g0[h[k].slot];
+            h[k].g1 = st.g1[h[k].slot];
             h[k].dx[0] = __fsub_rn(h[k].g0.x, pxa); h[k].dx[1] = __fsub_rn(h[k].g0.x, pxb);
             h[k].dy[0] = __fsub_rn(h[k].g0.y, pya); h[k].dy[1] = __fsub_rn(h[k].g0.y, pyb);
             const float zxa = __fmul_rn(h[k].g0.z, h[k].dx[0]), zxb = __fmul_rn(h[k].g0.z, h[k].dx[1]);
@@ -302,7 +294,7 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
 #pragma unroll
             for (int k = 0; k < HITS; ++k) {
                 const Hit& hk = h[k];
-                const float4 g2 = GATHER ? __ldg(rec + 3 * (int64_t)st.id[hk.slot] + 2) : st.g2[hk.slot];
+                const float4 g2 = st.g2[hk.slot];
                 const float opac = hk.g1.z;
                 float Swx = 0.f, Swy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f, Su = 0.f;
                 float col[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
@@ -363,276 +355,6 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                 prefetch(pf, staged, warp_last, n_entries, rec, vals, lane);
             }
         }
-    }
-}
-
-// ---- mask-queue ring: hit masks + ids only ------------------------------------------------------------------
-template <int NW>
-struct __align__(16) MRing {
-    uint32_t hits[32 * NW]; // [ring word][quad]
-    int id[32 * NW];
-};
-struct Pf2 {
-    float4 g0, g1;
-    int id;
-    bool have;
-};
-template <int DIR = -1>
-__device__ __forceinline__ void prefetch2(Pf2& pf, int word, int first, int n_entries, const float4* __restrict__ rec,
-                                          const int32_t* __restrict__ vals, int lane) {
-    const int e = 32 * word + lane;
-    const int id = (e < n_entries) ? __ldg(vals + first + DIR * e) : -1;
-    pf.have = id >= 0;
-    pf.id = pf.have ? id : 0;
-    pf.g0 = make_float4(0.f, 0.f, 0.f, 0.f);
-    pf.g1 = pf.g0;
-    if (pf.have) {
-        const float4* r = rec + 3 * (int64_t)id;
-        pf.g0 = __ldg(r);
-        pf.g1 = __ldg(r + 1);
-    }
-}
-template <int NW>
-__device__ __forceinline__ void commit_masks(MRing<NW>& st, const Pf2& pf, int word, float bx0, float by0, int lane) {
-    const unsigned wsl = ((unsigned)word & (NW - 1)) * 32u;
-    __syncwarp();
-    st.id[wsl + lane] = pf.id;
-    publish_hits(st, pf.have, pf.g0, pf.g1, wsl, bx0, by0, lane);
-    __syncwarp();
-}
-// initial fill: batches of 8 words, every load of a batch in flight at once (ids, then the two geometry float4)
-template <int NW, int DIR>
-__device__ __forceinline__ int initial_fill_masks(MRing<NW>& st, int first, int n_entries, int n_words,
-                                                  const float4* __restrict__ rec, const int32_t* __restrict__ vals,
-                                                  float bx0, float by0, int lane) {
-    const int nfill = min(NW, n_words);
-    for (int w0 = 0; w0 < nfill; w0 += 8) {
-        int ids[8];
-        float4 g0[8], g1[8];
-#pragma unroll
-        for (int w = 0; w < 8; ++w) {
-            const int e = 32 * (w0 + w) + lane;
-            ids[w] = (w0 + w < nfill && e < n_entries) ? __ldg(vals + first + DIR * e) : -1;
-        }
-#pragma unroll
-        for (int w = 0; w < 8; ++w) {
-            g0[w] = make_float4(0.f, 0.f, 0.f, 0.f);
-            g1[w] = g0[w];
-            if (ids[w] >= 0) {
-                const float4* r = rec + 3 * (int64_t)ids[w];
-                g0[w] = __ldg(r);
-                g1[w] = __ldg(r + 1);
-            }
-        }
-#pragma unroll
-        for (int w = 0; w < 8; ++w) {
-            if (w0 + w < nfill) {                      // warp-uniform
-                const unsigned wsl = 32u * (unsigned)(w0 + w);
-                st.id[wsl + lane] = ids[w] >= 0 ? ids[w] : 0;
-                publish_hits(st, ids[w] >= 0, g0[w], g1[w], wsl, bx0, by0, lane);
-            }
-        }
-    }
-    __syncwarp();
-    return nfill;
-}
-
-// ---- mask-queue variant (experiment): the ring holds ONLY the per-quad hit masks and the Gaussian ids (256 B per
-// 32-entry word instead of 1 792 B), so a window of 32 words = 1 024 entries fits in 8 KB per warp and the window no
-// longer limits how far a fast quad runs ahead; the 48-byte record of a hit is gathered from global memory (L1 / L2
-// resident) when the lane evaluates it.
-template <int CH, int NW, bool GEOM, int HITS>
-__global__ void __launch_bounds__(THREADS, HITS == 1 ? 8 : 7)
-blend_bwd_mq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* __restrict__ vals,
-                    const int32_t* __restrict__ ranges, const float* __restrict__ alpha,
-                    const int32_t* __restrict__ last, const float* __restrict__ v_render,
-                    const float* __restrict__ v_alpha, float* __restrict__ v_rec) {
-    extern __shared__ __align__(16) unsigned char s_raw[];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    using R = MRing<NW>;
-    R& st = reinterpret_cast<R*>(s_raw)[wid];
-    // half tile h = 2 * tile_y + half; a CTA holds blockDim.x / 32 consecutive halves of one tile column
-    const int hidx = blockIdx.y * (blockDim.x >> 5) + wid, ty = hidx >> 1, half = hidx & 1;
-    const int tile = ty * cam.tw + blockIdx.x;
-    const int qx = lane & 7, qy = lane >> 3;
-    const int x0 = blockIdx.x * TILE + 2 * qx, y0 = ty * TILE + 8 * half + 2 * qy;
-    const float bx0 = (float)(blockIdx.x * TILE) + 0.5f, by0 = (float)(ty * TILE + 8 * half) + 0.5f;
-    const float pxa = (float)x0 + 0.5f, pxb = (float)x0 + 1.5f, pya = (float)y0 + 0.5f, pyb = (float)y0 + 1.5f;
-    const int start = ranges[tile];
-    const int64_t P = (int64_t)cam.width * cam.height;
-
-    int first[4]; // first list entry (back to front) that contributed to pixel p
-    float T[4], bdot[4], va_eff[4], vr[4][CH];
-    int quad_last = start - 1;
-#pragma unroll
-    for (int p = 0; p < 4; ++p) {
-        const int xi = x0 + (p & 1), yi = y0 + (p >> 1);
-        const bool inside = xi < cam.width && yi < cam.height;
-        const int64_t pix = inside ? (int64_t)yi * cam.width + xi : 0;
-        const int my_last = inside ? last[pix] : start - 1;
-        first[p] = my_last; // turned into an entry index below
-        quad_last = max(quad_last, my_last);
-        const float T_final = inside ? 1.0f - alpha[pix] : 1.0f;
-        T[p] = T_final;
-#pragma unroll
-        for (int k = 0; k < CH; ++k) vr[p][k] = inside ? v_render[k * P + pix] : 0.f;
-        const float va = (inside && v_alpha) ? v_alpha[pix] : 0.f;
-        float bg_dot = 0.f;
-#pragma unroll
-        for (int k = 0; k < 3; ++k) bg_dot += cam.bg[k] * vr[p][k];
-        va_eff[p] = T_final * (va - bg_dot);
-        bdot[p] = 0.f;
-    }
-    const int warp_last = __reduce_max_sync(FULL, quad_last);
-    if (warp_last < start) return; // nothing was blended into this warp's half tile
-    const int n_entries = warp_last - start + 1;
-    const int n_words = (n_entries + 31) >> 5;
-    const int e_first = warp_last - quad_last;
-#pragma unroll
-    for (int p = 0; p < 4; ++p) first[p] = warp_last - first[p];
-
-    int staged = 0, base = 0; // warp-uniform: words [base, staged) are live in the ring
-    staged = initial_fill_masks<NW, -1>(st, warp_last, n_entries, n_words, rec, vals, bx0, by0, lane);
-    Pf2 pf;
-    prefetch2(pf, staged, warp_last, n_entries, rec, vals, lane);
-    static_assert((NW & (NW - 1)) == 0, "NW must be a power of two");
-    const uint32_t* hq = st.hits + lane; // this quad's hit word of ring slot base wsl is hq[wsl]
-    auto fetch = [&](int w, unsigned wsl_) -> uint32_t {
-        const uint32_t m = hq[wsl_];
-        const int cut = e_first - 32 * w; // entries in front of e_first lie behind this quad's last contributor
-        return cut <= 0 ? m : (cut >= 32 ? 0u : (m & ~((1u << cut) - 1u)));
-    };
-    int jq = min(e_first >> 5, staged - 1);
-    unsigned wsl = ((unsigned)jq & (NW - 1)) * 32u;
-    uint32_t bits = fetch(jq, wsl);
-    if (quad_last < start) { jq = FAR; bits = 0u; wsl = 0u; }
-    // ---- software-pipelined walk: the records of the NEXT iteration's hits are requested before the current
-    // iteration's are evaluated, so the L1 / L2 latency of the gather hides behind one whole body
-    struct Sel { float4 g0, g1, g2; int id, e; };
-    Sel cur[HITS], nxt[HITS];
-    auto select = [&](Sel (&o)[HITS]) {
-        if (bits == 0u && jq + 1 < staged) {
-            ++jq;
-            wsl = (wsl + 32u) & (32u * NW - 1u);
-            bits = fetch(jq, wsl);
-        }
-#pragma unroll
-        for (int k = 0; k < HITS; ++k) {
-            const bool on = bits != 0u;
-            const int sk = on ? __ffs(bits) - 1 : 0;
-            bits &= bits - 1u;
-            o[k].e = on ? 32 * jq + sk : -1;
-            o[k].id = on ? st.id[wsl + sk] : -1;
-            o[k].g0 = make_float4(0.f, 0.f, 0.f, 0.f);
-            o[k].g1 = o[k].g0;
-            o[k].g2 = o[k].g0;
-            if (on) {
-                const float4* r = rec + 3 * (int64_t)o[k].id;
-                o[k].g0 = __ldg(r);
-                o[k].g1 = __ldg(r + 1);
-                o[k].g2 = __ldg(r + 2);
-            }
-        }
-    };
-    select(cur);
-    while (true) {
-        select(nxt);
-        // the word this quad reads next: every ring word in front of the minimum over the quads can be retired (the
-        // ids / masks of the selected hits are already in registers)
-        const int wmin = __reduce_min_sync(FULL, bits != 0u ? jq : jq + 1);
-        bool pending = false;
-#pragma unroll
-        for (int k = 0; k < HITS; ++k) pending |= (cur[k].e >= 0) || (nxt[k].e >= 0);
-        if (wmin >= n_words && !__any_sync(FULL, pending)) break;
-        bool anyv = false;
-        float dxs[HITS][2], dys[HITS][2], sigma[HITS][4];
-        bool valid[HITS][4], anyk[HITS];
-#pragma unroll
-        for (int k = 0; k < HITS; ++k) {
-            const Sel& c = cur[k];
-            dxs[k][0] = __fsub_rn(c.g0.x, pxa); dxs[k][1] = __fsub_rn(c.g0.x, pxb);
-            dys[k][0] = __fsub_rn(c.g0.y, pya); dys[k][1] = __fsub_rn(c.g0.y, pyb);
-            const float zxa = __fmul_rn(c.g0.z, dxs[k][0]), zxb = __fmul_rn(c.g0.z, dxs[k][1]);
-            const float cya = __fmul_rn(__fmul_rn(c.g1.x, dys[k][0]), dys[k][0]);
-            const float cyb = __fmul_rn(__fmul_rn(c.g1.x, dys[k][1]), dys[k][1]);
-            sigma[k][0] = __fmaf_rn(__fmaf_rn(c.g0.w, dys[k][0], zxa), dxs[k][0], cya);
-            sigma[k][1] = __fmaf_rn(__fmaf_rn(c.g0.w, dys[k][0], zxb), dxs[k][1], cya);
-            sigma[k][2] = __fmaf_rn(__fmaf_rn(c.g0.w, dys[k][1], zxa), dxs[k][0], cyb);
-            sigma[k][3] = __fmaf_rn(__fmaf_rn(c.g0.w, dys[k][1], zxb), dxs[k][1], cyb);
-            anyk[k] = false;
-#pragma unroll
-            for (int p = 0; p < 4; ++p) {
-                valid[k][p] = c.e >= first[p] && sigma[k][p] >= 0.f && sigma[k][p] <= c.g1.y;
-                anyk[k] |= valid[k][p];
-            }
-            anyv |= anyk[k];
-        }
-        if (__any_sync(FULL, anyv)) {
-#pragma unroll
-            for (int k = 0; k < HITS; ++k) {
-                const Sel& c = cur[k];
-                const float4 g2 = c.g2;
-                const float opac = c.g1.z;
-                float Swx = 0.f, Swy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f, Su = 0.f;
-                float col[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-                for (int p = 0; p < 4; ++p) {
-                    const float dx = dxs[k][p & 1], dy = dys[k][p >> 1];
-                    const float vis = __expf(valid[k][p] ? -sigma[k][p] : 0.f);
-                    const float ov = opac * vis;
-                    const float a = fminf(MAX_ALPHA, ov);
-                    const float ra = __fdividef(1.0f, 1.0f - a);
-                    const float Tn = T[p] * ra;
-                    T[p] = valid[k][p] ? Tn : T[p];
-                    const float fac = valid[k][p] ? a * Tn : 0.f;
-                    float cdot = c.g1.w * vr[p][0];
-                    cdot = fmaf(g2.x, vr[p][1], cdot);
-                    cdot = fmaf(g2.y, vr[p][2], cdot);
-                    cdot = fmaf(g2.z, vr[p][3], cdot);
-                    if (CH == 5) cdot = fmaf(g2.w, vr[p][CH - 1], cdot);
-                    const float v_a = fmaf(Tn, cdot, ra * (va_eff[p] - bdot[p]));
-                    bdot[p] = fmaf(fac, cdot, bdot[p]);
-                    const float u = (valid[k][p] && ov <= MAX_ALPHA) ? vis * v_a : 0.f;
-                    const float v_sigma = -opac * u;
-                    const float wx = v_sigma * dx, wy = v_sigma * dy;
-                    Swx += wx;
-                    Swy += wy;
-                    Sxx = fmaf(wx, dx, Sxx);
-                    Sxy = fmaf(wx, dy, Sxy);
-                    Syy = fmaf(wy, dy, Syy);
-                    if (!GEOM) {
-                        Su += u;
-#pragma unroll
-                        for (int cc = 0; cc < 3; ++cc) col[cc] = fmaf(fac, vr[p][cc], col[cc]);
-                    }
-#pragma unroll
-                    for (int cc = 3; cc < CH; ++cc) col[cc] = fmaf(fac, vr[p][cc], col[cc]);
-                }
-                if (anyk[k]) {
-                    const float ca = 2.0f * c.g0.z, cb = c.g0.w, cc2 = 2.0f * c.g1.x;
-                    const float v0 = fmaf(ca, Swx, cb * Swy), v1 = fmaf(cb, Swx, cc2 * Swy);
-                    float* dst = v_rec + (int64_t)c.id * REC;
-                    red_add_v4(dst, v0, v1, 0.5f * Sxx, Sxy);
-                    if (GEOM) {
-                        atomicAdd(dst + 4, 0.5f * Syy);
-                        red_add_v4(dst + 8, 0.f, col[3], col[4], 0.f);
-                    } else {
-                        red_add_v4(dst + 4, 0.5f * Syy, Su, col[0], col[1]);
-                        red_add_v4(dst + 8, col[2], col[3], col[4], 0.f);
-                    }
-                }
-            }
-        }
-        if (wmin > base) {
-            ++base;
-            if (staged < n_words) {
-                commit_masks<NW>(st, pf, staged, bx0, by0, lane);
-                ++staged;
-                prefetch2(pf, staged, warp_last, n_entries, rec, vals, lane);
-            }
-        }
-#pragma unroll
-        for (int k = 0; k < HITS; ++k) cur[k] = nxt[k];
     }
 }
 
@@ -802,15 +524,6 @@ int launch(const DevCam& dc, const float* rec, const int32_t* vals, const int32_
         attr_dev = dev;
     }
     dim3 grid(dc.tw, dc.th);
-    static const int mq = [] { const char* e = getenv("ISOGS_MQ"); return e ? atoi(e) : 0; }();
-    if (mq && !GEOM && CH == 5) {
-        if (mq == 2)
-            blend_bwd_mq_kernel<CH, 32, GEOM, 1><<<grid, THREADS, sizeof(MRing<32>) * WARPS, stream>>>(
-                dc, (const float4*)rec, vals, ranges, alpha, last, v_render, v_alpha, v_rec);
-        else
-            blend_bwd_mq_kernel<CH, 32, GEOM, HITS><<<grid, THREADS, sizeof(MRing<32>) * WARPS, stream>>>(
-                dc, (const float4*)rec, vals, ranges, alpha, last, v_render, v_alpha, v_rec);
-    } else
     blend_bwd_lq_kernel<CH, NW, GEOM, HITS><<<grid, THREADS, smem, stream>>>(dc, (const float4*)rec, vals, ranges, alpha, last,
                                                                                  v_render, v_alpha, v_rec);
     ISOGS_CUDA(cudaGetLastError());
