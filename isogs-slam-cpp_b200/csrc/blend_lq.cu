@@ -173,6 +173,14 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+// sigma in [0, L]  <=>  bits(sigma) < bits(L) + 1 as UNSIGNED integers (negative and NaN sigmas have the sign bit set
+// or exceed every finite L; a negative L admits nothing): ONE integer compare per pixel instead of two float compares
+// and a predicate AND.  on = false (the lane has no hit this iteration) admits nothing either.  (-0.0 cannot come out
+// of the sigma expression: its last addend is a square, +0 at least, and x + (+0) rounds to +0.)
+__device__ __forceinline__ uint32_t sigma_limit(float L, bool on) {
+    return (on && L >= 0.f) ? __float_as_uint(L) + 1u : 0u;
+}
+
 // one (quad, Gaussian) pair being evaluated by a lane
 struct Hit {
     float4 g0, g1;
@@ -281,9 +289,10 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
             h[k].sigma[2] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[1], zxa), h[k].dx[0], cyb);
             h[k].sigma[3] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[1], zxb), h[k].dx[1], cyb);
             h[k].any = false;
+            const uint32_t lim = sigma_limit(h[k].g1.y, true);   // (no hit: e = -1 < first[p])
 #pragma unroll
             for (int p = 0; p < 4; ++p) {
-                h[k].valid[p] = h[k].e >= first[p] && h[k].sigma[p] >= 0.f && h[k].sigma[p] <= h[k].g1.y;
+                h[k].valid[p] = h[k].e >= first[p] && __float_as_uint(h[k].sigma[p]) < lim;
                 h[k].any |= h[k].valid[p];
             }
         }
@@ -301,8 +310,9 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
 #pragma unroll
                 for (int p = 0; p < 4; ++p) {
                     const float dx = hk.dx[p & 1], dy = hk.dy[p >> 1];
-                    // branch-free: an invalid pixel runs with sigma = 0 and contributes exact zeros
-                    const float vis = __expf(hk.valid[p] ? -hk.sigma[p] : 0.f);
+                    // branch-free: every use of an invalid pixel's values below is behind a select on valid[p] (or
+                    // multiplies an exact 0), so its sigma needs no clamping
+                    const float vis = __expf(-hk.sigma[p]);
                     const float ov = opac * vis;
                     const float a = fminf(MAX_ALPHA, ov);
                     const float ra = __fdividef(1.0f, 1.0f - a);
@@ -433,10 +443,11 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                 h[k].sigma[2] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[1], zxa), h[k].dx[0], cyb);
                 h[k].sigma[3] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[1], zxb), h[k].dx[1], cyb);
                 h[k].any = false;
+                const uint32_t lim = sigma_limit(h[k].g1.y, on);
 #pragma unroll
                 for (int p = 0; p < 4; ++p) {
                     // (liveness is re-checked when the hit is applied: an earlier hit of this iteration may saturate the pixel)
-                    h[k].valid[p] = on && h[k].sigma[p] >= 0.f && h[k].sigma[p] <= h[k].g1.y;
+                    h[k].valid[p] = __float_as_uint(h[k].sigma[p]) < lim;
                     h[k].any |= h[k].valid[p] && T[p] > 0.f;
                 }
             }
@@ -452,7 +463,8 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
 #pragma unroll
                     for (int p = 0; p < 4; ++p) {
                         const bool hit = hk.valid[p] && T[p] > 0.f;
-                        const float a = fminf(MAX_ALPHA, hk.g1.z * __expf(hit ? -hk.sigma[p] : 0.f));
+                        // (a pixel that is not hit may evaluate anything here: every use below is behind a select)
+                        const float a = fminf(MAX_ALPHA, hk.g1.z * __expf(-hk.sigma[p]));
                         const float nT = T[p] * (1.0f - a);
                         const bool sat = hit && nT <= T_CUTOFF;
                         const bool contrib = hit && !sat;
@@ -466,7 +478,10 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                         T[p] = contrib ? nT : (sat ? -T[p] : T[p]);
                     }
                 }
-                if (T[0] < 0.f && T[1] < 0.f && T[2] < 0.f && T[3] < 0.f) { jq = FAR; bits = 0u; } // quad saturated
+                // quad saturated: all four sign bits set
+                if ((int32_t)(__float_as_uint(T[0]) & __float_as_uint(T[1]) & __float_as_uint(T[2]) & __float_as_uint(T[3])) < 0) {
+                    jq = FAR; bits = 0u;
+                }
             }
             if (wmin > base) {
                 ++base;
