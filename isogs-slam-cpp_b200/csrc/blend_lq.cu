@@ -310,15 +310,15 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
 #pragma unroll
                 for (int p = 0; p < 4; ++p) {
                     const float dx = hk.dx[p & 1], dy = hk.dy[p >> 1];
-                    // branch-free: every use of an invalid pixel's values below is behind a select on valid[p] (or
-                    // multiplies an exact 0), so its sigma needs no clamping
-                    const float vis = __expf(-hk.sigma[p]);
+                    // branch-free with ONE select: an invalid pixel runs with sigma = +huge, so vis = a = 0 exactly,
+                    // ra = 1, Tn = T and every term it adds below is an exact zero
+                    const float vis = __expf(hk.valid[p] ? -hk.sigma[p] : -1e30f);
                     const float ov = opac * vis;
                     const float a = fminf(MAX_ALPHA, ov);
                     const float ra = __fdividef(1.0f, 1.0f - a);
                     const float Tn = T[p] * ra; // transmittance in front of this Gaussian
-                    T[p] = hk.valid[p] ? Tn : T[p];
-                    const float fac = hk.valid[p] ? a * Tn : 0.f;
+                    T[p] = Tn;
+                    const float fac = a * Tn;
                     float cdot = hk.g1.w * vr[p][0];
                     cdot = fmaf(g2.x, vr[p][1], cdot);
                     cdot = fmaf(g2.y, vr[p][2], cdot);
@@ -326,7 +326,7 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                     if (CH == 5) cdot = fmaf(g2.w, vr[p][CH - 1], cdot);
                     const float v_a = fmaf(Tn, cdot, ra * (va_eff[p] - bdot[p]));
                     bdot[p] = fmaf(fac, cdot, bdot[p]);
-                    const float u = (hk.valid[p] && ov <= MAX_ALPHA) ? vis * v_a : 0.f;
+                    const float u = (ov <= MAX_ALPHA) ? vis * v_a : 0.f;
                     const float v_sigma = -opac * u;
                     const float wx = v_sigma * dx, wy = v_sigma * dy;
                     Swx += wx;
