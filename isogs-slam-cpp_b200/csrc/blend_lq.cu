@@ -289,11 +289,16 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
             h[k].sigma[2] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[1], zxa), h[k].dx[0], cyb);
             h[k].sigma[3] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[1], zxb), h[k].dx[1], cyb);
             h[k].any = false;
-            const uint32_t lim = sigma_limit(h[k].g1.y, true);   // (no hit: e = -1 < first[p])
+            uint32_t lim = sigma_limit(h[k].g1.y, true);   // (no hit: e = -1 < first[p])
+            asm volatile("" : "+r"(lim));                   // one limit per hit, not re-derived per pixel
+            // all the predicate work of a hit happens here: a pixel the Gaussian does not reach (or that lies behind
+            // the pixel's last contributor) gets sigma = +huge, so that below vis = a = 0 EXACTLY, ra = 1, Tn = T and
+            // every term it adds is an exact zero -- the body needs no per-pixel flags
 #pragma unroll
             for (int p = 0; p < 4; ++p) {
-                h[k].valid[p] = h[k].e >= first[p] && __float_as_uint(h[k].sigma[p]) < lim;
-                h[k].any |= h[k].valid[p];
+                const bool v = h[k].e >= first[p] && __float_as_uint(h[k].sigma[p]) < lim;
+                h[k].sigma[p] = v ? h[k].sigma[p] : 1e30f;
+                h[k].any |= v;
             }
         }
         bool anyv = h[0].any;
@@ -310,9 +315,7 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
 #pragma unroll
                 for (int p = 0; p < 4; ++p) {
                     const float dx = hk.dx[p & 1], dy = hk.dy[p >> 1];
-                    // branch-free with ONE select: an invalid pixel runs with sigma = +huge, so vis = a = 0 exactly,
-                    // ra = 1, Tn = T and every term it adds below is an exact zero
-                    const float vis = __expf(hk.valid[p] ? -hk.sigma[p] : -1e30f);
+                    const float vis = __expf(-hk.sigma[p]);
                     const float ov = opac * vis;
                     const float a = fminf(MAX_ALPHA, ov);
                     const float ra = __fdividef(1.0f, 1.0f - a);
