@@ -446,12 +446,21 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                 h[k].sigma[2] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[1], zxa), h[k].dx[0], cyb);
                 h[k].sigma[3] = __fmaf_rn(__fmaf_rn(h[k].g0.w, h[k].dy[1], zxb), h[k].dx[1], cyb);
                 h[k].any = false;
-                const uint32_t lim = sigma_limit(h[k].g1.y, on);
+                uint32_t lim = sigma_limit(h[k].g1.y, on);
+                asm volatile("" : "+r"(lim));
 #pragma unroll
                 for (int p = 0; p < 4; ++p) {
-                    // (liveness is re-checked when the hit is applied: an earlier hit of this iteration may saturate the pixel)
-                    h[k].valid[p] = __float_as_uint(h[k].sigma[p]) < lim;
-                    h[k].any |= h[k].valid[p] && T[p] > 0.f;
+                    if (HITS == 1) {
+                        // one hit per iteration: the pixel's liveness cannot change before the hit is applied, so it is
+                        // folded in here and a pixel that is not hit gets sigma = +huge (a = 0 exactly below)
+                        const bool v = __float_as_uint(h[k].sigma[p]) < lim && T[p] > 0.f;
+                        h[k].sigma[p] = v ? h[k].sigma[p] : 1e30f;
+                        h[k].any |= v;
+                    } else {
+                        // (liveness is re-checked when the hit is applied: an earlier hit of this iteration may saturate the pixel)
+                        h[k].valid[p] = __float_as_uint(h[k].sigma[p]) < lim;
+                        h[k].any |= h[k].valid[p] && T[p] > 0.f;
+                    }
                 }
             }
             bool anyh = h[0].any;
@@ -465,6 +474,22 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                     const int idx = start + hk.e;
 #pragma unroll
                     for (int p = 0; p < 4; ++p) {
+                        if (HITS == 1) {
+                            // a = 0 exactly for a pixel that is not hit (or done): nT = T, vis = 0.  A live pixel has
+                            // T > T_CUTOFF, a done one T < 0 (so has nT): "live and nT <= cutoff" is ONE unsigned compare
+                            const float a = fminf(MAX_ALPHA, hk.g1.z * __expf(-hk.sigma[p]));
+                            const float nT = T[p] * (1.0f - a);
+                            const bool sat = __float_as_uint(nT) <= __float_as_uint(T_CUTOFF);
+                            const float vis = sat ? 0.f : a * T[p];
+                            acc[p][0] = fmaf(hk.g1.w, vis, acc[p][0]);
+                            acc[p][1] = fmaf(g2.x, vis, acc[p][1]);
+                            acc[p][2] = fmaf(g2.y, vis, acc[p][2]);
+                            acc[p][3] = fmaf(g2.z, vis, acc[p][3]);
+                            if (CH == 5) acc[p][CH - 1] = fmaf(g2.w, vis, acc[p][CH - 1]);
+                            last_idx[p] = vis > 0.f ? idx : last_idx[p];
+                            T[p] = sat ? -T[p] : nT;
+                            continue;
+                        }
                         const bool hit = hk.valid[p] && T[p] > 0.f;
                         // (a pixel that is not hit may evaluate anything here: every use below is behind a select)
                         const float a = fminf(MAX_ALPHA, hk.g1.z * __expf(-hk.sigma[p]));
