@@ -2,7 +2,7 @@
 # Usage: gpurun --gpus N -- bash scripts/scale_check.sh <tag> N
 TAG=$1; N=$2
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_multi.py -q -s > gpurun_out/${TAG}_multi_pytest.log 2>&1; grep -E "MULTI_GPU_PARITY|passed|failed|skipped" gpurun_out/${TAG}_multi_pytest.log | cut -c1-700
+[ -n "$SKIP_PYTEST" ] || timeout 900 python -m pytest tests/test_gpu_multi.py -q -s > gpurun_out/${TAG}_multi_pytest.log 2>&1; grep -E "MULTI_GPU_PARITY|passed|failed|skipped" gpurun_out/${TAG}_multi_pytest.log | cut -c1-700
 for mode in ${MODES:-nvls fused p2p nccl}; do
   timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29577 bench.py --gpus $N --steps 20 --warmup 5 --allreduce $mode > gpurun_out/${TAG}_bench_${N}gpu_$mode.json 2> gpurun_out/${TAG}_bench_${N}gpu_$mode.err || tail -5 gpurun_out/${TAG}_bench_${N}gpu_$mode.err
   python - <<PY
