@@ -298,6 +298,7 @@ blend_bwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
             for (int p = 0; p < 4; ++p) {
                 const bool v = h[k].e >= first[p] && __float_as_uint(h[k].sigma[p]) < lim;
                 h[k].sigma[p] = v ? h[k].sigma[p] : 1e30f;
+                asm volatile("" : "+f"(h[k].sigma[p]));   // select HERE: the predicate dies instead of riding into the body
                 h[k].any |= v;
             }
         }
@@ -455,6 +456,7 @@ blend_fwd_lq_kernel(DevCam cam, const float4* __restrict__ rec, const int32_t* _
                         // folded in here and a pixel that is not hit gets sigma = +huge (a = 0 exactly below)
                         const bool v = __float_as_uint(h[k].sigma[p]) < lim && T[p] > 0.f;
                         h[k].sigma[p] = v ? h[k].sigma[p] : 1e30f;
+                        asm volatile("" : "+f"(h[k].sigma[p]));   // select HERE: the predicate dies instead of riding into the body
                         h[k].any |= v;
                     } else {
                         // (liveness is re-checked when the hit is applied: an earlier hit of this iteration may saturate the pixel)
