@@ -17,9 +17,10 @@ preprocess_fwd_kernel(DevCam cam, DevPose pose, int64_t N, const float* __restri
                       int n_bins) {
     // fused tile count (intersect_tile pass 1 + the histogram of the counting sort): CTA-private bins in shared
     // memory, ONE global atomic per (CTA, touched tile); n_bins = 0: no shared bins (more tiles than fit)
-    extern __shared__ int32_t s_bins[];
+    extern __shared__ __align__(16) int32_t s_bins[];   // n_bins rounded up to a multiple of 4 (16-byte clears / reads)
+    const int n_bins4 = (n_bins + 3) >> 2;
     if (tile_counts != nullptr && n_bins > 0) {
-        for (int b = threadIdx.x; b < n_bins; b += blockDim.x) s_bins[b] = 0;
+        for (int b = threadIdx.x; b < n_bins4; b += blockDim.x) reinterpret_cast<int4*>(s_bins)[b] = make_int4(0, 0, 0, 0);
         __syncthreads();
     }
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -76,9 +77,15 @@ preprocess_fwd_kernel(DevCam cam, DevPose pose, int64_t N, const float* __restri
             for (int y = tr.y0; y < tr.y1; ++y)
                 for (int x = tr.x0; x < tr.x1; ++x) atomicAdd(s_bins + (y * cam.tw + x), 1);
             __syncthreads();
-            for (int b = threadIdx.x; b < n_bins; b += blockDim.x) {
-                const int32_t c = s_bins[b];
-                if (c) atomicAdd(tile_counts + b, c);
+            // a CTA's 256 Gaussians touch a few dozen of the bins: read four at a time, most groups are all zero
+            for (int b = threadIdx.x; b < n_bins4; b += blockDim.x) {
+                const int4 c = reinterpret_cast<const int4*>(s_bins)[b];
+                if ((c.x | c.y | c.z | c.w) != 0) {
+                    if (c.x) atomicAdd(tile_counts + 4 * b, c.x);
+                    if (c.y) atomicAdd(tile_counts + 4 * b + 1, c.y);
+                    if (c.z) atomicAdd(tile_counts + 4 * b + 2, c.z);
+                    if (c.w) atomicAdd(tile_counts + 4 * b + 3, c.w);
+                }
             }
         } else {
             for (int y = tr.y0; y < tr.y1; ++y)
@@ -368,7 +375,7 @@ extern "C" int isogs_preprocess_fwd(const isogs_camera* cam, const isogs_pose* p
     const unsigned grid = (unsigned)((N + block - 1) / block);
     const int n_tiles = dc.tw * dc.th;
     const int n_bins = (tile_counts != nullptr && n_tiles <= 11264) ? n_tiles : 0; // 44 KB of bins: default 48 KB limit
-    const size_t smem = sizeof(int32_t) * (size_t)n_bins;
+    const size_t smem = sizeof(int32_t) * (size_t)((n_bins + 3) & ~3);
     if (scale_dim == 1)
         preprocess_fwd_kernel<true><<<grid, block, smem, stream>>>(dc, dp, N, means, scales, quats, opacities, colors,
                                                                     ch, flags, (float4*)rec, (int2*)radii, tiles,
