@@ -17,6 +17,16 @@ def _bench():
     return importlib.import_module("bench")
 
 
+def _latest_tag():
+    """Tag of the newest complete record set under profiles/ (bench line + reference arm + ncu launch list)."""
+    tags = sorted(os.path.basename(p)[:-len("_launches.csv")] for p in glob.glob(os.path.join(ROOT, "profiles", "r*_launches.csv")))
+    tags = [t for t in tags if os.path.exists(os.path.join(ROOT, "profiles", f"{t}_bench.json"))
+            and os.path.exists(os.path.join(ROOT, "profiles", f"{t}_bench_reference_arm.json"))
+            and "parity" in json.load(open(os.path.join(ROOT, "profiles", f"{t}_bench.json")))]
+    assert tags, "no complete record set (bench line with parity + reference arm + launch list) under profiles/"
+    return tags[-1]
+
+
 def test_traffic_json_has_the_per_shape_layout_the_bench_reads():
     d = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
     shapes = d["shapes"]
@@ -32,9 +42,8 @@ def test_traffic_json_has_the_per_shape_layout_the_bench_reads():
 
 
 def test_committed_bench_record_carries_the_contract_keys():
-    recs = sorted(glob.glob(os.path.join(ROOT, "profiles", "r3h_bench.json")))
-    assert recs, "the round's bench record is committed under profiles/"
-    d = json.load(open(recs[-1]))
+    tag = _latest_tag()
+    d = json.load(open(os.path.join(ROOT, "profiles", f"{tag}_bench.json")))
     for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
               "vs_baseline", "dtype", "data", "config", "e2e", "gpu_launches", "roofline", "cpu_baseline", "clocks",
               "parity", "stage_ms", "timing"):
@@ -47,17 +56,17 @@ def test_committed_bench_record_carries_the_contract_keys():
     assert d["parity"]["loss_rel"] < 1e-5 and d["parity"]["param_step_rel"] < 1e-2
     b = _bench()
     assert d["config"]["workload"] == b.workload_string("replica", 1200, 680, 1000000, b.WINDOW)
-    ref = json.load(open(os.path.join(ROOT, "profiles", "r3h_bench_reference_arm.json")))
+    ref = json.load(open(os.path.join(ROOT, "profiles", f"{tag}_bench_reference_arm.json")))
     assert ref["impl"] == "reference" and ref["config"]["workload"] == d["config"]["workload"]
     assert ref["metric"] == d["metric"] and ref["unit"] == d["unit"]
 
 
 def test_launch_count_constant_agrees_with_the_ncu_launch_list():
-    """profiles/r3h_launches.csv lists every launch of 6 eager mapping iterations: our kernels per iteration must be
+    """profiles/<tag>_launches.csv lists every launch of 6 eager mapping iterations: our kernels per iteration must be
     what bench.launches_per_step() says, and no torch kernel may appear once the iterations have started."""
     b = _bench()
     names = []
-    with open(os.path.join(ROOT, "profiles", "r3h_launches.csv")) as f:
+    with open(os.path.join(ROOT, "profiles", f"{_latest_tag()}_launches.csv")) as f:
         rows = [r for r in csv.reader(f) if len(r) > 4]
     hdr = next(r for r in rows if "Kernel Name" in r)
     ik, im = hdr.index("Kernel Name"), hdr.index("Metric Name")
