@@ -270,8 +270,8 @@ def run_ours(args):
         k["rgb8_h"] = torch.from_numpy(k["rgb8"]).pin_memory()
         k["d16_h"] = torch.from_numpy(k["d16"].view(np.int16)).pin_memory()
     # e2e arm: every step's keyframe comes from PINNED HOST memory in the reference's source formats (5 bytes per
-    # pixel).  The copy of step i+1 runs on a copy stream while step i computes (two staging slots); isogs_unpack_rgbd
-    # expands it into the fp32 planes the step reads; the loss scalars of step i are read on the host while step i+1
+    # pixel).  The copy of step i+1 runs on a copy stream while step i computes (two staging slots) and isogs_unpack_rgbd
+    # expands it into the fp32 planes the step reads on that stream as well; the loss scalars of step i are read on the host while step i+1
     # is in flight (one step late), so no step waits on the PCIe round trip.
     copy_stream = torch.cuda.Stream(device=dev)
     slots = [dict(rgb8=torch.empty((H, W, 3), dtype=torch.uint8, device=dev),
@@ -295,6 +295,10 @@ def run_ours(args):
             copy_stream.wait_event(s["free"])          # the step that last used this slot has finished
             s["rgb8"].copy_(k["rgb8_h"], non_blocking=True)
             s["d16"].copy_(k["d16_h"], non_blocking=True)
+            # the unpack into the fp32 planes rides on the copy stream too, behind its copy: it overlaps the step in flight
+            pkg._lib.check(L.isogs_unpack_rgbd(C.byref(cam), C.c_void_p(s["rgb8"].data_ptr()), C.c_void_p(s["d16"].data_ptr()),
+                                               k["inv_scale"], C.c_void_p(s["rgb"].data_ptr()), C.c_void_p(s["depth"].data_ptr()),
+                                               C.c_void_p(copy_stream.cuda_stream)))
             s["ready"].record(copy_stream)
         e2e_state["prefetched"] = i
 
@@ -304,10 +308,7 @@ def run_ours(args):
             e2e_prefetch(i)
         e2e_prefetch(i + 1)
         s, k = slots[i % 2], kfs[dp.keyframe_for(i, rank, world, WINDOW)]
-        cur.wait_event(s["ready"])
-        pkg._lib.check(L.isogs_unpack_rgbd(C.byref(cam), C.c_void_p(s["rgb8"].data_ptr()), C.c_void_p(s["d16"].data_ptr()),
-                                           k["inv_scale"], C.c_void_p(s["rgb"].data_ptr()), C.c_void_p(s["depth"].data_ptr()),
-                                           C.c_void_p(cur.cuda_stream)))
+        cur.wait_event(s["ready"])                     # copy + unpack of THIS step's frame have finished
         losses = ss.map_step(ws, gmap, k["pose"], s["rgb"], s["depth"], k["inv_nd"], allreduce=ar, graph=use_graph)
         s["free"].record(cur)
         s["loss"].copy_(losses, non_blocking=True)
