@@ -147,6 +147,33 @@ def test_oracle_mapping_matches_reference(orc, fx):
         _check_adam_update(st["p"][k], fx[f"map_out_{k}"], fx[f"map_grad_{k}"], osl.MAP_LRS[k], 2, rows, k)
 
 
+MODES = os.path.join(ROOT, "tests", "golden", "splatam_modes_64x48.npz")
+
+
+@pytest.mark.parametrize("mode", ["outlier", "ba"])
+def test_oracle_mapping_side_modes_match_reference(orc, fx, mode):
+    """The two get_loss modes the shipped configs leave off, against the reference's OWN get_loss
+    (tests/golden/splatam_modes_64x48.npz from oracle/pin_modes_splatam.py, same inputs as the mapping fixture):
+    mapping with ignore_outlier_depth_loss (mean over the masked pixels, splatam.py:545-559) and do_ba=True (pose AND
+    Gaussians get gradients, :505-510), each with the complete mapping loss."""
+    fm = dict(np.load(MODES))
+    ocam = orc.make_camera(*_cam_args(fx))
+    st = osl.new_state({k: fx[f"map_in_{k}"] for k in GAUSS})
+    q, t = fm["pose"][:4], fm["pose"][4:]
+    g = {}
+    ts = osl.TrackState(q, t) if mode == "ba" else None
+    loss = osl.map_iteration(orc, ocam, st, q, t, fx["rgb1"], fx["d1"][0], grads_out=g, ssim=True, isoflat=True,
+                             ignore_outlier_depth=(mode == "outlier"), ba=ts)
+    ref = fm[f"{mode}_losses"]
+    assert abs(loss - ref[0]) < 2e-5 * ref[0], (loss, ref)
+    if mode == "outlier":   # the mask bites: the depth term differs from the unmasked evaluation of the same inputs
+        assert fm["outlier_losses"][2] < 0.95 * fm["ba_losses"][2]
+    rows = _check_map_gradients(lambda k: g[k], dict(fx, **{f"map_grad_{k}": fm[f"{mode}_grad_{k}"] for k in GAUSS}))
+    assert rows.mean() > 0.99
+    if mode == "ba":
+        assert _relmax(g["pose"], fm["ba_grad_pose"]) < 1e-3, (g["pose"], fm["ba_grad_pose"])
+
+
 def test_init_camera_pose_matches_reference(fx):
     """initialize_camera_pose (splatam.py:844-863) on the fixture's poses of frames 0 and 1 (host arithmetic)."""
     import importlib
