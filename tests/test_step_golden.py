@@ -265,6 +265,50 @@ def test_gpu_map_step_matches_reference(fx):
 
 
 @pytest.mark.gpu
+def test_gpu_map_step_outlier_mode_matches_reference(fx):
+    """map_step(ignore_outlier_depth=True) with the complete mapping loss against the reference's own
+    get_loss(mapping=True, ignore_outlier_depth_loss=True) (tests/golden/splatam_modes_64x48.npz): the depth term is
+    the mean over the pixels with |err| < 10 * median(err), normaliser counted on the device."""
+    fm = dict(np.load(MODES))
+    pkg, ss, torch, dev, gcam = _gpu(fx)
+    gmap = ss.GaussianMap({k: fx[f"map_in_{k}"] for k in GAUSS}, device="cuda")
+    ws = ss.StepWorkspace(gcam, gmap.count, torch.device("cuda"))
+    pose = pkg.make_pose(fm["pose"][:4], fm["pose"][4:])
+    inv_nd = 1.0 / int((fx["d1"] > 0).sum())            # ignored in this mode: the normaliser is 1 / n(mask)
+    losses = ss.map_step(ws, gmap, pose, dev(fx["rgb1"]), dev(fx["d1"][0]), inv_nd, ssim=True, isoflat=True,
+                         ignore_outlier_depth=True)
+    torch.cuda.synchronize()
+    ref = fm["outlier_losses"]
+    assert abs(float(losses[0]) - ref[0]) < 2e-4 * ref[0], (float(losses[0]), ref[0])
+    g = {k: gmap.g[k].cpu().numpy() for k in GAUSS}
+    rows = _check_map_gradients(lambda k: g[k], dict(fx, **{f"map_grad_{k}": fm[f"outlier_grad_{k}"] for k in GAUSS}))
+    assert rows.mean() > 0.99
+
+
+@pytest.mark.gpu
+def test_gpu_map_step_ba_pose_gradient_matches_reference(fx):
+    """map_step(ba=PoseState) (isogs_map_step_ba) against the reference's own get_loss(mapping=True, do_ba=True): the
+    flat / iso terms do not depend on the pose, so the keyframe-pose gradient of the reference's complete loss is the
+    pose gradient of colour (0.8 L1 + 0.2 (1 - SSIM)) + depth -- what map_step(ba=..., ssim=True) evaluates."""
+    fm = dict(np.load(MODES))
+    pkg, ss, torch, dev, gcam = _gpu(fx)
+    gmap = ss.GaussianMap({k: fx[f"map_in_{k}"] for k in GAUSS}, device="cuda")
+    ws = ss.StepWorkspace(gcam, gmap.count, torch.device("cuda"))
+    ps = ss.PoseState(fm["pose"][:4], fm["pose"][4:], "cuda")
+    inv_nd = 1.0 / int((fx["d1"] > 0).sum())
+    lrs = dict(ss.MAPPING_LRS, cam_unnorm_rots=4e-4, cam_trans=2e-3)
+    losses = ss.map_step(ws, gmap, pkg.make_pose(fm["pose"][:4], fm["pose"][4:]), dev(fx["rgb1"]), dev(fx["d1"][0]), inv_nd,
+                         lrs=lrs, ssim=True, ba=ps)
+    torch.cuda.synchronize()
+    ref = fm["ba_losses"]
+    want = ref[1] + ref[2]                      # the recorded terms are the weighted ones: colour + depth, no flat / iso
+    assert abs(float(losses[0]) - want) < 5e-4 * want, (float(losses[0]), want, ref)
+    v = ws.v_pose.cpu().numpy()
+    assert _relmax(v, fm["ba_grad_pose"]) < 1e-3, (v, fm["ba_grad_pose"])
+    assert np.abs(ps.pose.cpu().numpy() - fm["pose"]).max() > 1e-4, "the pose must have taken its Adam step"
+
+
+@pytest.mark.gpu
 def test_gpu_add_new_gaussians_matches_reference(fx):
     """add_new_gaussians (splatam.py:799-841) at the tracked pose of frame 1: same pixels selected, in the
     same (row-major) order, same back-projected parameters ("anisotropic": no noise)."""
